@@ -1,0 +1,1010 @@
+// hj_api.cu -- the C ABI of include/hj_b200.h on top of the sm_100a kernels.
+//
+// One handle owns one CUDA device: a compute stream, a copy stream, the global
+// table, the overflow structures, the radix partition buffers and staging
+// buffers for host inputs.  Buffers grow on demand and are reused, so -- like
+// the reference, which allocates before gettimeofday (AtomicHashBuild.hpp:25-34)
+// -- a warmed-up handle allocates nothing inside a timed call.
+//
+// There is deliberately no CPU path in this file: without a device every entry
+// point fails with HJ_ECUDA.
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <new>
+
+#include "../../include/hj_b200.h"
+#include "gt_kernels.cuh"
+#include "rx_kernels.cuh"
+
+using namespace hj;
+
+namespace {
+
+enum Ev { E_T0 = 0, E_CLEAR, E_SAMPLE, E_BUILD, E_PROBE0, E_PROBE, E_JOIN0, E_JOIN, E_END, E_CP0, E_CPR, E_CPS,
+          E_RX,  // 5 events per relation: hist0, hist, scan, scatter1, scatter2
+          E_COUNT = E_RX + 10 };
+
+struct DevBuf {
+  u64* p = nullptr;
+  u64 cap = 0;  // in u64 elements
+};
+
+struct RelBufs {  // radix-side buffers for one relation
+  DevBuf tmp, out, ghist, offsets, cursors, poff, pcur, ptiles, one;
+};
+
+}  // namespace
+
+struct hj_handle {
+  hj_config cfg;
+  int device = 0;
+  int sm_count = 148;
+  u64 l2_bytes = 126ull << 20;
+  size_t smem_optin = 227 * 1024;
+  cudaStream_t stream = nullptr, copy_stream = nullptr;
+  cudaEvent_t ev[E_COUNT];
+  bool ev_set[E_COUNT];
+  u64* ctr = nullptr;    // device counters
+  u64* h_ctr = nullptr;  // pinned mirror
+  // global table
+  DevBuf table, ovf_table, ovf_list;
+  u64 slots = 0, mask = 0;
+  bool built = false;
+  // staging for host inputs
+  DevBuf stageR, stageS;
+  // radix
+  RelBufs rb[2];
+  DevBuf flush;
+  u32 launches = 0;
+  char err[256];
+};
+
+namespace {
+
+#define CK(call)                                                                                   \
+  do {                                                                                             \
+    cudaError_t e_ = (call);                                                                       \
+    if (e_ != cudaSuccess) {                                                                       \
+      snprintf(h->err, sizeof(h->err), "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+      return e_ == cudaErrorMemoryAllocation ? HJ_ENOMEM : HJ_ECUDA;                               \
+    }                                                                                              \
+  } while (0)
+
+int ensure(hj_handle* h, DevBuf& b, u64 elems) {
+  if (b.cap >= elems) return HJ_OK;
+  if (b.p) CK(cudaFree(b.p));
+  b.p = nullptr;
+  b.cap = 0;
+  CK(cudaMalloc(&b.p, elems * sizeof(u64)));
+  b.cap = elems;
+  return HJ_OK;
+}
+
+void mark(hj_handle* h, int e, cudaStream_t s = nullptr) {
+  cudaEventRecord(h->ev[e], s ? s : h->stream);
+  h->ev_set[e] = true;
+}
+float span_us(hj_handle* h, int a, int b) {
+  if (!h->ev_set[a] || !h->ev_set[b]) return 0.f;
+  float ms = 0.f;
+  if (cudaEventElapsedTime(&ms, h->ev[a], h->ev[b]) != cudaSuccess) return 0.f;
+  return ms * 1000.f;
+}
+
+bool is_device_ptr(const void* p) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+int grid_for(hj_handle* h, const void* kernel, int threads, size_t smem) {
+  int per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem) != cudaSuccess || per_sm < 1) {
+    cudaGetLastError();
+    per_sm = 1;
+  }
+  return h->sm_count * per_sm;
+}
+
+u32 ipt_for(u32 tsize) {
+  if (tsize == 0) return 4;
+  if (tsize >= 8) return 8;
+  if (tsize >= 4) return 4;
+  if (tsize >= 2) return 2;
+  return 1;
+}
+
+// ---- global table -------------------------------------------------------------
+
+template <int IPT, bool NOCC, bool STATS>
+int launch_build_t(hj_handle* h, const u64* R, const SegMap& sm, u64 key_mask) {
+  auto k = gt_build_kernel<IPT, NOCC, STATS>;
+  int grid = grid_for(h, (const void*)k, kGtThreads, 0);
+  u64 chunks = ((sm.seg_len + kGtThreads * IPT - 1) / (kGtThreads * IPT)) * sm.nslices;
+  if (chunks == 0) return HJ_OK;
+  if ((u64)grid > chunks) grid = (int)chunks;
+  k<<<grid, kGtThreads, 0, h->stream>>>(R, sm, h->table.p, h->mask, key_mask, h->cfg.probe_length, h->ovf_list.p,
+                                        h->ctr);
+  h->launches++;
+  CK(cudaGetLastError());
+  return HJ_OK;
+}
+
+int launch_build(hj_handle* h, const u64* R, const SegMap& sm, bool nocc, bool stats, u32 ipt) {
+  const u64 km = h->cfg.key_mask;
+  // 16-byte loads need even tuple offsets from a 16-byte aligned base
+  if ((((uintptr_t)R) & 15) || (sm.slice_stride & 1) || (sm.slice_off & 1)) ipt = 1;
+  if (stats) {
+    if (ipt == 1) return launch_build_t<1, false, true>(h, R, sm, km);
+    return launch_build_t<2, false, true>(h, R, sm, km);
+  }
+  if (nocc) {
+    switch (ipt) {
+      case 1: return launch_build_t<1, true, false>(h, R, sm, km);
+      case 2: return launch_build_t<2, true, false>(h, R, sm, km);
+      case 4: return launch_build_t<4, true, false>(h, R, sm, km);
+      default: return launch_build_t<8, true, false>(h, R, sm, km);
+    }
+  }
+  switch (ipt) {
+    case 1: return launch_build_t<1, false, false>(h, R, sm, km);
+    case 2: return launch_build_t<2, false, false>(h, R, sm, km);
+    case 4: return launch_build_t<4, false, false>(h, R, sm, km);
+    default: return launch_build_t<8, false, false>(h, R, sm, km);
+  }
+}
+
+template <int IPT>
+int launch_probe_t(hj_handle* h, const u64* S, u64 m) {
+  auto k = gt_probe_kernel<IPT>;
+  int grid = grid_for(h, (const void*)k, kGtThreads, 0);
+  u64 chunks = (m + kGtThreads * IPT - 1) / (kGtThreads * IPT);
+  if (chunks == 0) return HJ_OK;
+  if ((u64)grid > chunks) grid = (int)chunks;
+  k<<<grid, kGtThreads, 0, h->stream>>>(S, m, h->table.p, h->mask, h->cfg.key_mask, h->cfg.probe_length,
+                                        h->ovf_table.p, h->ovf_table.cap, h->ctr);
+  h->launches++;
+  CK(cudaGetLastError());
+  return HJ_OK;
+}
+int launch_probe(hj_handle* h, const u64* S, u64 m, u32 ipt) {
+  if (((uintptr_t)S) & 15) ipt = 1;
+  switch (ipt) {
+    case 1: return launch_probe_t<1>(h, S, m);
+    case 2: return launch_probe_t<2>(h, S, m);
+    case 4: return launch_probe_t<4>(h, S, m);
+    default: return launch_probe_t<8>(h, S, m);
+  }
+}
+
+int zero_async(hj_handle* h, u64* p, u64 elems) {
+  // 16 B stores from a full-chip grid; cudaMemsetAsync would do as well but a
+  // kernel keeps the launch accounting honest
+  if (elems == 0) return HJ_OK;
+  u64 n2 = elems / 2;
+  int grid = h->sm_count * 8;
+  fill_zero_kernel<<<grid, 256, 0, h->stream>>>(reinterpret_cast<ulonglong2*>(p), n2);
+  h->launches++;
+  if (elems & 1) CK(cudaMemsetAsync(p + elems - 1, 0, 8, h->stream));
+  CK(cudaGetLastError());
+  return HJ_OK;
+}
+
+int prepare_table(hj_handle* h, u64 n) {
+  u32 scale = h->cfg.scale_output ? h->cfg.scale_output : 2;
+  u64 slots = pow2_ceil_u64(n * scale < 64 ? 64 : n * scale);
+  int rc;
+  if ((rc = ensure(h, h->table, slots))) return rc;
+  if ((rc = ensure(h, h->ovf_table, slots))) return rc;  // worst case: everything overflows, load 0.5
+  if ((rc = ensure(h, h->ovf_list, n ? n : 1))) return rc;
+  h->slots = slots;
+  h->mask = slots - 1;
+  return HJ_OK;
+}
+
+// Stage a host relation on the copy stream (or pass a device pointer through).
+// *pending is set when the compute stream still has to wait for ev_done.
+int stage(hj_handle* h, const u64* p, u64 n, DevBuf& buf, const u64** dev, int ev_done, bool* pending) {
+  *pending = false;
+  if (n == 0 || p == nullptr) {
+    *dev = nullptr;
+    return HJ_OK;
+  }
+  if (is_device_ptr(p)) {
+    *dev = p;
+    return HJ_OK;
+  }
+  int rc;
+  if ((rc = ensure(h, buf, n + (n & 1)))) return rc;
+  CK(cudaMemcpyAsync(buf.p, p, n * sizeof(u64), cudaMemcpyHostToDevice, h->copy_stream));
+  mark(h, ev_done, h->copy_stream);
+  *pending = true;
+  *dev = buf.p;
+  return HJ_OK;
+}
+int wait_staged(hj_handle* h, int ev_done, bool pending) {
+  if (pending) CK(cudaStreamWaitEvent(h->stream, h->ev[ev_done], 0));
+  return HJ_OK;
+}
+
+void reset_events(hj_handle* h) {
+  for (int i = 0; i < E_COUNT; i++) h->ev_set[i] = false;
+  h->launches = 0;
+}
+
+int fetch_counters(hj_handle* h) {
+  CK(cudaMemcpyAsync(h->h_ctr, h->ctr, C_COUNT * sizeof(u64), cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  return HJ_OK;
+}
+
+void fill_common(hj_handle* h, hj_result* r) {
+  const u64* c = h->h_ctr;
+  r->matches = c[C_MATCHES];
+  r->checksum = c[C_CHECKSUM];
+  r->window_matches = c[C_WINDOW_MATCHES];
+  r->conflicts = c[C_CONFLICTS];
+  r->cas_retries = c[C_CAS_RETRIES];
+  r->probe_steps = c[C_PROBE_STEPS];
+  r->sampled = c[C_SAMPLED];
+  r->sectors = c[C_SECTORS];
+  r->max_partition = c[C_MAX_PART];
+  r->kernel_launches = h->launches;
+  r->us_total = span_us(h, E_T0, E_END);
+  r->us_h2d = span_us(h, E_CP0, h->ev_set[E_CPS] ? E_CPS : E_CPR);
+  r->us_clear = span_us(h, E_T0, E_CLEAR);
+  r->us_sample = span_us(h, E_CLEAR, E_SAMPLE);
+  r->us_build = span_us(h, h->ev_set[E_SAMPLE] ? E_SAMPLE : E_CLEAR, E_BUILD);
+  r->us_probe = span_us(h, E_PROBE0, E_PROBE);
+  for (int rel = 0; rel < 2; rel++) {
+    const int b = E_RX + 5 * rel;
+    r->us_hist += span_us(h, b, b + 1);
+    r->us_scan += span_us(h, b + 1, b + 2);
+    r->us_scatter1 += span_us(h, b + 2, b + 3);
+    r->us_scatter2 += span_us(h, b + 3, b + 4);
+  }
+  r->us_join = span_us(h, E_JOIN0, E_JOIN);
+}
+
+// contention signal of the sampling round (see DESIGN.md "Adaptive switch")
+double contention_of(hj_handle* h) {
+  const u64* c = h->h_ctr;
+  if (c[C_SAMPLED] == 0) return 0.0;
+  double retry = (double)c[C_CAS_RETRIES] / (double)c[C_SAMPLED];
+  double span_bytes = c[C_CHUNKS] ? 8.0 * (double)c[C_SPAN] / (double)c[C_CHUNKS] : 0.0;
+  double locality = span_bytes / (double)h->l2_bytes;
+  if (locality > 1.0) locality = 1.0;
+  return locality + retry;
+}
+
+SegMap whole(u64 n) {
+  SegMap sm;
+  sm.n = n;
+  sm.seg_len = n;
+  sm.slice_stride = 0;
+  sm.slice_off = 0;
+  sm.nslices = 1;
+  return sm;
+}
+
+// Sampling geometry of HTMHashBuild.hpp:100-113: 64 slices, K*16384 tuples each.
+void sample_geometry(const hj_handle* h, u64 n, u64* stride, u64* sample_len) {
+  const u64 nsl = 64;
+  u32 K = h->cfg.sample_rounds ? h->cfg.sample_rounds : 5;
+  u64 st = n / nsl;
+  u64 sl = (u64)K * 16384ull;
+  if (st < 2) {  // tiny relation: one slice, sample an eighth
+    *stride = 0;
+    *sample_len = n / 8 ? n / 8 : n;
+    return;
+  }
+  if (sl > st / 4) sl = st / 4 ? st / 4 : 1;  // never sample more than a quarter
+  *stride = st;
+  *sample_len = sl;
+}
+
+int run_sample(hj_handle* h, const u64* dR, u64 n, u64* stride_out, u64* len_out) {
+  u64 stride, slen;
+  sample_geometry(h, n, &stride, &slen);
+  SegMap sm;
+  sm.n = n;
+  sm.seg_len = slen;
+  sm.slice_stride = stride;
+  sm.slice_off = 0;
+  sm.nslices = stride ? 64 : 1;
+  *stride_out = stride;
+  *len_out = slen;
+  return launch_build(h, dR, sm, false, true, 2);
+}
+
+int run_build_rest(hj_handle* h, const u64* dR, u64 n, u64 stride, u64 slen, bool nocc, u32 ipt) {
+  int rc;
+  if (stride == 0) {  // single slice: the rest is [slen, n)
+    SegMap sm;
+    sm.n = n; sm.seg_len = n - slen; sm.slice_stride = 0; sm.slice_off = slen; sm.nslices = 1;
+    return sm.seg_len ? launch_build(h, dR, sm, nocc, false, ipt) : HJ_OK;
+  }
+  SegMap sm;
+  sm.n = n; sm.seg_len = stride - slen; sm.slice_stride = stride; sm.slice_off = slen; sm.nslices = 64;
+  if ((rc = launch_build(h, dR, sm, nocc, false, ipt))) return rc;
+  if (64 * stride < n) {  // tail not covered by the 64 slices
+    SegMap t;
+    t.n = n; t.seg_len = n - 64 * stride; t.slice_stride = 0; t.slice_off = 64 * stride; t.nslices = 1;
+    if ((rc = launch_build(h, dR, t, nocc, false, ipt))) return rc;
+  }
+  return HJ_OK;
+}
+
+int run_overflow(hj_handle* h) {
+  int grid = h->sm_count * 4;
+  gt_ovf_clear_kernel<<<grid, 256, 0, h->stream>>>(h->ovf_table.p, h->ctr, h->ovf_table.cap);
+  gt_ovf_insert_kernel<<<grid, 256, 0, h->stream>>>(h->ovf_list.p, h->ovf_table.p, h->ctr, h->cfg.key_mask,
+                                                    h->ovf_table.cap);
+  h->launches += 2;
+  CK(cudaGetLastError());
+  return HJ_OK;
+}
+
+int clear_probe_counters(hj_handle* h) {
+  CK(cudaMemsetAsync(h->ctr + C_MATCHES, 0, 3 * sizeof(u64), h->stream));
+  return HJ_OK;
+}
+
+// ---- radix --------------------------------------------------------------------
+
+struct RadixPlan {
+  u32 bits, passes, b1, b2;
+  u32 slots;        // join table slots
+  u32 tile_ipt;     // scatter items per thread
+};
+
+constexpr u32 kMaxBitsPerPass = 12;
+constexpr u32 kMaxTotalBits = 15;  // 2^15 bins * 4 B = 128 KiB privatised histogram
+
+int plan_radix(hj_handle* h, u64 n, RadixPlan* pl) {
+  u32 bits = 0;
+  if (h->cfg.num_partitions) {
+    u32 f = h->cfg.num_partitions;
+    if (f & (f - 1)) return HJ_EINVAL;
+    while ((1u << bits) < f) bits++;
+  } else {
+    // default: R partitions of <= 4096 tuples -> 8192-slot (64 KiB) tables, 3 CTAs per SM
+    while (bits < kMaxTotalBits && (n >> bits) > 4096) bits++;
+    if (bits < 4) bits = 4;
+  }
+  if (bits < 1 || bits > kMaxTotalBits) return HJ_EINVAL;
+  u32 passes = h->cfg.passes;
+  if (passes == 0) passes = bits > 8 ? 2 : 1;
+  if (passes > 2) return HJ_EINVAL;
+  if (passes == 1 && bits > kMaxBitsPerPass) return HJ_EINVAL;
+  if (passes == 2 && bits < 2) passes = 1;
+  pl->bits = bits;
+  pl->passes = passes;
+  pl->b1 = passes == 2 ? bits / 2 : bits;  // prj_params.h:76-78: pass 1 gets floor(b/2)
+  pl->b2 = bits - pl->b1;
+  // join table: expected partition * 2, power of two, capped by shared memory
+  u64 per = (n >> bits) + 1;
+  u64 slots = pow2_ceil_u64(per * 2 < 1024 ? 1024 : per * 2);
+  u64 cap = 1;
+  while (cap * 2 * sizeof(u64) <= h->smem_optin - 1024) cap *= 2;  // 16384 slots at 227 KB
+  if (slots > cap) slots = cap;
+  pl->slots = (u32)slots;
+  pl->tile_ipt = 8;
+  return HJ_OK;
+}
+
+int ensure_rel(hj_handle* h, RelBufs& rb, u64 n, const RadixPlan& pl) {
+  int rc;
+  u64 nb = 1ull << pl.bits;
+  u64 np = 1ull << pl.b1;
+  if ((rc = ensure(h, rb.out, n + 2))) return rc;
+  if (pl.passes == 2 && (rc = ensure(h, rb.tmp, n + 2))) return rc;
+  if ((rc = ensure(h, rb.ghist, nb))) return rc;
+  if ((rc = ensure(h, rb.offsets, nb + 1))) return rc;
+  if ((rc = ensure(h, rb.cursors, nb))) return rc;
+  if ((rc = ensure(h, rb.poff, np + 2))) return rc;
+  if ((rc = ensure(h, rb.pcur, np + 2))) return rc;
+  if ((rc = ensure(h, rb.ptiles, np + 2))) return rc;
+  if ((rc = ensure(h, rb.one, 4))) return rc;
+  return HJ_OK;
+}
+
+template <int IPT>
+int launch_scatter_t(hj_handle* h, const u64* in, u64* out, const Digit& dg, u32 F, u32 nparent, const u64* poff,
+                     const u64* ptiles, u64* cursors, u64 max_tiles) {
+  auto k = rx_scatter_kernel<IPT>;
+  size_t smem = (size_t)kScThreads * IPT * 8 + (size_t)F * 16;
+  CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int grid = grid_for(h, (const void*)k, kScThreads, smem);
+  if ((u64)grid > max_tiles) grid = (int)(max_tiles ? max_tiles : 1);
+  k<<<grid, kScThreads, smem, h->stream>>>(in, out, dg, F, nparent, poff, ptiles, cursors);
+  h->launches++;
+  CK(cudaGetLastError());
+  return HJ_OK;
+}
+
+// Partition `in` (device, n tuples) by pl into rb.out; rb.offsets gets 2^bits+1 offsets.
+// evb = first of this relation's five phase events (or -1: untimed).
+int radix_partition_rel(hj_handle* h, const u64* in, u64 n, RelBufs& rb, const RadixPlan& pl, int evb) {
+  const u32 nb = 1u << pl.bits;
+  const u32 F1 = 1u << pl.b1, F2 = 1u << pl.b2;
+  const u32 tile = kScThreads * pl.tile_ipt;
+  Digit full;
+  memset(&full, 0, sizeof(full));
+  full.key_mask = h->cfg.key_mask;
+  if (pl.passes == 2) { full.mode = 1; full.b1 = pl.b1; full.b2 = pl.b2; }
+  else { full.mode = 0; full.shift = 0; full.bits = pl.bits; }
+
+  if (evb >= 0) mark(h, evb);
+  CK(cudaMemsetAsync(rb.ghist.p, 0, nb * sizeof(u64), h->stream));
+  {
+    size_t smem = (size_t)nb * 4;
+    auto k = rx_hist_kernel<true>;
+    CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int grid = grid_for(h, (const void*)k, kHistThreads, smem);
+    u64 tiles = (n + kHistThreads * kHistIPT - 1) / (kHistThreads * kHistIPT);
+    if ((u64)grid > tiles) grid = (int)(tiles ? tiles : 1);
+    k<<<grid, kHistThreads, smem, h->stream>>>(in, n, full, nb, rb.ghist.p);
+    h->launches++;
+    CK(cudaGetLastError());
+  }
+  if (evb >= 0) mark(h, evb + 1);
+  // scan: final offsets, the pass-1 ("parent") view and the one-parent view {0,n}.
+  // Single pass: f2 = nb makes parent 0 span every bin.
+  rx_scan_kernel<<<1, kScanThreads, 0, h->stream>>>(rb.ghist.p, nb, rb.offsets.p, rb.cursors.p,
+                                                    pl.passes == 2 ? F2 : nb, rb.poff.p, rb.pcur.p, rb.ptiles.p,
+                                                    rb.one.p, tile, nullptr);
+  h->launches++;
+  CK(cudaGetLastError());
+  if (evb >= 0) mark(h, evb + 2);
+
+  const u64 max_tiles1 = (n + tile - 1) / tile;
+  int rc;
+  if (pl.passes == 1) {
+    if ((rc = launch_scatter_t<8>(h, in, rb.out.p, full, nb, 1, rb.poff.p, rb.ptiles.p, rb.cursors.p, max_tiles1)))
+      return rc;
+    if (evb >= 0) { mark(h, evb + 3); mark(h, evb + 4); }
+  } else {
+    // pass 1: the whole relation by the low b1 bits into tmp, claiming from the parent cursors
+    Digit d1;
+    memset(&d1, 0, sizeof(d1));
+    d1.key_mask = h->cfg.key_mask; d1.mode = 0; d1.shift = 0; d1.bits = pl.b1;
+    if ((rc = launch_scatter_t<8>(h, in, rb.tmp.p, d1, F1, 1, rb.one.p, rb.one.p + 2, rb.pcur.p, max_tiles1)))
+      return rc;
+    if (evb >= 0) mark(h, evb + 3);
+    // pass 2: every pass-1 partition by the next b2 bits into out (radix_cluster, :402-440)
+    Digit d2;
+    memset(&d2, 0, sizeof(d2));
+    d2.key_mask = h->cfg.key_mask; d2.mode = 0; d2.shift = pl.b1; d2.bits = pl.b2;
+    if ((rc = launch_scatter_t<8>(h, rb.tmp.p, rb.out.p, d2, F2, F1, rb.poff.p, rb.ptiles.p, rb.cursors.p,
+                                  max_tiles1 + F1)))
+      return rc;
+    if (evb >= 0) mark(h, evb + 4);
+  }
+  return HJ_OK;
+}
+
+int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS, u64 m, bool pendS, hj_result* res) {
+  RadixPlan pl;
+  int rc;
+  if ((rc = plan_radix(h, n, &pl))) {
+    snprintf(h->err, sizeof(h->err), "radix plan: numPartitions must be a power of two <= 2^%u (<= 2^%u for 1 pass)",
+             kMaxTotalBits, kMaxBitsPerPass);
+    return rc;
+  }
+  if ((rc = ensure_rel(h, h->rb[0], n, pl))) return rc;
+  if (dS && (rc = ensure_rel(h, h->rb[1], m, pl))) return rc;
+  CK(cudaMemsetAsync(h->ctr, 0, C_COUNT * sizeof(u64), h->stream));
+  if ((rc = wait_staged(h, E_CPR, pendR))) return rc;
+  if ((rc = radix_partition_rel(h, dR, n, h->rb[0], pl, E_RX))) return rc;
+  if (dS) {
+    if ((rc = wait_staged(h, E_CPS, pendS))) return rc;
+    if ((rc = radix_partition_rel(h, dS, m, h->rb[1], pl, E_RX + 5))) return rc;
+  }
+  mark(h, E_JOIN0);
+  {
+    size_t smem = (size_t)pl.slots * 8;
+    auto k = rx_join_kernel;
+    CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int grid = grid_for(h, (const void*)k, kJoinThreads, smem);
+    u32 nparts = 1u << pl.bits;
+    if ((u32)grid > nparts) grid = (int)nparts;
+    k<<<grid, kJoinThreads, smem, h->stream>>>(h->rb[0].out.p, h->rb[0].offsets.p, dS ? h->rb[1].out.p : nullptr,
+                                               dS ? h->rb[1].offsets.p : nullptr, nparts, pl.bits, pl.slots,
+                                               h->cfg.key_mask, h->ctr);
+    h->launches++;
+    CK(cudaGetLastError());
+  }
+  mark(h, E_JOIN);
+  mark(h, E_END);
+  if ((rc = fetch_counters(h))) return rc;
+  if (res) {
+    fill_common(h, res);
+    res->path_taken = HJ_PATH_RADIX;
+    res->radix_bits = pl.bits;
+    res->passes = pl.passes;
+    res->hbm_bytes = 8ull * (2 * pl.passes + 1) * (n + (dS ? m : 0));  // 8*(2P+1) per tuple
+  }
+  return HJ_OK;
+}
+
+int run_global_join(hj_handle* h, const u64* dR, u64 n, const u64* dS, u64 m, bool pendS, bool nocc,
+                    bool adaptive_prefix, u64 stride, u64 slen, hj_result* res) {
+  int rc;
+  const u32 ipt = ipt_for(h->cfg.transaction_size);
+  if (!adaptive_prefix) {
+    if ((rc = launch_build(h, dR, whole(n), nocc, false, ipt))) return rc;
+  } else {
+    if ((rc = run_build_rest(h, dR, n, stride, slen, nocc, ipt))) return rc;
+  }
+  if ((rc = run_overflow(h))) return rc;
+  mark(h, E_BUILD);
+  h->built = true;
+  if (dS && m) {
+    if ((rc = wait_staged(h, E_CPS, pendS))) return rc;
+    mark(h, E_PROBE0);
+    if ((rc = launch_probe(h, dS, m, ipt))) return rc;
+    mark(h, E_PROBE);
+  }
+  mark(h, E_END);
+  if ((rc = fetch_counters(h))) return rc;
+  if (res) {
+    fill_common(h, res);
+    res->path_taken = HJ_PATH_GLOBAL;
+    res->hbm_bytes = 16ull * n + 16ull * (dS ? m : 0);  // 16 B per R tuple + 16 B per S tuple
+  }
+  return HJ_OK;
+}
+
+}  // namespace
+
+// ===========================================================================
+// C ABI
+// ===========================================================================
+extern "C" {
+
+int hj_abi_version(void) { return HJ_ABI_VERSION; }
+
+int hj_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+const char* hj_strerror(int code) {
+  switch (code) {
+    case HJ_OK: return "ok";
+    case HJ_EINVAL: return "invalid argument";
+    case HJ_ENOMEM: return "out of memory";
+    case HJ_ECUDA: return "CUDA error (no usable device, or a runtime failure; see hj_last_error)";
+    case HJ_EOVERFLOW: return "partition overflow";
+    case HJ_ESTATE: return "call order violated";
+    default: return "unknown error";
+  }
+}
+
+const char* hj_last_error(const hj_handle* h) { return h ? h->err : "null handle"; }
+
+void hj_config_default(hj_config* cfg) {
+  if (!cfg) return;
+  memset(cfg, 0, sizeof(*cfg));
+  cfg->struct_size = sizeof(hj_config);
+  cfg->algo = HJ_ALGO_ATOMIC;
+  cfg->device = 0;
+  cfg->probe_length = 4;      // main.cpp:81
+  cfg->scale_output = 2;      // main.cpp:84
+  cfg->num_partitions = 0;
+  cfg->passes = 0;
+  cfg->transaction_size = 16; // main.cpp:83
+  cfg->enable_probe = 1;
+  cfg->sample_rounds = 5;     // HTMHashBuild.hpp:48-52 (HTM_SWITCH)
+  cfg->key_mask = ~0ull;
+  cfg->adaptive_threshold = 0.0;
+}
+
+int hj_create(const hj_config* cfg, hj_handle** out) {
+  if (!cfg || !out || cfg->struct_size != sizeof(hj_config)) return HJ_EINVAL;
+  if (cfg->algo < HJ_ALGO_ATOMIC || cfg->algo > HJ_ALGO_ADAPTIVE) return HJ_EINVAL;
+  if (cfg->probe_length == 0 || cfg->probe_length > 1024) return HJ_EINVAL;
+  int ndev = hj_device_count();
+  if (ndev <= 0 || cfg->device < 0 || cfg->device >= ndev) return HJ_ECUDA;
+  hj_handle* h = new (std::nothrow) hj_handle();
+  if (!h) return HJ_ENOMEM;
+  h->cfg = *cfg;
+  if (h->cfg.key_mask == 0) h->cfg.key_mask = ~0ull;
+  h->device = cfg->device;
+  h->err[0] = 0;
+  for (int i = 0; i < E_COUNT; i++) h->ev_set[i] = false;
+  auto fail = [&](int code) { hj_destroy(h); return code; };
+  if (cudaSetDevice(h->device) != cudaSuccess) return fail(HJ_ECUDA);
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, h->device) != cudaSuccess) return fail(HJ_ECUDA);
+  h->sm_count = prop.multiProcessorCount;
+  h->l2_bytes = prop.l2CacheSize ? (u64)prop.l2CacheSize : (126ull << 20);
+  h->smem_optin = prop.sharedMemPerBlockOptin;
+  if (cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess) return fail(HJ_ECUDA);
+  if (cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking) != cudaSuccess) return fail(HJ_ECUDA);
+  for (int i = 0; i < E_COUNT; i++)
+    if (cudaEventCreate(&h->ev[i]) != cudaSuccess) return fail(HJ_ECUDA);
+  if (cudaMalloc(&h->ctr, C_COUNT * sizeof(u64)) != cudaSuccess) return fail(HJ_ENOMEM);
+  if (cudaMallocHost(&h->h_ctr, C_COUNT * sizeof(u64)) != cudaSuccess) return fail(HJ_ENOMEM);
+  cudaMemset(h->ctr, 0, C_COUNT * sizeof(u64));
+  *out = h;
+  return HJ_OK;
+}
+
+void hj_destroy(hj_handle* h) {
+  if (!h) return;
+  cudaSetDevice(h->device);
+  if (h->stream) cudaStreamSynchronize(h->stream);
+  DevBuf* bufs[] = {&h->table, &h->ovf_table, &h->ovf_list, &h->stageR, &h->stageS, &h->flush};
+  for (DevBuf* b : bufs)
+    if (b->p) cudaFree(b->p);
+  for (RelBufs& rb : h->rb) {
+    DevBuf* rbufs[] = {&rb.tmp, &rb.out, &rb.ghist, &rb.offsets, &rb.cursors, &rb.poff, &rb.pcur, &rb.ptiles, &rb.one};
+    for (DevBuf* b : rbufs)
+      if (b->p) cudaFree(b->p);
+  }
+  if (h->ctr) cudaFree(h->ctr);
+  if (h->h_ctr) cudaFreeHost(h->h_ctr);
+  for (int i = 0; i < E_COUNT; i++)
+    if (h->ev[i]) cudaEventDestroy(h->ev[i]);
+  if (h->stream) cudaStreamDestroy(h->stream);
+  if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
+  delete h;
+}
+
+int hj_reserve(hj_handle* h, uint64_t max_r, uint64_t max_s) {
+  if (!h) return HJ_EINVAL;
+  CK(cudaSetDevice(h->device));
+  int rc;
+  if (h->cfg.algo != HJ_ALGO_RADIX) {
+    if ((rc = prepare_table(h, max_r))) return rc;
+  }
+  if (h->cfg.algo == HJ_ALGO_RADIX || h->cfg.algo == HJ_ALGO_ADAPTIVE) {
+    RadixPlan pl;
+    if ((rc = plan_radix(h, max_r, &pl))) return rc;
+    if ((rc = ensure_rel(h, h->rb[0], max_r, pl))) return rc;
+    if (max_s && (rc = ensure_rel(h, h->rb[1], max_s, pl))) return rc;
+  }
+  return HJ_OK;
+}
+
+int hj_build(hj_handle* h, const uint64_t* R, uint64_t n, hj_result* res) {
+  if (!h || !R || !n) return HJ_EINVAL;
+  if (h->cfg.algo == HJ_ALGO_RADIX) return HJ_ESTATE;  // the radix path has no standalone table
+  CK(cudaSetDevice(h->device));
+  if (res) memset(res, 0, sizeof(*res));
+  reset_events(h);
+  int rc;
+  if ((rc = prepare_table(h, n))) return rc;
+  mark(h, E_T0);
+  CK(cudaMemsetAsync(h->ctr, 0, C_COUNT * sizeof(u64), h->stream));
+  if ((rc = zero_async(h, h->table.p, h->slots))) return rc;
+  mark(h, E_CLEAR);
+  const u64* dR = nullptr;
+  bool pendR = false;
+  mark(h, E_CP0, h->copy_stream);
+  if ((rc = stage(h, (const u64*)R, n, h->stageR, &dR, E_CPR, &pendR))) return rc;
+  if ((rc = wait_staged(h, E_CPR, pendR))) return rc;
+  return run_global_join(h, dR, n, nullptr, 0, false, h->cfg.algo == HJ_ALGO_NOCC, false, 0, 0, res);
+}
+
+int hj_probe(hj_handle* h, const uint64_t* S, uint64_t m, hj_result* res) {
+  if (!h || (!S && m)) return HJ_EINVAL;
+  if (!h->built) return HJ_ESTATE;
+  CK(cudaSetDevice(h->device));
+  if (res) memset(res, 0, sizeof(*res));
+  reset_events(h);
+  int rc;
+  const u64* dS = nullptr;
+  bool pendS = false;
+  mark(h, E_CP0, h->copy_stream);
+  if ((rc = stage(h, (const u64*)S, m, h->stageS, &dS, E_CPS, &pendS))) return rc;
+  if ((rc = wait_staged(h, E_CPS, pendS))) return rc;
+  mark(h, E_T0);
+  if ((rc = clear_probe_counters(h))) return rc;
+  mark(h, E_PROBE0);
+  if (m && (rc = launch_probe(h, dS, m, ipt_for(h->cfg.transaction_size)))) return rc;
+  mark(h, E_PROBE);
+  mark(h, E_END);
+  if ((rc = fetch_counters(h))) return rc;
+  if (res) {
+    fill_common(h, res);
+    res->path_taken = HJ_PATH_GLOBAL;
+    res->hbm_bytes = 16ull * m;
+  }
+  return HJ_OK;
+}
+
+int hj_sample(hj_handle* h, const uint64_t* R, uint64_t n, hj_result* res) {
+  if (!h || !R || !n) return HJ_EINVAL;
+  if (h->cfg.algo == HJ_ALGO_RADIX) return HJ_ESTATE;
+  CK(cudaSetDevice(h->device));
+  if (res) memset(res, 0, sizeof(*res));
+  reset_events(h);
+  int rc;
+  if ((rc = prepare_table(h, n))) return rc;
+  mark(h, E_T0);
+  CK(cudaMemsetAsync(h->ctr, 0, C_COUNT * sizeof(u64), h->stream));
+  if ((rc = zero_async(h, h->table.p, h->slots))) return rc;
+  mark(h, E_CLEAR);
+  const u64* dR = nullptr;
+  bool pendR = false;
+  mark(h, E_CP0, h->copy_stream);
+  if ((rc = stage(h, (const u64*)R, n, h->stageR, &dR, E_CPR, &pendR))) return rc;
+  if ((rc = wait_staged(h, E_CPR, pendR))) return rc;
+  u64 stride, slen;
+  if ((rc = run_sample(h, dR, n, &stride, &slen))) return rc;
+  mark(h, E_SAMPLE);
+  mark(h, E_END);
+  if ((rc = fetch_counters(h))) return rc;
+  h->built = false;
+  if (res) {
+    fill_common(h, res);
+    res->us_build = 0.f;
+    res->contention = contention_of(h);
+    res->path_taken = HJ_PATH_NONE;
+  }
+  return HJ_OK;
+}
+
+int hj_join(hj_handle* h, const uint64_t* R, uint64_t n, const uint64_t* S, uint64_t m, hj_result* res) {
+  if (!h || !R || !n) return HJ_EINVAL;
+  if (!S) m = 0;
+  if (!h->cfg.enable_probe || m == 0) { S = nullptr; m = 0; }
+  CK(cudaSetDevice(h->device));
+  if (res) memset(res, 0, sizeof(*res));
+  reset_events(h);
+  int rc;
+  const int algo = h->cfg.algo;
+  const u64 *dR = nullptr, *dS = nullptr;
+  bool pendR = false, pendS = false;
+  if (algo == HJ_ALGO_RADIX) {
+    mark(h, E_T0);
+    mark(h, E_CP0, h->copy_stream);
+    if ((rc = stage(h, (const u64*)R, n, h->stageR, &dR, E_CPR, &pendR))) return rc;
+    if ((rc = stage(h, (const u64*)S, m, h->stageS, &dS, E_CPS, &pendS))) return rc;
+    return run_radix_join(h, dR, n, pendR, dS, m, pendS, res);
+  }
+  // the table clear needs no input: enqueue it first so it runs under the R copy
+  if ((rc = prepare_table(h, n))) return rc;
+  mark(h, E_T0);
+  CK(cudaMemsetAsync(h->ctr, 0, C_COUNT * sizeof(u64), h->stream));
+  if ((rc = zero_async(h, h->table.p, h->slots))) return rc;
+  mark(h, E_CLEAR);
+  mark(h, E_CP0, h->copy_stream);
+  if ((rc = stage(h, (const u64*)R, n, h->stageR, &dR, E_CPR, &pendR))) return rc;
+  if ((rc = wait_staged(h, E_CPR, pendR))) return rc;
+  if (algo == HJ_ALGO_ATOMIC || algo == HJ_ALGO_NOCC) {
+    // launch the build before staging S so the S copy runs under it
+    // (run_global_join waits for S right before the probe)
+    const bool host_s = S && !is_device_ptr(S);
+    if (!host_s) {
+      if ((rc = stage(h, (const u64*)S, m, h->stageS, &dS, E_CPS, &pendS))) return rc;
+      return run_global_join(h, dR, n, dS, m, pendS, algo == HJ_ALGO_NOCC, false, 0, 0, res);
+    }
+    const u32 ipt = ipt_for(h->cfg.transaction_size);
+    if ((rc = launch_build(h, dR, whole(n), algo == HJ_ALGO_NOCC, false, ipt))) return rc;
+    if ((rc = run_overflow(h))) return rc;
+    mark(h, E_BUILD);
+    h->built = true;
+    if ((rc = stage(h, (const u64*)S, m, h->stageS, &dS, E_CPS, &pendS))) return rc;
+    if ((rc = wait_staged(h, E_CPS, pendS))) return rc;
+    mark(h, E_PROBE0);
+    if ((rc = launch_probe(h, dS, m, ipt))) return rc;
+    mark(h, E_PROBE);
+    mark(h, E_END);
+    if ((rc = fetch_counters(h))) return rc;
+    if (res) {
+      fill_common(h, res);
+      res->path_taken = HJ_PATH_GLOBAL;
+      res->hbm_bytes = 16ull * n + 16ull * m;
+    }
+    return HJ_OK;
+  }
+
+  // HJ_ALGO_ADAPTIVE: HTMHashBuild.hpp:100-156 -- sample, measure, decide.
+  u64 stride, slen;
+  if ((rc = run_sample(h, dR, n, &stride, &slen))) return rc;
+  mark(h, E_SAMPLE);
+  if ((rc = stage(h, (const u64*)S, m, h->stageS, &dS, E_CPS, &pendS))) return rc;
+  if ((rc = fetch_counters(h))) return rc;
+  const double contention = contention_of(h);
+  const u64 sampled = h->h_ctr[C_SAMPLED], retries = h->h_ctr[C_CAS_RETRIES], sectors = h->h_ctr[C_SECTORS];
+  const float us_sample = span_us(h, E_CLEAR, E_SAMPLE), us_clear = span_us(h, E_T0, E_CLEAR);
+  const double thr = h->cfg.adaptive_threshold > 0 ? h->cfg.adaptive_threshold : 0.25;
+  if (contention > thr) {
+    // radix path; the sampled prefix is abandoned with the table
+    h->built = false;
+    rc = run_radix_join(h, dR, n, false, dS, m, pendS, res);
+    if (res && rc == HJ_OK) {
+      res->contention = contention;
+      res->sampled = sampled;
+      res->cas_retries = retries;
+      res->sectors = sectors;
+      res->us_sample = us_sample;
+      res->us_clear = us_clear;
+    }
+    return rc;
+  }
+  // global path: the sampled prefix stays inserted (HTMHashBuild.hpp:170)
+  rc = run_global_join(h, dR, n, dS, m, pendS, false, true, stride, slen, res);
+  if (res && rc == HJ_OK) {
+    res->contention = contention;
+    res->us_sample = us_sample;
+  }
+  return rc;
+}
+
+int hj_checksums(hj_handle* h, const uint64_t* R, uint64_t n, hj_result* res) {
+  if (!h || !res) return HJ_EINVAL;
+  CK(cudaSetDevice(h->device));
+  int rc;
+  const u64* dR = nullptr;
+  if (R && n) {
+    bool pend = false;
+    if ((rc = stage(h, (const u64*)R, n, h->stageR, &dR, E_CPR, &pend))) return rc;
+    if ((rc = wait_staged(h, E_CPR, pend))) return rc;
+  }
+  CK(cudaMemsetAsync(h->ctr + C_SUM0, 0, 3 * sizeof(u64), h->stream));
+  int grid = h->sm_count * 8;
+  if (dR) sum_u64_kernel<<<grid, 256, 0, h->stream>>>(dR, n, h->ctr + C_SUM0);
+  if (h->built) {
+    sum_u64_kernel<<<grid, 256, 0, h->stream>>>(h->table.p, h->slots, h->ctr + C_SUM1);
+    sum_ovf_kernel<<<grid, 256, 0, h->stream>>>(h->ovf_list.p, h->ctr, h->ctr + C_SUM2);
+  }
+  CK(cudaGetLastError());
+  if ((rc = fetch_counters(h))) return rc;
+  res->input_sum = h->h_ctr[C_SUM0];
+  res->table_sum = h->h_ctr[C_SUM1];
+  res->overflow_sum = h->h_ctr[C_SUM2];
+  res->conflicts = h->h_ctr[C_CONFLICTS];
+  return HJ_OK;
+}
+
+int hj_radix_partition(hj_handle* h, const uint64_t* in, uint64_t n, uint32_t shift, uint32_t bits, uint64_t* out,
+                       uint64_t* offsets) {
+  if (!h || !in || !out || !offsets || bits < 1 || bits > kMaxBitsPerPass) return HJ_EINVAL;
+  if (!is_device_ptr(in) || !is_device_ptr(out) || !is_device_ptr(offsets)) return HJ_EINVAL;
+  CK(cudaSetDevice(h->device));
+  RelBufs& rb = h->rb[0];
+  const u32 F = 1u << bits;
+  int rc;
+  if ((rc = ensure(h, rb.ghist, F < 8 ? 8 : F))) return rc;
+  if ((rc = ensure(h, rb.cursors, F))) return rc;
+  if ((rc = ensure(h, rb.poff, 4))) return rc;
+  if ((rc = ensure(h, rb.pcur, 4))) return rc;
+  if ((rc = ensure(h, rb.ptiles, 4))) return rc;
+  if ((rc = ensure(h, rb.one, 4))) return rc;
+  Digit dg;
+  memset(&dg, 0, sizeof(dg));
+  dg.key_mask = h->cfg.key_mask; dg.mode = 0; dg.shift = shift; dg.bits = bits;
+  const u32 tile = kScThreads * 8;
+  CK(cudaMemsetAsync(rb.ghist.p, 0, F * sizeof(u64), h->stream));
+  size_t smem = (size_t)F * 4;
+  auto k = rx_hist_kernel<true>;
+  CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int grid = grid_for(h, (const void*)k, kHistThreads, smem);
+  k<<<grid, kHistThreads, smem, h->stream>>>((const u64*)in, n, dg, F, rb.ghist.p);
+  rx_scan_kernel<<<1, kScanThreads, 0, h->stream>>>(rb.ghist.p, F, (u64*)offsets, rb.cursors.p, F, rb.poff.p,
+                                                    rb.pcur.p, rb.ptiles.p, rb.one.p, tile, nullptr);
+  CK(cudaGetLastError());
+  if ((rc = launch_scatter_t<8>(h, (const u64*)in, (u64*)out, dg, F, 1, rb.poff.p, rb.ptiles.p, rb.cursors.p,
+                                (n + tile - 1) / tile)))
+    return rc;
+  CK(cudaStreamSynchronize(h->stream));
+  return HJ_OK;
+}
+
+int hj_exchange_partition(hj_handle* h, const uint64_t* in, uint64_t n, uint32_t n_dest, uint32_t domain_bits,
+                          uint64_t* out, uint64_t* offsets) {
+  if (!h || !in || !out || !offsets || n_dest < 1 || n_dest > 4096 || domain_bits > 62) return HJ_EINVAL;
+  if (!is_device_ptr(in) || !is_device_ptr(out) || !is_device_ptr(offsets)) return HJ_EINVAL;
+  CK(cudaSetDevice(h->device));
+  RelBufs& rb = h->rb[0];
+  const u32 F = n_dest;
+  int rc;
+  if ((rc = ensure(h, rb.ghist, F < 8 ? 8 : F))) return rc;
+  if ((rc = ensure(h, rb.cursors, F))) return rc;
+  if ((rc = ensure(h, rb.poff, 4))) return rc;
+  if ((rc = ensure(h, rb.pcur, 4))) return rc;
+  if ((rc = ensure(h, rb.ptiles, 4))) return rc;
+  if ((rc = ensure(h, rb.one, 4))) return rc;
+  Digit dg;
+  memset(&dg, 0, sizeof(dg));
+  dg.key_mask = h->cfg.key_mask; dg.mode = 2; dg.ndest = n_dest; dg.domain_bits = domain_bits;
+  const u32 tile = kScThreads * 8;
+  CK(cudaMemsetAsync(rb.ghist.p, 0, F * sizeof(u64), h->stream));
+  size_t smem = (size_t)F * 4;
+  auto k = rx_hist_kernel<true>;
+  CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int grid = grid_for(h, (const void*)k, kHistThreads, smem);
+  k<<<grid, kHistThreads, smem, h->stream>>>((const u64*)in, n, dg, F, rb.ghist.p);
+  rx_scan_kernel<<<1, kScanThreads, 0, h->stream>>>(rb.ghist.p, F, (u64*)offsets, rb.cursors.p, F, rb.poff.p,
+                                                    rb.pcur.p, rb.ptiles.p, rb.one.p, tile, nullptr);
+  CK(cudaGetLastError());
+  if ((rc = launch_scatter_t<8>(h, (const u64*)in, (u64*)out, dg, F, 1, rb.poff.p, rb.ptiles.p, rb.cursors.p,
+                                (n + tile - 1) / tile)))
+    return rc;
+  CK(cudaStreamSynchronize(h->stream));
+  return HJ_OK;
+}
+
+int hj_generate(hj_handle* h, int kind, uint64_t first, uint64_t count, uint64_t domain, uint64_t seed,
+                uint64_t* out) {
+  if (!h || !out || kind < 0 || kind > 1) return HJ_EINVAL;
+  if (kind == 1 && (domain == 0 || (domain & (domain - 1)))) return HJ_EINVAL;
+  if (!is_device_ptr(out)) return HJ_EINVAL;
+  CK(cudaSetDevice(h->device));
+  u32 k = 0;
+  while ((1ull << k) < domain) k++;
+  gen_kernel<<<h->sm_count * 8, 256, 0, h->stream>>>(kind, first, count, k, seed, (u64*)out);
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(h->stream));
+  return HJ_OK;
+}
+
+int hj_device_alloc(hj_handle* h, uint64_t bytes, void** out) {
+  if (!h || !out) return HJ_EINVAL;
+  CK(cudaSetDevice(h->device));
+  CK(cudaMalloc(out, bytes ? bytes : 8));
+  return HJ_OK;
+}
+int hj_device_free(hj_handle* h, void* p) {
+  if (!h) return HJ_EINVAL;
+  CK(cudaSetDevice(h->device));
+  CK(cudaFree(p));
+  return HJ_OK;
+}
+int hj_host_alloc(uint64_t bytes, void** out) {
+  if (!out) return HJ_EINVAL;
+  if (cudaMallocHost(out, bytes ? bytes : 8) != cudaSuccess) {
+    cudaGetLastError();
+    return HJ_ENOMEM;
+  }
+  return HJ_OK;
+}
+int hj_host_free(void* p) {
+  if (cudaFreeHost(p) != cudaSuccess) {
+    cudaGetLastError();
+    return HJ_ECUDA;
+  }
+  return HJ_OK;
+}
+int hj_copy(hj_handle* h, void* dst, const void* src, uint64_t bytes) {
+  if (!h || !dst || !src) return HJ_EINVAL;
+  CK(cudaSetDevice(h->device));
+  CK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  return HJ_OK;
+}
+int hj_flush_l2(hj_handle* h) {
+  if (!h) return HJ_EINVAL;
+  CK(cudaSetDevice(h->device));
+  const u64 elems = (256ull << 20) / 8;  // 256 MiB > 126 MB L2
+  int rc;
+  if ((rc = ensure(h, h->flush, elems))) return rc;
+  fill_zero_kernel<<<h->sm_count * 8, 256, 0, h->stream>>>(reinterpret_cast<ulonglong2*>(h->flush.p), elems / 2);
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(h->stream));
+  return HJ_OK;
+}
+int hj_sync(hj_handle* h) {
+  if (!h) return HJ_EINVAL;
+  CK(cudaSetDevice(h->device));
+  CK(cudaStreamSynchronize(h->stream));
+  CK(cudaStreamSynchronize(h->copy_stream));
+  return HJ_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,412 @@
+// rx_kernels.cuh -- radix join: histogram, scan, scatter, per-partition join.
+//
+// Replaces mc/src/parallel_radix_join.c: parallel_radix_partition (:559-627,
+// histogram :586-589, prefix :592-617, scatter :622-626), its software
+// write-combining variant (:701-795), serial_radix_partition/radix_cluster
+// (:516-549, :402-440) for pass 2, and the per-partition joins
+// bucket_chaining_join (:231-283) / histogram_join (:306-369).
+//
+// B200 shape of the same steps:
+//   rx_hist     ONE read of the relation builds the histogram over ALL radix
+//               bits of all passes (shared-memory privatised, merged with
+//               global atomics) -- the reference re-reads per pass.
+//   rx_scan     one CTA: exclusive offsets of every final partition; the
+//               pass-1 partitions are every F2-th entry of the same array.
+//   rx_scatter  a CTA stages a tile of tuples in shared memory, ranks them by
+//               digit there, claims one global range per (tile, digit) with a
+//               single atomicAdd and writes each digit's run contiguously:
+//               the write-combining buffer is the digit-sorted tile, flushed
+//               as runs of T/F tuples (full 128 B lines at the default fan-out).
+//   rx_join     one CTA per final partition: open-addressing table of R_p in
+//               shared memory, S_p streamed through it; R partitions larger
+//               than the table are processed in chunks.
+#pragma once
+#include "hj_common.cuh"
+
+namespace hj {
+
+// How a key maps to a bin.
+//   mode 0: (key >> shift) & (2^bits - 1)                    one radix pass
+//   mode 1: p1-major index over two passes: ((key & (F1-1)) << b2) | ((key >> b1) & (F2-1))
+//           (pass 1 = low b1 bits, pass 2 = next b2 bits: prj_params.h:76-78,
+//            parallel_radix_join.c:870-871,960-961)
+//   mode 2: range split for the G-way exchange: min(G-1, ((key-1)*G) >> domain_bits)
+struct Digit {
+  u32 mode, shift, bits, b1, b2, ndest, domain_bits, pad;
+  u64 key_mask;
+};
+__device__ __forceinline__ u32 digit_of(const Digit& d, u64 v) {
+  const u64 key = v & d.key_mask;
+  if (d.mode == 0) return (u32)((key >> d.shift) & ((1u << d.bits) - 1u));
+  if (d.mode == 1) return (u32)(((key & ((1u << d.b1) - 1u)) << d.b2) | ((key >> d.b1) & ((1u << d.b2) - 1u)));
+  u64 q = ((key - 1) * (u64)d.ndest) >> d.domain_bits;
+  return (u32)(q < d.ndest ? q : d.ndest - 1);
+}
+
+// ---- histogram ---------------------------------------------------------------
+constexpr int kHistThreads = 512;
+constexpr int kHistIPT = 8;
+
+// nbins*4 bytes of dynamic shared memory when SMEM, else straight global atomics
+template <bool SMEM>
+__global__ void __launch_bounds__(kHistThreads)
+rx_hist_kernel(const u64* __restrict__ in, u64 n, Digit dg, u32 nbins, u64* __restrict__ ghist) {
+  extern __shared__ u32 shist[];
+  const u32 tid = threadIdx.x;
+  if (SMEM) {
+    for (u32 i = tid; i < nbins; i += kHistThreads) shist[i] = 0;
+    __syncthreads();
+  }
+  constexpr int TILE = kHistThreads * kHistIPT;
+  const u64 ntiles = (n + TILE - 1) / TILE;
+  for (u64 t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    const u64 base = t * TILE;
+    u64 v[kHistIPT];
+#pragma unroll
+    for (int j = 0; j < kHistIPT / 2; j++) {
+      const u64 i = base + 2ull * (j * kHistThreads + tid);
+      if (i + 1 < n) {
+        ulonglong2 x = ld_stream_v2(in + i);
+        v[2 * j] = x.x;
+        v[2 * j + 1] = x.y;
+      } else {
+        v[2 * j] = i < n ? ld_stream(in + i) : 0ull;
+        v[2 * j + 1] = 0ull;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < kHistIPT; j++) {
+      const bool valid = v[j] != 0ull;
+      const u32 d = valid ? digit_of(dg, v[j]) : 0xffffffffu;
+      // sorted input on high bits puts a whole warp in one bin: add once
+      const u32 d0 = __shfl_sync(0xffffffffu, d, 0);
+      if (__all_sync(0xffffffffu, d == d0)) {
+        if (lane_id() == 0 && valid) {
+          if (SMEM) atomicAdd(shist + d, 32u);
+          else atomicAdd(ghist + d, 32ull);
+        }
+      } else if (valid) {
+        if (SMEM) atomicAdd(shist + d, 1u);
+        else atomicAdd(ghist + d, 1ull);
+      }
+    }
+  }
+  if (SMEM) {
+    __syncthreads();
+    for (u32 i = tid; i < nbins; i += kHistThreads) {
+      const u32 c = shist[i];
+      if (c) atomicAdd(ghist + i, (u64)c);
+    }
+  }
+}
+
+// ---- scan ----------------------------------------------------------------------
+// One CTA.  offsets[0..nbins] = exclusive prefix of ghist; cursors[i] = offsets[i]
+// (claimed by the final scatter pass).  When f2 > 1 also emits the pass-1 view:
+// parent_off[p1] = offsets[p1*f2] (nparent = nbins/f2 entries + 1),
+// parent_cursor[p1] = parent_off[p1], and for both passes the tile prefix
+// tiles[p] = number of scatter tiles of `tile` tuples before parent p.
+// one[0..3] = the single-parent view {0, n} / {0, ceil(n/tile)} used by pass 1.
+constexpr int kScanThreads = 1024;
+__global__ void __launch_bounds__(kScanThreads)
+rx_scan_kernel(const u64* __restrict__ ghist, u32 nbins, u64* __restrict__ offsets, u64* __restrict__ cursors,
+               u32 f2, u64* __restrict__ parent_off, u64* __restrict__ parent_cursor, u64* __restrict__ parent_tiles,
+               u64* __restrict__ one, u32 tile, u64* __restrict__ max_bin) {
+  __shared__ u64 wsum[kScanThreads / 32];
+  __shared__ u64 carry_s;
+  const u32 tid = threadIdx.x;
+  if (tid == 0) carry_s = 0;
+  __syncthreads();
+  u64 mx = 0;
+  for (u32 base = 0; base < nbins; base += kScanThreads) {
+    const u32 i = base + tid;
+    const u64 x = i < nbins ? ghist[i] : 0ull;
+    mx = x > mx ? x : mx;
+    u64 incl = x;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const u64 y = __shfl_up_sync(0xffffffffu, incl, o);
+      if ((int)lane_id() >= o) incl += y;
+    }
+    if (lane_id() == 31) wsum[tid >> 5] = incl;
+    __syncthreads();
+    if (tid < 32) {
+      u64 w = wsum[tid];
+      u64 wi = w;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const u64 y = __shfl_up_sync(0xffffffffu, wi, o);
+        if ((int)tid >= o) wi += y;
+      }
+      wsum[tid] = wi - w;  // exclusive warp offsets
+    }
+    __syncthreads();
+    const u64 carry = carry_s;
+    const u64 excl = carry + wsum[tid >> 5] + incl - x;
+    if (i < nbins) {
+      offsets[i] = excl;
+      cursors[i] = excl;
+    }
+    __syncthreads();
+    if (tid == kScanThreads - 1) carry_s = excl + x;
+    __syncthreads();
+  }
+  if (tid == 0) {
+    offsets[nbins] = carry_s;
+    if (one) {  // one-parent view of the whole relation: offsets {0, n}, tiles {0, ceil(n/tile)}
+      one[0] = 0; one[1] = carry_s; one[2] = 0; one[3] = (carry_s + tile - 1) / tile;
+    }
+  }
+  if (max_bin) {
+    mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, 16));
+    mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
+    mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, 4));
+    mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+    mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+    if (lane_id() == 0) atomicMax(max_bin, mx);
+  }
+  __syncthreads();
+  // parent (pass-1) view and tile prefixes; nparent <= 4096, serial per thread chunk is fine
+  if (parent_off) {
+    const u32 nparent = nbins / f2;
+    for (u32 p = tid; p <= nparent; p += kScanThreads) {
+      const u64 o = offsets[p * f2];  // p == nparent reads offsets[nbins]
+      parent_off[p] = o;
+      if (p < nparent) parent_cursor[p] = o;
+    }
+    __syncthreads();
+    if (tid == 0) {
+      u64 t = 0;
+      for (u32 p = 0; p < nparent; p++) {
+        parent_tiles[p] = t;
+        t += (parent_off[p + 1] - parent_off[p] + tile - 1) / tile;
+      }
+      parent_tiles[nparent] = t;
+    }
+  }
+}
+
+// ---- scatter ---------------------------------------------------------------------
+// A launch re-partitions every "parent" range [parent_off[p], parent_off[p+1]) of
+// `in` by the digit `dg` into `out`, claiming space from cursors[p*F + digit].
+// Pass 1 / single pass: one parent covering the whole relation.
+// Dynamic shared memory: tile (TILE*8) | gdelta (F*8) | hist (F*4) | lbase (F*4).
+constexpr int kScThreads = 512;
+
+template <int IPT>
+__global__ void __launch_bounds__(kScThreads)
+rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u32 F, u32 nparent,
+                  const u64* __restrict__ parent_off, const u64* __restrict__ parent_tiles,
+                  u64* __restrict__ cursors) {
+  constexpr int TILE = kScThreads * IPT;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  u64* tile = reinterpret_cast<u64*>(smem_raw);
+  u64* gdelta = tile + TILE;
+  u32* hist = reinterpret_cast<u32*>(gdelta + F);
+  u32* lbase = hist + F;
+  __shared__ u32 warp_tot[kScThreads / 32];
+
+  const u32 tid = threadIdx.x;
+  const u64 total_tiles = parent_tiles[nparent];
+  const u32 per_thread = (F + kScThreads - 1) / kScThreads;  // bins each thread scans
+
+  for (u64 t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+    // which parent does tile t belong to: last p with parent_tiles[p] <= t
+    u32 lo = 0, hi = nparent;
+    while (hi - lo > 1) {
+      const u32 mid = (lo + hi) >> 1;
+      if (parent_tiles[mid] <= t) lo = mid; else hi = mid;
+    }
+    const u32 p = lo;
+    const u64 begin = parent_off[p] + (t - parent_tiles[p]) * TILE;
+    u64 end = begin + TILE;
+    const u64 pend = parent_off[p + 1];
+    if (end > pend) end = pend;
+    const u32 cnt = (u32)(end - begin);
+
+    for (u32 i = tid; i < F; i += kScThreads) hist[i] = 0;
+    __syncthreads();
+
+    u64 v[IPT];
+    u32 rank[IPT];
+    const bool aligned = ((begin & 1ull) == 0);
+#pragma unroll
+    for (int j = 0; j < IPT / 2; j++) {
+      const u64 i = begin + 2ull * (j * kScThreads + tid);
+      if (aligned && i + 1 < end) {
+        ulonglong2 x = ld_stream_v2(in + i);
+        v[2 * j] = x.x;
+        v[2 * j + 1] = x.y;
+      } else {
+        v[2 * j] = i < end ? ld_stream(in + i) : 0ull;
+        v[2 * j + 1] = i + 1 < end ? ld_stream(in + i + 1) : 0ull;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < IPT; j++)
+      if (v[j]) rank[j] = atomicAdd(hist + digit_of(dg, v[j]), 1u);
+    __syncthreads();
+
+    // exclusive scan of hist -> lbase; one global claim per non-empty digit
+    {
+      const u32 b0 = tid * per_thread;
+      u32 local = 0;
+      for (u32 k = 0; k < per_thread; k++) {
+        const u32 b = b0 + k;
+        if (b < F) local += hist[b];
+      }
+      u32 incl = local;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const u32 y = __shfl_up_sync(0xffffffffu, incl, o);
+        if ((int)lane_id() >= o) incl += y;
+      }
+      if (lane_id() == 31) warp_tot[tid >> 5] = incl;
+      __syncthreads();
+      if (tid < 32) {
+        const u32 w = tid < kScThreads / 32 ? warp_tot[tid] : 0u;
+        u32 wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const u32 y = __shfl_up_sync(0xffffffffu, wi, o);
+          if ((int)tid >= o) wi += y;
+        }
+        if (tid < kScThreads / 32) warp_tot[tid] = wi - w;
+      }
+      __syncthreads();
+      u32 run = warp_tot[tid >> 5] + incl - local;
+      for (u32 k = 0; k < per_thread; k++) {
+        const u32 b = b0 + k;
+        if (b < F) {
+          const u32 c = hist[b];
+          lbase[b] = run;
+          if (c) gdelta[b] = atomicAdd(cursors + (u64)p * F + b, (u64)c) - run;
+          run += c;
+        }
+      }
+    }
+    __syncthreads();
+
+#pragma unroll
+    for (int j = 0; j < IPT; j++)
+      if (v[j]) tile[lbase[digit_of(dg, v[j])] + rank[j]] = v[j];
+    __syncthreads();
+
+    // flush: element i of the digit-sorted tile goes to gdelta[digit] + i
+    for (u32 i = tid; i < cnt; i += kScThreads) {
+      const u64 x = tile[i];
+      out[gdelta[digit_of(dg, x)] + i] = x;
+    }
+    __syncthreads();
+  }
+}
+
+// ---- per-partition join --------------------------------------------------------
+// Dynamic shared memory: slots * 8 bytes (slots = power of two).  R_p is inserted
+// in chunks of slots/2 tuples so the load factor never exceeds 0.5; S_p is
+// streamed once per chunk.  Hash = bits above the radix bits, as the reference
+// (idx = (key & MASK) >> NUM_RADIX_BITS, parallel_radix_join.c:252,339).
+// With S == nullptr this is the build-only PRO of the reference and the result
+// is its "Results" checksum: sum of idx with N = NEXT_POW_2(|R_p|) (:239-257).
+constexpr int kJoinThreads = 512;
+
+__global__ void __launch_bounds__(kJoinThreads)
+rx_join_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const u64* __restrict__ Sp,
+               const u64* __restrict__ offS, u32 nparts, u32 radix_bits, u32 slots, u64 key_mask,
+               u64* __restrict__ ctr) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  u64* tab = reinterpret_cast<u64*>(smem_raw);
+  const u32 tid = threadIdx.x;
+  const u32 smask = slots - 1;
+  const u32 chunk_cap = slots / 2;
+  u64 matches = 0, checksum = 0, maxpart = 0, chunked = 0;
+
+  for (u32 p = blockIdx.x; p < nparts; p += gridDim.x) {
+    const u64 r0 = offR[p], r1 = offR[p + 1];
+    const u64 nr = r1 - r0;
+    maxpart = nr > maxpart ? nr : maxpart;
+    if (Sp == nullptr) {
+      // build-only: reference checksum (bucket_chaining_join)
+      u32 N = 1;
+      while (N < nr) N <<= 1;
+      const u32 msk = (N - 1) << radix_bits;
+      for (u64 i = r0 + tid; i < r1; i += kJoinThreads) checksum += ((u32)Rp[i] & msk) >> radix_bits;
+      continue;
+    }
+    const u64 s0 = offS[p], s1 = offS[p + 1];
+    if (nr == 0 || s1 == s0) continue;
+    if (nr > chunk_cap) chunked++;
+    for (u64 c0 = r0; c0 < r1; c0 += chunk_cap) {
+      const u64 c1 = c0 + chunk_cap < r1 ? c0 + chunk_cap : r1;
+      __syncthreads();  // previous probe finished before the table is cleared
+      for (u32 i = tid; i < slots; i += kJoinThreads) tab[i] = 0ull;
+      __syncthreads();
+      for (u64 i = c0 + tid; i < c1; i += kJoinThreads) {
+        const u64 v = ld_stream(Rp + i);
+        u32 slot = (u32)((v & key_mask) >> radix_bits) & smask;
+        while (atomicCAS(tab + slot, 0ull, v) != 0ull) slot = (slot + 1) & smask;
+      }
+      __syncthreads();
+      for (u64 i = s0 + tid; i < s1; i += kJoinThreads) {
+        const u64 s = ld_stream(Sp + i);
+        const u64 key = s & key_mask;
+        u32 slot = (u32)(key >> radix_bits) & smask;
+        u64 cnt = 0, sumr = 0;
+        while (true) {
+          const u64 cur = tab[slot];
+          if (cur == 0ull) break;
+          if ((cur & key_mask) == key) { ++cnt; sumr += cur; }
+          slot = (slot + 1) & smask;
+        }
+        matches += cnt;
+        checksum += sumr + cnt * s;
+      }
+    }
+  }
+  u64 v[2] = {matches, checksum};
+  u64* const d[2] = {ctr + C_MATCHES, ctr + C_CHECKSUM};
+  block_sum_atomic<2, kJoinThreads>(v, d);
+  // bookkeeping: largest partition, partitions that needed chunking
+  maxpart = max(maxpart, __shfl_xor_sync(0xffffffffu, maxpart, 16));
+  maxpart = max(maxpart, __shfl_xor_sync(0xffffffffu, maxpart, 8));
+  maxpart = max(maxpart, __shfl_xor_sync(0xffffffffu, maxpart, 4));
+  maxpart = max(maxpart, __shfl_xor_sync(0xffffffffu, maxpart, 2));
+  maxpart = max(maxpart, __shfl_xor_sync(0xffffffffu, maxpart, 1));
+  if (tid == 0) {
+    atomicMax(ctr + C_MAX_PART, maxpart);
+    if (chunked) atomicAdd(ctr + C_TOO_BIG, chunked);
+  }
+}
+
+// ---- counter-based generators (hj_generate; CPU restatement in oracle/) ---------
+// 4-round Feistel-style bijection on [0, 2^k): x -> perm(x).  For odd k the two
+// halves differ by one bit; cycle-walking is avoided by using an unbalanced
+// network whose round function folds into the narrower half.
+__host__ __device__ __forceinline__ u64 mix64(u64 x) {
+  x ^= x >> 33; x *= 0xff51afd7ed558ccdull;
+  x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ull;
+  x ^= x >> 33;
+  return x;
+}
+__host__ __device__ __forceinline__ u64 feistel_perm(u64 x, u32 k, u64 seed) {
+  const u32 hb = k / 2, lb = k - hb;  // high half hb bits, low half lb bits (lb >= hb)
+  u64 l = x & ((1ull << lb) - 1), h = x >> lb;
+  if (k < 2) return x;
+#pragma unroll
+  for (u32 r = 0; r < 4; r++) {
+    // alternate which half is rewritten; each step is invertible (xor with a function of the other half)
+    h ^= mix64(l + seed + r * 0x9E3779B97F4A7C15ull) & ((1ull << hb) - 1);
+    l ^= mix64(h + (seed ^ 0xD1B54A32D192ED03ull) + r * 0xBF58476D1CE4E5B9ull) & ((1ull << lb) - 1);
+  }
+  return (h << lb) | l;
+}
+__global__ void __launch_bounds__(256) gen_kernel(int kind, u64 first, u64 count, u32 kbits, u64 seed,
+                                                   u64* __restrict__ out) {
+  const u64 dmask = (1ull << kbits) - 1;
+  for (u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (u64)gridDim.x * blockDim.x) {
+    const u64 g = first + i;
+    out[i] = kind == 0 ? g + 1 : feistel_perm(g & dmask, kbits, seed + (g >> kbits)) + 1;
+  }
+}
+
+}  // namespace hj

@@ -1,0 +1,176 @@
+/*
+ * hj_b200.h -- C ABI of the B200-native (sm_100a) build/probe hash-join path.
+ *
+ * This is the drop-in boundary for HTM-HashJoin's L2 "join operator" layer:
+ * the bodies of AtomicHashBuild / NoCCHashBuild / HTMHashBuild (main binary)
+ * and PRO (mc/ radix join) are replaced by calls through these entry points.
+ * Plain C: pointers and sizes only, no CUDA / torch / C++ types.  Paths cited
+ * below are relative to the reference repository root.
+ *
+ * Tuple format: one 8-byte word per tuple,
+ *   low 32 bits = key, high 32 bits = payload
+ * which is bit-compatible with the reference's bare uint64_t values
+ * (include/DataGen.hpp:26-122, values <= 2^28) and with mc's
+ * struct {int32 key; int32 payload;} (mc/src/types.h:31-37).  0 is the empty
+ * slot sentinel, so keys must be non-zero (DataGen.hpp:41,58,83 guarantee it).
+ *
+ * There is no CPU fallback behind this ABI: every entry point that computes
+ * needs a CUDA device and returns HJ_ECUDA when none is usable.
+ */
+#ifndef HJ_B200_H
+#define HJ_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HJ_ABI_VERSION 1
+
+/* ---- status codes (reference: none; it perror()+exit()s, HTMHashBuild.hpp:66-70) */
+enum {
+  HJ_OK = 0,
+  HJ_EINVAL = -1,    /* bad argument / bad config                        */
+  HJ_ENOMEM = -2,    /* device or host allocation failed                 */
+  HJ_ECUDA = -3,     /* CUDA runtime error (see hj_last_error)           */
+  HJ_EOVERFLOW = -4, /* a partition does not fit the planned buffers     */
+  HJ_ESTATE = -5     /* call order violated (probe before build, ...)    */
+};
+
+/* ---- which path (reference: --algo, main.cpp:99-122) */
+enum {
+  HJ_ALGO_ATOMIC = 0,  /* global table, CAS inserts   (AtomicHashBuild.hpp:37-67)   */
+  HJ_ALGO_NOCC = 1,    /* global table, plain stores  (NoCCHashBuild.hpp:37-62)     */
+  HJ_ALGO_RADIX = 2,   /* radix join                  (mc/src/parallel_radix_join.c)*/
+  HJ_ALGO_ADAPTIVE = 3 /* sample, then global or radix (HTMHashBuild.hpp:100-156)   */
+};
+
+/* path_taken values in hj_result */
+enum { HJ_PATH_NONE = 0, HJ_PATH_GLOBAL = 1, HJ_PATH_RADIX = 2 };
+
+/* Everything that is a command-line flag (main.cpp:47-62) or a compile-time
+ * macro (config.h:4-16, mc/src/prj_params.h:15-22) in the reference. */
+typedef struct hj_config {
+  uint32_t struct_size;      /* = sizeof(hj_config), ABI check                          */
+  int32_t algo;              /* HJ_ALGO_*                                               */
+  int32_t device;            /* CUDA device ordinal                                     */
+  uint32_t probe_length;     /* --probeLength, default 4 (main.cpp:81)                  */
+  uint32_t scale_output;     /* --scaleOutput, default 2; table = pow2(scale*|R|)       */
+  uint32_t num_partitions;   /* --numPartitions: CPU work split for atomic/nocc
+                                (ignored on the GPU); radix FAN-OUT for radix/adaptive
+                                (power of two, 0 = choose so a partition fits smem)     */
+  uint32_t passes;           /* radix passes 1|2 (NUM_PASSES, prj_params.h:20), 0=auto  */
+  uint32_t transaction_size; /* --transactionSize: tuples a thread inserts per batch
+                                (HTM's tSize -> CAS batch / loads in flight), 0 = 2     */
+  uint32_t enable_probe;     /* ENABLE_PROBE (config.h:4)                               */
+  uint32_t sample_rounds;    /* K of HTMHashBuild.hpp:48-52 (K*16384 tuples / slice)    */
+  uint64_t key_mask;         /* key = tuple & key_mask; 0 = all 64 bits (main binary),
+                                0xffffffff for mc tuples                                */
+  double adaptive_threshold; /* contention above this -> radix path; <=0 = default     */
+  uint64_t reserved[4];
+} hj_config;
+
+/* Per-call outcome.  The first block mirrors the JSON the reference prints
+ * (AtomicHashBuild.hpp:133-152, HTMHashBuild.hpp:417-449). */
+typedef struct hj_result {
+  uint64_t matches;        /* true equi-join cardinality sum_k cntR(k)*cntS(k)           */
+  uint64_t checksum;       /* sum over matching pairs of (r + s) mod 2^64               */
+  uint64_t window_matches; /* matches inside the probe window only = the reference's
+                              "totalMatches" (AtomicHashBuild.hpp:75-83,126-131)        */
+  uint64_t input_sum;      /* "inputSum"  (AtomicHashBuild.hpp:90-98)                   */
+  uint64_t table_sum;      /* sum of table slots (:100-107)                             */
+  uint64_t overflow_sum;   /* sum of tuples that left the window (:109-119, fixed idx)  */
+  uint64_t conflicts;      /* "conflicts": tuples whose probe budget ran out (:62-63)   */
+  uint64_t cas_retries;    /* lost CAS races (the HTM-abort stand-in)                   */
+  uint64_t probe_steps;    /* slots skipped because occupied, build side                */
+  uint64_t sampled;        /* tuples in the sampling round (0 if none)                  */
+  uint64_t sectors;        /* distinct 32 B table sectors touched per warp, summed      */
+  double contention;       /* adaptive signal, see DESIGN.md                            */
+  int32_t path_taken;      /* HJ_PATH_*                                                 */
+  uint32_t radix_bits;     /* log2 fan-out actually used                                */
+  uint32_t passes;         /* passes actually used                                      */
+  uint32_t kernel_launches;/* kernels launched by this call                             */
+  /* device time of each phase, microseconds, CUDA events on the handle's stream */
+  float us_total, us_h2d, us_clear, us_sample, us_build, us_probe;
+  float us_hist, us_scan, us_scatter1, us_scatter2, us_join;
+  float us_reserved[5];
+  uint64_t hbm_bytes;      /* algorithmic HBM bytes of the path taken       */
+  uint64_t max_partition;  /* largest R partition seen by the radix join                */
+  uint64_t reserved[6];
+} hj_result;
+
+typedef struct hj_handle hj_handle;
+
+/* ---- lifetime -------------------------------------------------------------- */
+void hj_config_default(hj_config *cfg);  /* main.cpp:78-85 defaults */
+int hj_create(const hj_config *cfg, hj_handle **out);
+void hj_destroy(hj_handle *h);
+int hj_abi_version(void);
+int hj_device_count(void);
+const char *hj_strerror(int code);
+const char *hj_last_error(const hj_handle *h); /* last CUDA error text */
+
+/* Pre-size every device buffer for |R| <= max_r, |S| <= max_s so that no
+ * allocation happens inside a timed call (the reference allocates before its
+ * timer too, AtomicHashBuild.hpp:25-34). */
+int hj_reserve(hj_handle *h, uint64_t max_r, uint64_t max_s);
+
+/* ---- the hot path ------------------------------------------------------------
+ * R / S may be host pointers (pageable or pinned; staged H2D inside the call)
+ * or device pointers on cfg.device (used in place); detected per pointer. */
+
+/* AtomicHashBuild.hpp:37-67 / NoCCHashBuild.hpp:37-62: (re)build the global
+ * table from R.  res may be NULL. */
+int hj_build(hj_handle *h, const uint64_t *R, uint64_t n, hj_result *res);
+/* AtomicHashBuild.hpp:69-85: probe the table built last with S. */
+int hj_probe(hj_handle *h, const uint64_t *S, uint64_t m, hj_result *res);
+/* Whole join, path chosen by cfg.algo; S == NULL / m == 0 means build only
+ * (ENABLE_PROBE=0).  For HJ_ALGO_RADIX this is PRO (parallel_radix_join.c:1305)
+ * with the probe of histogram_join (:306-369) restored. */
+int hj_join(hj_handle *h, const uint64_t *R, uint64_t n, const uint64_t *S,
+            uint64_t m, hj_result *res);
+/* HTMHashBuild.hpp:100-156 sampling round: insert K*16384 tuples of each of
+ * the 64 slices of R into the (cleared) global table, measure contention.
+ * The sampled prefix stays in the table, as in the reference (:170). */
+int hj_sample(hj_handle *h, const uint64_t *R, uint64_t n, hj_result *res);
+/* Verification sums (untimed in the reference, AtomicHashBuild.hpp:90-119):
+ * fills input_sum (over R, may be NULL), table_sum, overflow_sum. */
+int hj_checksums(hj_handle *h, const uint64_t *R, uint64_t n, hj_result *res);
+
+/* ---- radix building blocks (exposed for the multi-GPU exchange and tests) ----
+ * One partitioning pass over bits [shift, shift+bits) of the key:
+ * parallel_radix_join.c:559-627 (histogram -> prefix -> scatter).  in/out/
+ * offsets are DEVICE pointers; offsets receives 2^bits+1 exclusive offsets
+ * (u64).  Order inside a partition is unspecified. */
+int hj_radix_partition(hj_handle *h, const uint64_t *in, uint64_t n,
+                       uint32_t shift, uint32_t bits, uint64_t *out,
+                       uint64_t *offsets);
+/* Destination histogram for the G-way exchange: dest = ((key-1) * G) >> domain_bits
+ * clamp G-1.  counts: G u64 on the device. */
+int hj_exchange_partition(hj_handle *h, const uint64_t *in, uint64_t n,
+                          uint32_t n_dest, uint32_t domain_bits, uint64_t *out,
+                          uint64_t *offsets);
+
+/* ---- device-side input synthesis (sizes beyond uint32_t/rand()) --
+ * Counter-based generators with a bit-identical CPU restatement in oracle/:
+ *   kind 0: out[i] = first + i + 1                       (sorted slice)
+ *   kind 1: out[i] = perm_{seed}((first + i) mod domain) + 1, perm = 4-round
+ *           Feistel-style bijection on [0, domain), domain = 2^k  (PK / FK slice)
+ * out is a device pointer. */
+int hj_generate(hj_handle *h, int kind, uint64_t first, uint64_t count,
+                uint64_t domain, uint64_t seed, uint64_t *out);
+
+/* ---- memory helpers so a C host needs no CUDA headers ------------------------ */
+int hj_device_alloc(hj_handle *h, uint64_t bytes, void **out);
+int hj_device_free(hj_handle *h, void *p);
+int hj_host_alloc(uint64_t bytes, void **out); /* pinned */
+int hj_host_free(void *p);
+int hj_copy(hj_handle *h, void *dst, const void *src, uint64_t bytes); /* any direction, synchronous */
+int hj_flush_l2(hj_handle *h); /* writes a >L2 scratch buffer (bench hygiene) */
+int hj_sync(hj_handle *h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HJ_B200_H */
