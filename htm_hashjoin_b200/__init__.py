@@ -1,0 +1,259 @@
+"""htm_hashjoin_b200 -- B200-native build/probe hash-join hot path.
+
+Python is only the test/bench harness over the C ABI (include/hj_b200.h,
+csrc/libhj_b200.so).  The functions below mirror the reference's interface for
+this path with the same names and argument meaning:
+
+  generate_data          include/DataGen.hpp:26
+  AtomicHashBuild        AtomicHashBuild.hpp:14-20
+  NoCCHashBuild          NoCCHashBuild.hpp:13-19
+  HTMHashBuild           HTMHashBuild.hpp:54-60  (adaptive path on the GPU)
+  PRO                    mc/src/parallel_radix_join.h:33-34
+
+Each *HashBuild returns the dict of the JSON line the reference prints
+(AtomicHashBuild.hpp:133-152) plus the extra keys.  Importing this package
+fails loudly when the CUDA library has not been built; nothing here computes
+a join on the CPU.
+"""
+import ctypes as C
+import json
+
+import numpy as np
+
+from . import _capi
+from ._capi import (HJ_ALGO_ADAPTIVE, HJ_ALGO_ATOMIC, HJ_ALGO_NOCC, HJ_ALGO_RADIX, HJ_OK, HJ_PATH_GLOBAL,
+                    HJ_PATH_RADIX, hj_config, hj_result)
+
+lib = _capi.load()  # raises ImportError if libhj_b200.so is missing
+
+ALGOS = {"atomic": HJ_ALGO_ATOMIC, "nocc": HJ_ALGO_NOCC, "radix": HJ_ALGO_RADIX,
+         "adaptive": HJ_ALGO_ADAPTIVE, "htm": HJ_ALGO_ADAPTIVE}
+
+
+class HJError(RuntimeError):
+    def __init__(self, code, where, detail=""):
+        self.code = code
+        msg = lib.hj_strerror(code).decode()
+        super().__init__(f"{where}: {msg} [{code}] {detail}")
+
+
+def _ptr(x):
+    """(address, element count) of a host numpy array, a torch tensor, or a raw int pointer."""
+    if x is None:
+        return None, 0
+    if isinstance(x, tuple):  # (raw device pointer, count)
+        return int(x[0]), int(x[1])
+    if isinstance(x, np.ndarray):
+        if x.dtype != np.uint64 or not x.flags["C_CONTIGUOUS"]:
+            raise TypeError("host relations must be C-contiguous uint64 arrays")
+        return x.ctypes.data, x.size
+    if hasattr(x, "data_ptr"):  # torch tensor (int64/uint64, cpu or cuda)
+        if x.element_size() != 8 or not x.is_contiguous():
+            raise TypeError("tensors must be contiguous with 8-byte elements")
+        return x.data_ptr(), x.numel()
+    raise TypeError(f"unsupported relation type {type(x)}")
+
+
+# ---- inputs (csrc/datagen.cpp) ------------------------------------------------
+def generate_data(dist, size, distinct_keys=None, local_shuffle_range=16):
+    """include/DataGen.hpp:26 -- same libc calls, bit-identical arrays."""
+    out = np.empty(int(size), dtype=np.uint64)
+    rc = lib.hj_generate_data(dist.encode(), int(size), int(distinct_keys if distinct_keys is not None else size),
+                              int(local_shuffle_range), out.ctypes.data)
+    if rc != 0:
+        raise ValueError("Unknown distribution")  # DataGen.hpp:117-120
+    return out
+
+
+def mc_relation_pk(n, seed=12345):
+    out = np.empty(int(n), dtype=np.uint64)
+    lib.hj_mc_relation_pk(out.ctypes.data, int(n), int(seed))
+    return out
+
+
+def mc_relation_fk(m, maxid, seed=54321):
+    out = np.empty(int(m), dtype=np.uint64)
+    lib.hj_mc_relation_fk(out.ctypes.data, int(m), int(maxid), int(seed))
+    return out
+
+
+# ---- handle --------------------------------------------------------------------
+class HashJoin:
+    """One hj_handle: owns the device buffers of one GPU."""
+
+    def __init__(self, algo="atomic", device=0, probe_length=4, scale_output=2, num_partitions=0, passes=0,
+                 transaction_size=16, enable_probe=True, sample_rounds=5, key_mask=0, adaptive_threshold=0.0):
+        cfg = hj_config()
+        lib.hj_config_default(C.byref(cfg))
+        cfg.algo = ALGOS[algo] if isinstance(algo, str) else int(algo)
+        cfg.device = device
+        cfg.probe_length = probe_length
+        cfg.scale_output = scale_output
+        cfg.num_partitions = num_partitions
+        cfg.passes = passes
+        cfg.transaction_size = transaction_size
+        cfg.enable_probe = 1 if enable_probe else 0
+        cfg.sample_rounds = sample_rounds
+        cfg.key_mask = key_mask if key_mask else 0xFFFFFFFFFFFFFFFF
+        cfg.adaptive_threshold = adaptive_threshold
+        self.cfg = cfg
+        self._h = C.c_void_p()
+        rc = lib.hj_create(C.byref(cfg), C.byref(self._h))
+        if rc != HJ_OK:
+            self._h = None
+            raise HJError(rc, "hj_create", "(no usable CUDA device; there is no CPU fallback)")
+
+    def _check(self, rc, where):
+        if rc != HJ_OK:
+            raise HJError(rc, where, lib.hj_last_error(self._h).decode())
+
+    def close(self):
+        if self._h:
+            lib.hj_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def reserve(self, max_r, max_s=0):
+        self._check(lib.hj_reserve(self._h, int(max_r), int(max_s)), "hj_reserve")
+
+    def build(self, R):
+        p, n = _ptr(R)
+        res = hj_result()
+        self._check(lib.hj_build(self._h, p, n, C.byref(res)), "hj_build")
+        return res
+
+    def probe(self, S):
+        p, m = _ptr(S)
+        res = hj_result()
+        self._check(lib.hj_probe(self._h, p, m, C.byref(res)), "hj_probe")
+        return res
+
+    def join(self, R, S=None):
+        pr, n = _ptr(R)
+        ps, m = _ptr(S)
+        res = hj_result()
+        self._check(lib.hj_join(self._h, pr, n, ps, m, C.byref(res)), "hj_join")
+        return res
+
+    def sample(self, R):
+        p, n = _ptr(R)
+        res = hj_result()
+        self._check(lib.hj_sample(self._h, p, n, C.byref(res)), "hj_sample")
+        return res
+
+    def checksums(self, R=None):
+        p, n = _ptr(R)
+        res = hj_result()
+        self._check(lib.hj_checksums(self._h, p, n, C.byref(res)), "hj_checksums")
+        return res
+
+    def radix_partition(self, d_in, n, shift, bits, d_out, d_offsets):
+        self._check(lib.hj_radix_partition(self._h, int(d_in), int(n), shift, bits, int(d_out), int(d_offsets)),
+                    "hj_radix_partition")
+
+    def exchange_partition(self, d_in, n, n_dest, domain_bits, d_out, d_offsets):
+        self._check(lib.hj_exchange_partition(self._h, int(d_in), int(n), n_dest, domain_bits, int(d_out),
+                                              int(d_offsets)), "hj_exchange_partition")
+
+    def generate(self, kind, first, count, domain, seed, d_out):
+        self._check(lib.hj_generate(self._h, kind, int(first), int(count), int(domain), int(seed), int(d_out)),
+                    "hj_generate")
+
+    def device_alloc(self, nbytes):
+        p = C.c_void_p()
+        self._check(lib.hj_device_alloc(self._h, int(nbytes), C.byref(p)), "hj_device_alloc")
+        return p.value
+
+    def device_free(self, p):
+        self._check(lib.hj_device_free(self._h, p), "hj_device_free")
+
+    def copy(self, dst, src, nbytes):
+        self._check(lib.hj_copy(self._h, int(dst), int(src), int(nbytes)), "hj_copy")
+
+    def to_device(self, arr):
+        """Copy a host uint64 array to a fresh device buffer; returns (ptr, count)."""
+        p = self.device_alloc(max(arr.nbytes, 8))
+        if arr.size:
+            self.copy(p, arr.ctypes.data, arr.nbytes)
+        return (p, arr.size)
+
+    def to_host(self, dptr, count):
+        out = np.empty(int(count), dtype=np.uint64)
+        if count:
+            self.copy(out.ctypes.data, dptr, out.nbytes)
+        return out
+
+    def flush_l2(self):
+        self._check(lib.hj_flush_l2(self._h), "hj_flush_l2")
+
+    def sync(self):
+        self._check(lib.hj_sync(self._h), "hj_sync")
+
+
+def pinned_empty(n):
+    """uint64 numpy array over pinned host memory (hj_host_alloc)."""
+    p = C.c_void_p()
+    rc = lib.hj_host_alloc(int(n) * 8, C.byref(p))
+    if rc != HJ_OK:
+        raise HJError(rc, "hj_host_alloc")
+    buf = (C.c_uint64 * int(n)).from_address(p.value)
+    arr = np.frombuffer(buf, dtype=np.uint64)
+    _PINNED[arr.ctypes.data] = p.value
+    return arr
+
+
+_PINNED = {}
+
+
+def pinned_free(arr):
+    p = _PINNED.pop(arr.ctypes.data, None)
+    if p is not None:
+        lib.hj_host_free(p)
+
+
+# ---- the reference's entry points ----------------------------------------------
+def _ref_run(algo, relR, rSize, relS, sSize, transactionSize, scaleOutput, numPartitions, probeLength, passes=0):
+    pr, n = _ptr(relR)
+    ps, m = _ptr(relS)
+    if rSize is not None:
+        n = int(rSize)
+    if relS is not None and sSize is not None:
+        m = int(sSize)
+    buf = C.create_string_buffer(4096)
+    rc = lib.hj_ref_run(algo.encode(), pr, n, ps, m, int(transactionSize), int(scaleOutput), int(numPartitions),
+                        int(probeLength), int(passes), buf, 4096)
+    line = buf.value.decode()
+    out = json.loads(line)
+    if rc != HJ_OK:
+        raise HJError(rc, "hj_ref_run", out.get("error", ""))
+    out["_json"] = line
+    return out
+
+
+def AtomicHashBuild(relR, rSize=None, relS=None, sSize=None, scaleOutput=2, numPartitions=64, probeLength=4):
+    return _ref_run("atomic", relR, rSize, relS, sSize, 0, scaleOutput, numPartitions, probeLength)
+
+
+def NoCCHashBuild(relR, rSize=None, relS=None, sSize=None, scaleOutput=2, numPartitions=64, probeLength=4):
+    return _ref_run("nocc", relR, rSize, relS, sSize, 0, scaleOutput, numPartitions, probeLength)
+
+
+def HTMHashBuild(relR, rSize=None, relS=None, sSize=None, transactionSize=16, scaleOutput=2, numPartitions=64,
+                 probeLength=4):
+    return _ref_run("htm", relR, rSize, relS, sSize, transactionSize, scaleOutput, numPartitions, probeLength)
+
+
+def PRO(relR, relS=None, nthreads=1, radix_bits=14, passes=2):
+    """mc PRO: returns the join cardinality, or with relS=None the reference's
+    build-only "Results" checksum (parallel_radix_join.c:231-283)."""
+    with HashJoin("radix", num_partitions=1 << radix_bits, passes=passes, key_mask=0xFFFFFFFF,
+                  enable_probe=relS is not None) as hj:
+        res = hj.join(relR, relS)
+        return int(res.matches if relS is not None else res.checksum)

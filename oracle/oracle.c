@@ -380,3 +380,38 @@ uint64_t orc_htm_build_serial(const uint64_t *R, uint64_t n, uint64_t *table_sum
   if (conflict_sum) *conflict_sum = cs;
   return conflicts;
 }
+
+/* ------------------------------------------------------------------------ */
+/* counter-based generator for sizes beyond the reference's uint32_t/rand()  */
+/* (SURVEY.md 8d, config C5).  The reference has no generator of this kind;  */
+/* this is the CPU statement the device generator (hj_generate) is checked   */
+/* against: kind 0 = sorted slice, kind 1 = 4-round Feistel-style bijection  */
+/* of [0, 2^k) per block of `domain` indices (one independent permutation    */
+/* per block, like the iterations of mc/src/generator.c:424-430).            */
+/* ------------------------------------------------------------------------ */
+static uint64_t mix64(uint64_t x) {
+  x ^= x >> 33; x *= 0xff51afd7ed558ccdull;
+  x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ull;
+  x ^= x >> 33;
+  return x;
+}
+static uint64_t feistel_perm(uint64_t x, uint32_t k, uint64_t seed) {
+  uint32_t hb = k / 2, lb = k - hb;
+  uint64_t l = x & ((1ull << lb) - 1), h = x >> lb;
+  if (k < 2) return x;
+  for (uint32_t r = 0; r < 4; r++) {
+    h ^= mix64(l + seed + r * 0x9E3779B97F4A7C15ull) & ((1ull << hb) - 1);
+    l ^= mix64(h + (seed ^ 0xD1B54A32D192ED03ull) + r * 0xBF58476D1CE4E5B9ull) & ((1ull << lb) - 1);
+  }
+  return (h << lb) | l;
+}
+void orc_feistel_gen(int kind, uint64_t first, uint64_t count, uint64_t domain,
+                     uint64_t seed, uint64_t *out) {
+  uint32_t k = 0;
+  while ((1ull << k) < domain) k++;
+  uint64_t dmask = (1ull << k) - 1;
+  for (uint64_t i = 0; i < count; i++) {
+    uint64_t g = first + i;
+    out[i] = kind == 0 ? g + 1 : feistel_perm(g & dmask, k, seed + (g >> k)) + 1;
+  }
+}

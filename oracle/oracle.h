@@ -101,6 +101,10 @@ uint64_t orc_radix_join(const uint64_t *R, uint64_t n, const uint64_t *S,
 uint64_t orc_htm_build_serial(const uint64_t *R, uint64_t n,
                               uint64_t *table_sum, uint64_t *conflict_sum);
 
+/* ---- counter-based generator (no reference counterpart; see oracle.c) ----- */
+void orc_feistel_gen(int kind, uint64_t first, uint64_t count, uint64_t domain,
+                     uint64_t seed, uint64_t *out);
+
 /* ---- helpers -------------------------------------------------------------- */
 uint64_t orc_sum(const uint64_t *a, uint64_t n);
 /* possum = sum (i+1)*a[i] mod 2^64: order-sensitive fingerprint */

@@ -1,0 +1,176 @@
+"""CPU tests: the oracle against the reference's golden vectors / KATs,
+against the reference itself compiled into oracle/_ref, and the host-side mirror
+(csrc/datagen.cpp) against both.  No GPU needed."""
+import json
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from tests import oracle_lib
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "kats.json")
+
+
+@pytest.fixture(scope="module")
+def kats():
+    with open(GOLDEN) as f:
+        return json.load(f)
+
+
+# ---- generator KATs (probed from the reference's DataGen.hpp with glibc rand) ----
+@pytest.mark.parametrize("name", ["sorted_2^20", "shuffle_2^20", "local_shuffle_2^20_w16", "local_shuffle_2^20_w4096",
+                                  "uniform_2^20"])
+def test_generator_kats(oracle, hj, kats, name):
+    k = kats["generators"][name]
+    for gen in (oracle.generate_data, hj.generate_data):
+        a = gen(k["dist"], k["n"], k["n"], k["range"])
+        assert oracle.possum(a) == k["possum"]
+        if "sum" in k:
+            assert oracle.sum(a) == k["sum"]
+        if "first8" in k:
+            assert a[:8].tolist() == k["first8"]
+
+
+def test_generator_matches_reference_binary(oracle, hj):
+    ref = oracle_lib.Reference(probe=True)
+    if not ref.available:
+        pytest.skip("oracle/_ref not built (no /root/reference)")
+    for dist, rng in (("uniform", 16), ("shuffle", 16), ("local_shuffle", 64), ("sorted", 16), ("random", 16)):
+        n = 1 << 16
+        want = ref.generate_data(dist, n, n, rng)
+        assert np.array_equal(oracle.generate_data(dist, n, n, rng), want), dist
+        assert np.array_equal(hj.generate_data(dist, n, n, rng), want), dist
+
+
+def test_unknown_distribution(oracle, hj):
+    with pytest.raises(ValueError):
+        oracle.generate_data("zipf", 16)
+    with pytest.raises(ValueError):
+        hj.generate_data("zipf", 16)
+
+
+def test_mc_generators_host_vs_oracle(oracle, hj):
+    assert np.array_equal(hj.mc_relation_pk(5000, 12345), oracle.mc_pk(5000, 12345))
+    fk_h, fk_o = hj.mc_relation_fk(23000, 5000, 54321), oracle.mc_fk(23000, 5000, 54321)
+    assert np.array_equal(fk_h, fk_o)
+    # 4 full permutations of 1..5000 and one of 1..3000
+    for i in range(4):
+        assert np.array_equal(np.sort(fk_o[i * 5000:(i + 1) * 5000]), np.arange(1, 5001, dtype=np.uint64))
+    assert np.array_equal(np.sort(fk_o[20000:]), np.arange(1, 3001, dtype=np.uint64))
+
+
+# ---- closed forms pinned by the reference's logs (scaled down) --------------------
+@pytest.mark.parametrize("n", [1 << 10, 1 << 16])
+def test_global_table_unique_keys_closed_form(oracle, n):
+    R = oracle.generate_data("shuffle", n)
+    S = oracle.generate_data("sorted", n)
+    r = oracle.gt_serial(R, S)
+    assert r["input_sum"] == n * (n + 1) // 2
+    assert r["conflicts"] == 0 and r["total_matches"] == n
+    assert r["table_sum"] + r["overflow_sum"] == r["input_sum"]
+    # NoCC prints inputSum - n (NoCCHashBuild.hpp:94 sums half the table), as every nocc log line shows
+    assert oracle.gt_serial(R, S, nocc=True)["ref_output_sum"] == r["input_sum"] - n
+    assert oracle.true_join(R, S) == (n, 2 * r["input_sum"])
+
+
+def test_logged_golden_values_are_the_closed_forms(kats):
+    g = kats["reference_logs_2^27"]
+    n = 1 << 27
+    assert g["inputSum"] == n * (n + 1) // 2
+    assert g["totalMatches"] == n
+    assert g["nocc_outputSum"] == g["inputSum"] - n
+    assert g["PRO_Results_b14"] == (n // 2) * (n // (1 << 14) - 1)
+
+
+def test_serial_reference_numbers_uniform(oracle, kats):
+    k = kats["ref_serial_uniform_2^20"]
+    R = oracle.generate_data("uniform", 1 << 20)
+    S = oracle.generate_data("sorted", 1 << 20)
+    r = oracle.gt_serial(R, S)
+    assert r["conflicts"] == k["conflicts"]
+    assert r["total_matches"] == k["totalMatches"]
+    assert r["table_sum"] + r["overflow_sum"] == r["input_sum"]
+    assert oracle.true_join(R, S)[0] == 1 << 20
+
+
+def test_oracle_vs_reference_library(oracle):
+    """The reference's own AtomicHashBuild/NoCCHashBuild, run with one partition so its
+    schedule is the serial one the oracle restates."""
+    ref = oracle_lib.Reference(probe=True)
+    if not ref.available:
+        pytest.skip("oracle/_ref not built")
+    n = 1 << 16
+    S = oracle.generate_data("sorted", n)
+    for dist in ("uniform", "shuffle", "local_shuffle"):
+        R = oracle.generate_data(dist, n)
+        o = oracle.gt_serial(R, S)
+        j = ref.hash_build("atomic", R.copy(), S.copy(), num_partitions=1)
+        assert j["conflicts"] == o["conflicts"], dist
+        assert j["totalMatches"] == o["total_matches"], dist
+        assert j["inputSum"] == o["input_sum"], dist
+        assert j["outputSum"] == o["ref_output_sum"], dist
+
+
+@pytest.mark.parametrize("bits", [7, 10, 14])
+def test_pro_checksum_closed_form(oracle, bits):
+    n = 1 << 20
+    R = oracle.mc_pk(n)
+    want = (n // 2) * (n // (1 << bits) - 1)
+    assert oracle.pro_checksum(R, bits) == want
+    if bits == 14:
+        assert want == 33030144
+
+
+def test_pro_checksum_vs_reference_binary(oracle):
+    exe = oracle_lib.mc_binary(10, 1)
+    if not exe:
+        pytest.skip("oracle/_ref mc binaries not built")
+    n = 1 << 20
+    out = subprocess.run([exe, "--algo=PRO", "--nthreads=2", f"--r-size={n}", "--s-size=2"], capture_output=True,
+                         text=True, timeout=120).stdout
+    got = [l for l in out.splitlines() if "Results" in l][0]
+    val = int(got.split("=")[1].split(".")[0])
+    assert val == oracle.pro_checksum(oracle.mc_pk(n), 10)
+
+
+def test_radix_join_equals_true_join(oracle):
+    n, m = 1 << 14, 5 << 14
+    R = oracle.mc_pk(n)
+    S = oracle.mc_fk(m, n)
+    want = oracle.true_join(R, S, 0xFFFFFFFF)
+    assert want[0] == m
+    for bits, passes in ((4, 1), (8, 2), (9, 2)):
+        assert oracle.radix_join(R, S, bits, passes) == want
+    Ru = oracle.generate_data("uniform", n)
+    Ss = oracle.generate_data("sorted", n)
+    assert oracle.radix_join(Ru, Ss, 6, 2) == oracle.true_join(Ru, Ss)
+
+
+def test_radix_partition_properties(oracle):
+    a = oracle.generate_data("shuffle", 1 << 12)
+    out, off = oracle.radix_partition(a, 3, 5)
+    assert off[0] == 0 and off[-1] == a.size
+    for p in range(32):
+        seg = out[off[p]:off[p + 1]]
+        assert np.all(((seg >> np.uint64(3)) & np.uint64(31)) == p)
+    assert np.array_equal(np.sort(out), np.sort(a))
+
+
+def test_feistel_generator_is_a_permutation(oracle):
+    for k in (1, 2, 7, 10, 13):
+        d = 1 << k
+        a = oracle.feistel_gen(1, 0, d, d, 42)
+        assert np.array_equal(np.sort(a), np.arange(1, d + 1, dtype=np.uint64)), k
+    # consecutive blocks are different permutations; slices agree with the whole
+    a = oracle.feistel_gen(1, 0, 3 << 10, 1 << 10, 7)
+    assert not np.array_equal(a[:1024], a[1024:2048])
+    assert np.array_equal(oracle.feistel_gen(1, 1500, 700, 1 << 10, 7), a[1500:2200])
+    assert np.array_equal(oracle.feistel_gen(0, 10, 5, 0, 0), np.arange(11, 16, dtype=np.uint64))
+
+
+def test_htm_serial_no_conflicts_on_dense_keys(oracle):
+    R = oracle.generate_data("shuffle", 1 << 14)
+    conflicts, ts, cs = oracle.htm_serial(R)
+    assert conflicts == 0 and cs == 0 and ts == oracle.sum(R)
