@@ -1,0 +1,92 @@
+"""CPU tests of the drop-in boundary: the C-ABI library loads, exports every symbol
+include/hj_b200.h declares, rejects bad arguments, and fails LOUDLY (HJ_ECUDA, no
+fallback) when there is no CUDA device.  No compute calls here."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_header_symbols_all_exported(hj):
+    hdr = open(os.path.join(ROOT, "include", "hj_b200.h")).read()
+    declared = set(re.findall(r"\b(hj_[a-z0-9_]+)\s*\(", hdr))
+    declared -= {"hj_config", "hj_result", "hj_handle"}
+    assert declared == set(hj._capi.ABI_SYMBOLS), declared ^ set(hj._capi.ABI_SYMBOLS)
+    for name in hj._capi.ABI_SYMBOLS + hj._capi.HOST_SYMBOLS:
+        assert hasattr(hj.lib, name), name
+
+
+def test_struct_sizes_match_abi(hj):
+    cfg = hj.hj_config()
+    hj.lib.hj_config_default(C.byref(cfg))
+    assert cfg.struct_size == C.sizeof(hj.hj_config)
+    # main.cpp:78-85 defaults
+    assert (cfg.probe_length, cfg.scale_output, cfg.transaction_size) == (4, 2, 16)
+    assert cfg.key_mask == 0xFFFFFFFFFFFFFFFF
+    assert hj.lib.hj_abi_version() == 1
+    assert C.sizeof(hj.hj_result) % 8 == 0
+
+
+def test_bad_config_rejected(hj):
+    cfg = hj.hj_config()
+    hj.lib.hj_config_default(C.byref(cfg))
+    h = C.c_void_p()
+    cfg.struct_size = 12
+    assert hj.lib.hj_create(C.byref(cfg), C.byref(h)) == hj._capi.HJ_EINVAL
+    hj.lib.hj_config_default(C.byref(cfg))
+    cfg.algo = 17
+    assert hj.lib.hj_create(C.byref(cfg), C.byref(h)) == hj._capi.HJ_EINVAL
+    hj.lib.hj_config_default(C.byref(cfg))
+    cfg.probe_length = 0
+    assert hj.lib.hj_create(C.byref(cfg), C.byref(h)) == hj._capi.HJ_EINVAL
+    assert hj.lib.hj_create(None, C.byref(h)) == hj._capi.HJ_EINVAL
+    assert b"invalid" in hj.lib.hj_strerror(hj._capi.HJ_EINVAL)
+
+
+def test_no_device_fails_loudly_no_fallback(hj):
+    """Without a GPU the product must refuse, not compute on the CPU."""
+    if hj.lib.hj_device_count() > 0:
+        pytest.skip("a CUDA device is present")
+    with pytest.raises(hj.HJError) as e:
+        hj.HashJoin("atomic")
+    assert e.value.code == hj._capi.HJ_ECUDA
+    R = hj.generate_data("sorted", 1024)
+    with pytest.raises(hj.HJError):
+        hj.AtomicHashBuild(R, 1024)
+
+
+def test_missing_library_is_an_import_error(hj, tmp_path, monkeypatch):
+    monkeypatch.setattr(hj._capi, "LIB_PATH", str(tmp_path / "nope.so"))
+    with pytest.raises(ImportError):
+        hj._capi.load()
+
+
+def test_product_never_touches_the_oracle():
+    """The oracle is test infrastructure: nothing under the package or include/ may name it."""
+    bad = []
+    for base in ("htm_hashjoin_b200", "include"):
+        for dp, _, files in os.walk(os.path.join(ROOT, base)):
+            for f in files:
+                if f.endswith((".py", ".cu", ".cuh", ".cpp", ".hpp", ".h", "Makefile")):
+                    txt = open(os.path.join(dp, f), errors="ignore").read()
+                    if re.search(r"liboracle|oracle_lib|orc_[a-z_]+\(|oracle/_ref|oracle\.h", txt):
+                        bad.append(os.path.join(dp, f))
+    assert not bad, bad
+
+
+def test_cli_flag_behaviour():
+    """main.cpp:63-66 (unknown flag -> exit 1), :107-108 (unknown algo -> message, exit 0)."""
+    exe = os.path.join(ROOT, "htm_hashjoin_b200", "csrc", "main")
+    if not os.path.exists(exe):
+        pytest.skip("CLI not built")
+    r = subprocess.run([exe, "--bogus", "1"], capture_output=True, text=True)
+    assert r.returncode == 1 and "Unknown option" in r.stdout
+    r = subprocess.run([exe, "--algo", "foo"], capture_output=True, text=True)
+    assert r.returncode == 0 and "Unknown Algo: foo" in r.stdout
+    r = subprocess.run([exe, "--algo", "atomic", "--rSize", "1K", "--dataDistr", "zipf"], capture_output=True,
+                       text=True)
+    assert r.returncode == 1 and "Unknown distribution" in r.stdout

@@ -1,0 +1,243 @@
+"""GPU parity tests: the CUDA path through the C ABI vs the oracle (bit-exact: match
+count + order-independent 64-bit checksum), vs the golden KATs, and size-independent
+properties at larger sizes."""
+import json
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+DISTS = [("sorted", 16), ("shuffle", 16), ("local_shuffle", 16), ("local_shuffle", 4096), ("uniform", 16),
+         ("random", 16)]
+
+
+def _inputs(hj, dist, rng, n):
+    R = hj.generate_data(dist, n, n, rng)
+    S = R.copy() if dist == "random" else hj.generate_data("sorted", n, n, 16)  # main.cpp:92-97
+    return R, S
+
+
+@pytest.mark.parametrize("dist,rng", DISTS)
+@pytest.mark.parametrize("algo", ["atomic", "radix", "adaptive"])
+def test_join_matches_oracle(hj, oracle, algo, dist, rng):
+    n = 1 << 18
+    R, S = _inputs(hj, dist, rng, n)
+    want = oracle.true_join(R, S)
+    with hj.HashJoin(algo) as h:
+        res = h.join(R, S)
+        assert (res.matches, res.checksum) == want
+        assert res.kernel_launches > 0
+        if res.path_taken == hj.HJ_PATH_GLOBAL:
+            sums = h.checksums(R)
+            assert sums.input_sum == oracle.sum(R)
+            assert sums.table_sum + sums.overflow_sum == sums.input_sum  # no tuple lost
+            if dist in ("sorted", "shuffle", "local_shuffle"):
+                assert res.conflicts == 0 and res.window_matches == n   # pinned by the logs
+
+
+@pytest.mark.parametrize("tsize", [1, 2, 4, 16])
+def test_transaction_size_variants(hj, oracle, tsize):
+    n = (1 << 17) + 13  # odd size: tails of the vector loads
+    R = hj.generate_data("uniform", n, 1 << 17, 16)
+    S = hj.generate_data("sorted", 1 << 17)
+    want = oracle.true_join(R, S)
+    with hj.HashJoin("atomic", transaction_size=tsize) as h:
+        res = h.join(R, S)
+        assert (res.matches, res.checksum) == want
+
+
+def test_nocc_unique_keys(hj, oracle):
+    n = 1 << 18
+    R, S = _inputs(hj, "shuffle", 16, n)
+    with hj.HashJoin("nocc") as h:
+        res = h.join(R, S)
+        assert (res.matches, res.checksum) == oracle.true_join(R, S)
+        sums = h.checksums(R)
+        assert sums.table_sum == sums.input_sum == n * (n + 1) // 2
+
+
+def test_serial_reference_numbers_bracket_gpu_conflicts(hj, oracle):
+    """conflicts/totalMatches on duplicate keys are schedule dependent: not
+    bit-pinned, but window matches + what the overflow table adds must be the true join,
+    and the GPU's conflict count must be of the order of the serial one."""
+    n = 1 << 20
+    R, S = _inputs(hj, "uniform", 16, n)
+    serial = oracle.gt_serial(R, S)
+    with hj.HashJoin("atomic") as h:
+        res = h.join(R, S)
+        assert res.matches == n
+        assert res.window_matches <= res.matches
+        assert 0.5 * serial["conflicts"] < res.conflicts < 2.0 * serial["conflicts"]
+        assert res.window_matches >= n - res.conflicts
+
+
+def test_device_resident_inputs_and_split_calls(hj, oracle):
+    n = 1 << 18
+    R, S = _inputs(hj, "uniform", 16, n)
+    want = oracle.true_join(R, S)
+    with hj.HashJoin("atomic") as h:
+        dR, dS = h.to_device(R), h.to_device(S)
+        b = h.build(dR)
+        p = h.probe(dS)
+        assert (p.matches, p.checksum) == want
+        assert b.us_h2d == 0.0
+        # probing twice gives the same answer (idempotent), and an empty probe is fine
+        p2 = h.probe(dS)
+        assert (p2.matches, p2.checksum) == want
+        h.device_free(dR[0]); h.device_free(dS[0])
+    with hj.HashJoin("atomic") as h:
+        with pytest.raises(hj.HJError) as e:
+            h.probe(S)
+        assert e.value.code == hj._capi.HJ_ESTATE
+
+
+@pytest.mark.parametrize("bits,passes", [(4, 1), (7, 1), (10, 1), (12, 1), (8, 2), (11, 2), (14, 2), (15, 2)])
+def test_radix_fanout_sweep_fk(hj, oracle, bits, passes):
+    n, m = 1 << 17, (5 << 17) + 77
+    R = hj.mc_relation_pk(n)
+    S = hj.mc_relation_fk(m, n)
+    want = oracle.true_join(R, S, 0xFFFFFFFF)
+    assert want[0] == m
+    with hj.HashJoin("radix", num_partitions=1 << bits, passes=passes, key_mask=0xFFFFFFFF) as h:
+        res = h.join(R, S)
+        assert (res.matches, res.checksum) == want
+        assert (res.radix_bits, res.passes) == (bits, passes)
+
+
+def test_radix_payloads_and_duplicates(hj, oracle):
+    """mc tuples: key in the low 32 bits, payload (row id) in the high 32."""
+    rng = np.random.default_rng(5)
+    n, m = 100003, 400007
+    keys_r = rng.integers(1, 30000, n, dtype=np.uint64)
+    keys_s = rng.integers(1, 40000, m, dtype=np.uint64)
+    R = keys_r | (np.arange(n, dtype=np.uint64) << np.uint64(32))
+    S = keys_s | (np.arange(m, dtype=np.uint64) << np.uint64(32))
+    want = oracle.true_join(R, S, 0xFFFFFFFF)
+    for algo, kw in (("radix", dict(num_partitions=1 << 6, passes=2)), ("radix", dict(num_partitions=1 << 9, passes=1)),
+                     ("atomic", {})):
+        with hj.HashJoin(algo, key_mask=0xFFFFFFFF, **kw) as h:
+            res = h.join(R, S)
+            assert (res.matches, res.checksum) == want, algo
+
+
+def test_radix_oversized_partitions_chunked(hj, oracle):
+    """Fan-out too small for shared memory: R partitions are joined in chunks."""
+    n = 1 << 18
+    R, S = _inputs(hj, "shuffle", 16, n)
+    with hj.HashJoin("radix", num_partitions=2, passes=1) as h:
+        res = h.join(R, S)
+        assert (res.matches, res.checksum) == oracle.true_join(R, S)
+        assert res.max_partition == n // 2
+
+
+def test_pro_build_only_checksum(hj, oracle):
+    """PRO as shipped by the reference: partition + build, Results = sum idx
+    (parallel_radix_join.c:231-283); closed form (n/2)(n/2^B - 1), SURVEY 8c."""
+    n = 1 << 20
+    R = hj.mc_relation_pk(n)
+    for bits, passes in ((14, 2), (10, 1), (7, 1)):
+        got = hj.PRO(R, None, radix_bits=bits, passes=passes)
+        assert got == (n // 2) * (n // (1 << bits) - 1) == oracle.pro_checksum(R, bits)
+    assert hj.PRO(R, None, radix_bits=14, passes=2) == 33030144
+
+
+def test_radix_partition_building_block(hj, oracle):
+    n = 300001
+    a = hj.generate_data("shuffle", n)
+    with hj.HashJoin("radix") as h:
+        d_in = h.to_device(a)
+        d_out = h.device_alloc(n * 8)
+        for shift, bits in ((0, 7), (3, 5), (5, 11)):
+            d_off = h.device_alloc(((1 << bits) + 1) * 8)
+            h.radix_partition(d_in[0], n, shift, bits, d_out, d_off)
+            out, off = h.to_host(d_out, n), h.to_host(d_off, (1 << bits) + 1)
+            want_out, want_off = oracle.radix_partition(a, shift, bits)
+            assert np.array_equal(off, want_off)
+            for p in range(1 << bits):  # order inside a partition is unspecified
+                assert np.array_equal(np.sort(out[off[p]:off[p + 1]]), np.sort(want_out[off[p]:off[p + 1]]))
+            h.device_free(d_off)
+
+
+def test_exchange_partition_ranges(hj):
+    n, G, dom = 1 << 18, 8, 18
+    a = hj.generate_data("shuffle", n)
+    with hj.HashJoin("radix") as h:
+        d_in = h.to_device(a)
+        d_out, d_off = h.device_alloc(n * 8), h.device_alloc((G + 1) * 8)
+        h.exchange_partition(d_in[0], n, G, dom, d_out, d_off)
+        out, off = h.to_host(d_out, n), h.to_host(d_off, G + 1)
+        assert off.tolist() == [g * (n // G) for g in range(G + 1)]
+        for g in range(G):
+            seg = out[off[g]:off[g + 1]]
+            assert seg.min() == g * (n // G) + 1 and seg.max() == (g + 1) * (n // G)
+
+
+def test_device_generator_matches_oracle(hj, oracle):
+    with hj.HashJoin("radix") as h:
+        d = h.device_alloc(5000 * 8)
+        for kind, first, count, domain, seed in ((0, 10, 5000, 0, 0), (1, 0, 4096, 4096, 9), (1, 3000, 5000, 2048, 3)):
+            h.generate(kind, first, count, max(domain, 1), seed, d)
+            assert np.array_equal(h.to_host(d, count), oracle.feistel_gen(kind, first, count, max(domain, 1), seed))
+
+
+def test_adaptive_switch_direction(hj):
+    """Sorted input stays on the global table; a fully shuffled one goes to radix."""
+    n = 1 << 24
+    S = hj.generate_data("sorted", n)
+    with hj.HashJoin("adaptive") as h:
+        r_sorted = h.join(S, S)
+        assert r_sorted.path_taken == hj.HJ_PATH_GLOBAL and r_sorted.matches == n
+        R = hj.generate_data("shuffle", n)
+        r_shuf = h.join(R, S)
+        assert r_shuf.matches == n and r_shuf.checksum == n * (n + 1)
+        assert r_shuf.contention > r_sorted.contention
+        assert r_shuf.sampled > 0
+
+
+def test_golden_2_24_and_full_size_properties(hj, oracle):
+    """BASELINE config 1 size: generator KAT, closed-form join result, and the
+    no-tuple-lost invariant; idempotence of the whole join."""
+    kats = json.load(open(os.path.join(ROOT, "tests", "golden", "kats.json")))
+    n = 1 << 24
+    R = hj.generate_data("uniform", n, n, 16)
+    assert oracle.sum(R) == kats["generators"]["uniform_2^24"]["sum"]
+    assert oracle.possum(R) == kats["generators"]["uniform_2^24"]["possum"]
+    S = hj.generate_data("sorted", n)
+    in_sum = oracle.sum(R)
+    # every R key is in [1, n] and S = 1..n: matches = n, checksum = sum(r) + sum(key of r) = 2*inputSum
+    for algo in ("atomic", "radix"):
+        with hj.HashJoin(algo) as h:
+            a = h.join(R, S)
+            b = h.join(R, S)
+            assert (a.matches, a.checksum) == (n, (2 * in_sum) % (1 << 64)) == (b.matches, b.checksum)
+            if algo == "atomic":
+                sums = h.checksums(R)
+                assert sums.input_sum == in_sum == sums.table_sum + sums.overflow_sum
+
+
+def test_reference_named_entry_points_and_cli(hj, oracle):
+    n = 1 << 20
+    R = hj.generate_data("shuffle", n)
+    S = hj.generate_data("sorted", n)
+    j = hj.AtomicHashBuild(R, n, S, n, 2, 64, 4)
+    keys = list(j.keys())
+    assert keys[:8] == ["algo", "rSize", "probeLength", "hashBuildTimeInMicroseconds", "conflicts", "totalMatches",
+                        "inputSum", "outputSum"]  # AtomicHashBuild.hpp:133-152 order
+    assert (j["conflicts"], j["totalMatches"], j["inputSum"], j["outputSum"]) == (0, n, n * (n + 1) // 2,
+                                                                                   n * (n + 1) // 2)
+    jb = hj.NoCCHashBuild(R, n)  # build-only form (ENABLE_PROBE=0)
+    assert "totalMatches" not in jb and jb["outputSum"] == jb["inputSum"]
+    jh = hj.HTMHashBuild(R, n, S, n, 16)
+    assert jh["algo"] == "htm" and jh["transactionSize"] == 16 and jh["matches"] == n
+    exe = os.path.join(ROOT, "htm_hashjoin_b200", "csrc", "main")
+    out = subprocess.run([exe, "--algo", "atomic", "--rSize", "1M", "--dataDistr", "uniform"], capture_output=True,
+                         text=True, timeout=300)
+    assert out.returncode == 0, out.stdout + out.stderr
+    line = json.loads(out.stdout.strip().splitlines()[-1])
+    Ru = hj.generate_data("uniform", n)
+    assert line["inputSum"] == oracle.sum(Ru) and line["matches"] == n
+    assert line["outputSum"] == line["inputSum"]
