@@ -188,3 +188,157 @@ def run_reference(args):
     }
     print(json.dumps(line))
     return 0
+
+
+# =============================================================================
+# B200 arm
+# =============================================================================
+def expected_result(G, log_r, log_s):
+    """FK S over PK R: every S tuple matches exactly one R tuple with r == s, so
+    matches = |S| and checksum = 2 * sum(S); S = |S|/D permutations of 1..D."""
+    D = G << log_r
+    m = G << log_s
+    blocks, rest = divmod(m, D)
+    assert rest == 0
+    return m, (2 * blocks * (D * (D + 1) // 2)) % (1 << 64)
+
+
+class Rank:
+    """One process = one GPU: inputs, exchange buffers and the hj handle."""
+
+    def __init__(self, args):
+        import torch
+        import htm_hashjoin_b200 as hj
+        self.torch, self.hj, self.args = torch, hj, args
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        torch.cuda.set_device(self.local)
+        self.dist = None
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
+            self.dist = dist
+        G = self.world
+        self.n, self.m = 1 << args.log_r, 1 << args.log_s
+        self.domain = G * self.n
+        self.h = hj.HashJoin(args.algo, device=self.local, num_partitions=(1 << args.radix_bits) if args.radix_bits else 0,
+                             passes=args.passes)
+        dev = torch.device("cuda", self.local)
+        self.dR = torch.empty(self.n, dtype=torch.int64, device=dev)
+        self.dS = torch.empty(self.m, dtype=torch.int64, device=dev)
+        t0 = time.time()
+        if G == 1 and args.r_dist != "feistel":
+            # R: the reference's own DataGen distribution (bit-identical, host generated)
+            self.hR = hj.pinned_empty(self.n)
+            self.hR[:] = hj.generate_data(args.r_dist, self.n, self.n, 16)
+            self.h.copy(self.dR.data_ptr(), self.hR.ctypes.data, self.n * 8)
+            self.r_desc = f"DataGen.hpp '{args.r_dist}' srand(0), host generated"
+        else:
+            self.h.generate(1, self.rank * self.n, self.n, self.domain, 12345, self.dR.data_ptr())
+            self.hR = None
+            self.r_desc = "counter-based PK permutation (hj_generate kind 1, seed 12345), slice per rank"
+        # S: FK relation = |S|/|R| independent permutations of 1..|R| (structure of
+        # mc/src/generator.c:409-445), generated on the device (rand() is too slow at 2^30)
+        self.h.generate(1, self.rank * self.m, self.m, self.domain, 54321, self.dS.data_ptr())
+        self.s_desc = "counter-based FK (hj_generate kind 1, seed 54321: |S|/|R| permutations of 1..|R|)"
+        self.hS = None
+        self.gen_s = time.time() - t0
+        if G > 1:
+            cap_r = self.n + self.n // 32 + 65536
+            cap_s = self.m + self.m // 32 + 65536
+            self.sendR = torch.empty(self.n, dtype=torch.int64, device=dev)
+            self.sendS = torch.empty(self.m, dtype=torch.int64, device=dev)
+            self.recvR = torch.empty(cap_r, dtype=torch.int64, device=dev)
+            self.recvS = torch.empty(cap_s, dtype=torch.int64, device=dev)
+            self.offR = torch.empty(G + 1, dtype=torch.int64, device=dev)
+            self.offS = torch.empty(G + 1, dtype=torch.int64, device=dev)
+        self.h.reserve(self.n + self.n // 16 + 65536, self.m + self.m // 16 + 65536)
+        self.last = None
+        self.launches = 0
+        self.nvlink_bytes = 0
+
+    def host_inputs(self):
+        """Pinned host copies of this rank's slices (for the e2e leg)."""
+        if self.hR is None:
+            self.hR = self.hj.pinned_empty(self.n)
+            self.h.copy(self.hR.ctypes.data, self.dR.data_ptr(), self.n * 8)
+        if self.hS is None:
+            self.hS = self.hj.pinned_empty(self.m)
+            self.h.copy(self.hS.ctypes.data, self.dS.data_ptr(), self.m * 8)
+
+    def step(self, host=False):
+        """One whole join.  host=True: inputs start in pinned host memory."""
+        torch, G = self.torch, self.world
+        if G == 1:
+            R = self.hR if host else self.dR
+            S = self.hS if host else self.dS
+            res = self.h.join(R, S)
+            self.launches += res.kernel_launches
+            self.last = res
+            return res.matches, res.checksum
+        if host:  # H2D of this rank's slices, then the same device pipeline
+            self.h.copy(self.dR.data_ptr(), self.hR.ctypes.data, self.n * 8)
+            self.h.copy(self.dS.data_ptr(), self.hS.ctypes.data, self.m * 8)
+        dom_bits = (self.domain - 1).bit_length()
+        # 1. split both slices by destination GPU (high key bits of the key domain)
+        self.h.exchange_partition(self.dR.data_ptr(), self.n, G, dom_bits, self.sendR.data_ptr(), self.offR.data_ptr())
+        self.h.exchange_partition(self.dS.data_ptr(), self.m, G, dom_bits, self.sendS.data_ptr(), self.offS.data_ptr())
+        self.launches += 6
+        offs = torch.stack([self.offR, self.offS]).cpu()
+        # 2. counts, then the tuples, all-to-all over NCCL (NVLink 5 / NVSwitch)
+        send_counts = (offs[:, 1:] - offs[:, :-1]).contiguous()  # [2, G]
+        recv_counts = torch.empty_like(send_counts)
+        sc, rc = send_counts.cuda(), recv_counts.cuda()
+        self.dist.all_to_all_single(rc[0], sc[0])
+        self.dist.all_to_all_single(rc[1], sc[1])
+        recv_counts = rc.cpu()
+        nr, ns = int(recv_counts[0].sum()), int(recv_counts[1].sum())
+        assert nr <= self.recvR.numel() and ns <= self.recvS.numel(), "exchange receive buffer too small"
+        self.dist.all_to_all_single(self.recvR[:nr], self.sendR, recv_counts[0].tolist(), send_counts[0].tolist())
+        self.dist.all_to_all_single(self.recvS[:ns], self.sendS, recv_counts[1].tolist(), send_counts[1].tolist())
+        torch.cuda.synchronize()
+        self.nvlink_bytes += 8 * (self.n - int(send_counts[0][self.rank]) + self.m - int(send_counts[1][self.rank]))
+        # 3. local join of the received partitions
+        res = self.h.join((self.recvR.data_ptr(), nr), (self.recvS.data_ptr(), ns))
+        self.launches += res.kernel_launches
+        self.last = res
+        # 4. {matches, checksum} summed over ranks (wrapping int64 add == u64 add)
+        out = torch.tensor([res.matches, res.checksum], dtype=torch.uint64).view(torch.int64).cuda()
+        self.dist.all_reduce(out)
+        out = out.cpu().view(torch.uint64)
+        return int(out[0]), int(out[1])
+
+    def barrier(self):
+        if self.dist:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def max_over_ranks(self, x):
+        if not self.dist:
+            return x
+        t = self.torch.tensor([x], dtype=self.torch.float64, device="cuda")
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t[0])
+
+    def timed(self, steps, host, want):
+        """K steps bracketed by barrier + synchronize, CUDA events, max over ranks (ms)."""
+        torch = self.torch
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        phases = {}
+        self.launches = 0
+        self.nvlink_bytes = 0
+        self.barrier()
+        e0.record()
+        for _ in range(steps):
+            got = self.step(host)
+            assert got == want, f"join result {got} != expected {want}"
+            r = self.last
+            for k in ("us_total", "us_hist", "us_scan", "us_scatter1", "us_scatter2", "us_join", "us_build",
+                      "us_probe", "us_clear", "us_h2d"):
+                phases[k] = phases.get(k, 0.0) + getattr(r, k)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = self.max_over_ranks(e0.elapsed_time(e1))
+        self.barrier()
+        return ms, {k: v / steps for k, v in phases.items()}
