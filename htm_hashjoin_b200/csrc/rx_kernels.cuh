@@ -304,11 +304,21 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
 // ---- per-partition join --------------------------------------------------------
 // Dynamic shared memory: slots * 8 bytes (slots = power of two).  R_p is inserted
 // in chunks of slots/2 tuples so the load factor never exceeds 0.5; S_p is
-// streamed once per chunk.  Hash = bits above the radix bits, as the reference
-// (idx = (key & MASK) >> NUM_RADIX_BITS, parallel_radix_join.c:252,339).
+// streamed once per chunk.  Hash = Fibonacci hash of the bits above the radix bits
+// (the reference uses those bits directly: idx = (key & MASK) >> NUM_RADIX_BITS,
+// parallel_radix_join.c:252,339).
 // With S == nullptr this is the build-only PRO of the reference and the result
 // is its "Results" checksum: sum of idx with N = NEXT_POW_2(|R_p|) (:239-257).
 constexpr int kJoinThreads = 512;
+
+// Fibonacci hashing of the key bits above the radix bits.  The reference indexes its
+// per-partition table with those bits directly (parallel_radix_join.c:252); with dense
+// keys that fills one contiguous run of slots, and a probe that must walk to the first
+// empty slot (to count duplicates) would walk the whole run.  The golden-ratio multiply
+// spreads consecutive keys evenly, so runs stay 1-2 slots long at load <= 0.5.
+__device__ __forceinline__ u32 join_slot(u64 hi_key, u32 hshift) {
+  return (u32)((hi_key * 0x9E3779B97F4A7C15ull) >> hshift);
+}
 
 __global__ void __launch_bounds__(kJoinThreads)
 rx_join_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const u64* __restrict__ Sp,
@@ -318,6 +328,7 @@ rx_join_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const u
   u64* tab = reinterpret_cast<u64*>(smem_raw);
   const u32 tid = threadIdx.x;
   const u32 smask = slots - 1;
+  const u32 hshift = 64 - (31 - __clz(slots));  // slots is a power of two
   const u32 chunk_cap = slots / 2;
   u64 matches = 0, checksum = 0, maxpart = 0, chunked = 0;
 
@@ -343,14 +354,14 @@ rx_join_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const u
       __syncthreads();
       for (u64 i = c0 + tid; i < c1; i += kJoinThreads) {
         const u64 v = ld_stream(Rp + i);
-        u32 slot = (u32)((v & key_mask) >> radix_bits) & smask;
+        u32 slot = join_slot((v & key_mask) >> radix_bits, hshift);
         while (atomicCAS(tab + slot, 0ull, v) != 0ull) slot = (slot + 1) & smask;
       }
       __syncthreads();
       for (u64 i = s0 + tid; i < s1; i += kJoinThreads) {
         const u64 s = ld_stream(Sp + i);
         const u64 key = s & key_mask;
-        u32 slot = (u32)(key >> radix_bits) & smask;
+        u32 slot = join_slot(key >> radix_bits, hshift);
         u64 cnt = 0, sumr = 0;
         while (true) {
           const u64 cur = tab[slot];
