@@ -415,6 +415,24 @@ int ensure_rel(hj_handle* h, RelBufs& rb, u64 n, const RadixPlan& pl) {
   return HJ_OK;
 }
 
+// Histogram launch: 512-thread CTAs, or 1024 when the privatised histogram (> 64 KiB)
+// leaves room for one CTA per SM only.
+int launch_hist(hj_handle* h, const u64* in, u64 n, const Digit& dg, u32 nbins, u64* ghist) {
+  const size_t smem = (size_t)nbins * 4;
+  const bool big = smem > 64 * 1024;
+  const int threads = big ? 1024 : 512;
+  const void* k = big ? (const void*)rx_hist_kernel<true, 1024> : (const void*)rx_hist_kernel<true, 512>;
+  CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int grid = grid_for(h, k, threads, smem);
+  u64 tiles = (n + (u64)threads * kHistIPT - 1) / ((u64)threads * kHistIPT);
+  if ((u64)grid > tiles) grid = (int)(tiles ? tiles : 1);
+  if (big) rx_hist_kernel<true, 1024><<<grid, 1024, smem, h->stream>>>(in, n, dg, nbins, ghist);
+  else rx_hist_kernel<true, 512><<<grid, 512, smem, h->stream>>>(in, n, dg, nbins, ghist);
+  h->launches++;
+  CK(cudaGetLastError());
+  return HJ_OK;
+}
+
 template <int IPT>
 int launch_scatter_t(hj_handle* h, const u64* in, u64* out, const Digit& dg, u32 F, u32 nparent, const u64* poff,
                      const u64* ptiles, u64* cursors, u64 max_tiles) {
@@ -444,15 +462,8 @@ int radix_partition_rel(hj_handle* h, const u64* in, u64 n, RelBufs& rb, const R
   if (evb >= 0) mark(h, evb);
   CK(cudaMemsetAsync(rb.ghist.p, 0, nb * sizeof(u64), h->stream));
   {
-    size_t smem = (size_t)nb * 4;
-    auto k = rx_hist_kernel<true>;
-    CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int grid = grid_for(h, (const void*)k, kHistThreads, smem);
-    u64 tiles = (n + kHistThreads * kHistIPT - 1) / (kHistThreads * kHistIPT);
-    if ((u64)grid > tiles) grid = (int)(tiles ? tiles : 1);
-    k<<<grid, kHistThreads, smem, h->stream>>>(in, n, full, nb, rb.ghist.p);
-    h->launches++;
-    CK(cudaGetLastError());
+    int rc0 = launch_hist(h, in, n, full, nb, rb.ghist.p);
+    if (rc0) return rc0;
   }
   if (evb >= 0) mark(h, evb + 1);
   // scan: final offsets, the pass-1 ("parent") view and the one-parent view {0,n}.
@@ -891,11 +902,7 @@ int hj_radix_partition(hj_handle* h, const uint64_t* in, uint64_t n, uint32_t sh
   dg.key_mask = h->cfg.key_mask; dg.mode = 0; dg.shift = shift; dg.bits = bits;
   const u32 tile = kScThreads * 8;
   CK(cudaMemsetAsync(rb.ghist.p, 0, F * sizeof(u64), h->stream));
-  size_t smem = (size_t)F * 4;
-  auto k = rx_hist_kernel<true>;
-  CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  int grid = grid_for(h, (const void*)k, kHistThreads, smem);
-  k<<<grid, kHistThreads, smem, h->stream>>>((const u64*)in, n, dg, F, rb.ghist.p);
+  if ((rc = launch_hist(h, (const u64*)in, n, dg, F, rb.ghist.p))) return rc;
   rx_scan_kernel<<<1, kScanThreads, 0, h->stream>>>(rb.ghist.p, F, (u64*)offsets, rb.cursors.p, F, rb.poff.p,
                                                     rb.pcur.p, rb.ptiles.p, rb.one.p, tile, nullptr);
   CK(cudaGetLastError());
@@ -925,11 +932,7 @@ int hj_exchange_partition(hj_handle* h, const uint64_t* in, uint64_t n, uint32_t
   dg.key_mask = h->cfg.key_mask; dg.mode = 2; dg.ndest = n_dest; dg.domain_bits = domain_bits;
   const u32 tile = kScThreads * 8;
   CK(cudaMemsetAsync(rb.ghist.p, 0, F * sizeof(u64), h->stream));
-  size_t smem = (size_t)F * 4;
-  auto k = rx_hist_kernel<true>;
-  CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  int grid = grid_for(h, (const void*)k, kHistThreads, smem);
-  k<<<grid, kHistThreads, smem, h->stream>>>((const u64*)in, n, dg, F, rb.ghist.p);
+  if ((rc = launch_hist(h, (const u64*)in, n, dg, F, rb.ghist.p))) return rc;
   rx_scan_kernel<<<1, kScanThreads, 0, h->stream>>>(rb.ghist.p, F, (u64*)offsets, rb.cursors.p, F, rb.poff.p,
                                                     rb.pcur.p, rb.ptiles.p, rb.one.p, tile, nullptr);
   CK(cudaGetLastError());

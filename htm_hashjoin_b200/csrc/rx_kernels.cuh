@@ -44,11 +44,10 @@ __device__ __forceinline__ u32 digit_of(const Digit& d, u64 v) {
 }
 
 // ---- histogram ---------------------------------------------------------------
-constexpr int kHistThreads = 512;
-constexpr int kHistIPT = 8;
+constexpr int kHistIPT = 8;  // threads per CTA: 512, or 1024 when the privatised histogram allows one CTA per SM only
 
 // nbins*4 bytes of dynamic shared memory when SMEM, else straight global atomics
-template <bool SMEM>
+template <bool SMEM, int kHistThreads>
 __global__ void __launch_bounds__(kHistThreads)
 rx_hist_kernel(const u64* __restrict__ in, u64 n, Digit dg, u32 nbins, u64* __restrict__ ghist) {
   extern __shared__ u32 shist[];
@@ -310,6 +309,7 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
 // With S == nullptr this is the build-only PRO of the reference and the result
 // is its "Results" checksum: sum of idx with N = NEXT_POW_2(|R_p|) (:239-257).
 constexpr int kJoinThreads = 512;
+constexpr int kJoinBatch = 8;  // loads in flight per thread
 
 // Fibonacci hashing of the key bits above the radix bits.  The reference indexes its
 // per-partition table with those bits directly (parallel_radix_join.c:252); with dense
@@ -320,7 +320,7 @@ __device__ __forceinline__ u32 join_slot(u64 hi_key, u32 hshift) {
   return (u32)((hi_key * 0x9E3779B97F4A7C15ull) >> hshift);
 }
 
-__global__ void __launch_bounds__(kJoinThreads)
+__global__ void __launch_bounds__(kJoinThreads, 2)
 rx_join_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const u64* __restrict__ Sp,
                const u64* __restrict__ offS, u32 nparts, u32 radix_bits, u32 slots, u64 key_mask,
                u64* __restrict__ ctr) {
@@ -352,25 +352,49 @@ rx_join_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const u
       __syncthreads();  // previous probe finished before the table is cleared
       for (u32 i = tid; i < slots; i += kJoinThreads) tab[i] = 0ull;
       __syncthreads();
-      for (u64 i = c0 + tid; i < c1; i += kJoinThreads) {
-        const u64 v = ld_stream(Rp + i);
-        u32 slot = join_slot((v & key_mask) >> radix_bits, hshift);
-        while (atomicCAS(tab + slot, 0ull, v) != 0ull) slot = (slot + 1) & smask;
+      // build: kJoinBatch loads in flight per thread, then the CAS inserts
+      for (u64 b = c0; b < c1; b += (u64)kJoinThreads * kJoinBatch) {
+        u64 rv[kJoinBatch];
+#pragma unroll
+        for (int j = 0; j < kJoinBatch; j++) {
+          const u64 i = b + (u64)j * kJoinThreads + tid;
+          rv[j] = i < c1 ? ld_stream(Rp + i) : 0ull;
+        }
+#pragma unroll
+        for (int j = 0; j < kJoinBatch; j++) {
+          if (rv[j] == 0ull) continue;
+          u32 slot = join_slot((rv[j] & key_mask) >> radix_bits, hshift);
+          while (atomicCAS(tab + slot, 0ull, rv[j]) != 0ull) slot = (slot + 1) & smask;
+        }
       }
       __syncthreads();
-      for (u64 i = s0 + tid; i < s1; i += kJoinThreads) {
-        const u64 s = ld_stream(Sp + i);
-        const u64 key = s & key_mask;
-        u32 slot = join_slot(key >> radix_bits, hshift);
-        u64 cnt = 0, sumr = 0;
-        while (true) {
-          const u64 cur = tab[slot];
-          if (cur == 0ull) break;
-          if ((cur & key_mask) == key) { ++cnt; sumr += cur; }
-          slot = (slot + 1) & smask;
+      // probe: a batch of S loads in flight, then the home slots of the batch, then the walks
+      for (u64 b = s0; b < s1; b += (u64)kJoinThreads * kJoinBatch) {
+        u64 sv[kJoinBatch], cur[kJoinBatch];
+        u32 sl[kJoinBatch];
+#pragma unroll
+        for (int j = 0; j < kJoinBatch; j++) {
+          const u64 i = b + (u64)j * kJoinThreads + tid;
+          sv[j] = i < s1 ? ld_stream(Sp + i) : 0ull;
         }
-        matches += cnt;
-        checksum += sumr + cnt * s;
+#pragma unroll
+        for (int j = 0; j < kJoinBatch; j++) {
+          sl[j] = join_slot((sv[j] & key_mask) >> radix_bits, hshift);
+          cur[j] = sv[j] ? tab[sl[j]] : 0ull;
+        }
+#pragma unroll
+        for (int j = 0; j < kJoinBatch; j++) {
+          const u64 key = sv[j] & key_mask;
+          u64 c = cur[j], cnt = 0, sumr = 0;
+          u32 slot = sl[j];
+          while (c != 0ull) {
+            if ((c & key_mask) == key) { ++cnt; sumr += c; }
+            slot = (slot + 1) & smask;
+            c = tab[slot];
+          }
+          matches += cnt;
+          checksum += sumr + cnt * sv[j];
+        }
       }
     }
   }
