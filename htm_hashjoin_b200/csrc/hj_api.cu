@@ -433,10 +433,10 @@ int launch_hist(hj_handle* h, const u64* in, u64 n, const Digit& dg, u32 nbins, 
   return HJ_OK;
 }
 
-template <int IPT>
-int launch_scatter_t(hj_handle* h, const u64* in, u64* out, const Digit& dg, u32 F, u32 nparent, const u64* poff,
-                     const u64* ptiles, u64* cursors, u64 max_tiles) {
-  auto k = rx_scatter_kernel<IPT>;
+template <int IPT, int MODE>
+int launch_scatter_tm(hj_handle* h, const u64* in, u64* out, const Digit& dg, u32 F, u32 nparent, const u64* poff,
+                      const u64* ptiles, u64* cursors, u64 max_tiles) {
+  auto k = rx_scatter_kernel<IPT, MODE>;
   size_t smem = (size_t)kScThreads * IPT * 8 + (size_t)F * 16;
   CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int grid = grid_for(h, (const void*)k, kScThreads, smem);
@@ -445,6 +445,15 @@ int launch_scatter_t(hj_handle* h, const u64* in, u64* out, const Digit& dg, u32
   h->launches++;
   CK(cudaGetLastError());
   return HJ_OK;
+}
+// mode-0 digits on bits below 32 take the specialised kernel; everything else the generic one
+template <int IPT>
+int launch_scatter_t(hj_handle* h, const u64* in, u64* out, const Digit& dg, u32 F, u32 nparent, const u64* poff,
+                     const u64* ptiles, u64* cursors, u64 max_tiles) {
+  const bool low32 = (h->cfg.key_mask & 0xffffffffull) == 0xffffffffull;
+  if (dg.mode == 0 && dg.shift + dg.bits <= 32 && low32 && (F & (F - 1)) == 0)
+    return launch_scatter_tm<IPT, 0>(h, in, out, dg, F, nparent, poff, ptiles, cursors, max_tiles);
+  return launch_scatter_tm<IPT, 2>(h, in, out, dg, F, nparent, poff, ptiles, cursors, max_tiles);
 }
 
 // Partition `in` (device, n tuples) by pl into rb.out; rb.offsets gets 2^bits+1 offsets.

@@ -192,8 +192,16 @@ rx_scan_kernel(const u64* __restrict__ ghist, u32 nbins, u64* __restrict__ offse
 // Dynamic shared memory: tile (TILE*8) | gdelta (F*8) | hist (F*4) | lbase (F*4).
 constexpr int kScThreads = 512;
 
-template <int IPT>
-__global__ void __launch_bounds__(kScThreads)
+// MODE: compile-time digit function (0 = one radix pass on bits [shift, shift+bits),
+// which must lie below bit 32; 2 = generic digit_of, used for the G-way range split).
+template <int MODE>
+__device__ __forceinline__ u32 sc_digit(const Digit& dg, u32 fmask, u64 v) {
+  if (MODE == 0) return (u32)(v >> dg.shift) & fmask;
+  return digit_of(dg, v);
+}
+
+template <int IPT, int MODE>
+__global__ void __launch_bounds__(kScThreads, 3)
 rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u32 F, u32 nparent,
                   const u64* __restrict__ parent_off, const u64* __restrict__ parent_tiles,
                   u64* __restrict__ cursors) {
@@ -206,6 +214,7 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
   __shared__ u32 warp_tot[kScThreads / 32];
 
   const u32 tid = threadIdx.x;
+  const u32 fmask = F - 1;
   const u64 total_tiles = parent_tiles[nparent];
   const u32 per_thread = (F + kScThreads - 1) / kScThreads;  // bins each thread scans
 
@@ -218,32 +227,37 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
     }
     const u32 p = lo;
     const u64 begin = parent_off[p] + (t - parent_tiles[p]) * TILE;
-    u64 end = begin + TILE;
     const u64 pend = parent_off[p + 1];
-    if (end > pend) end = pend;
-    const u32 cnt = (u32)(end - begin);
+    const u32 cnt = (u32)(pend - begin < (u64)TILE ? pend - begin : (u64)TILE);
+    const u64* src = in + begin;
 
     for (u32 i = tid; i < F; i += kScThreads) hist[i] = 0;
     __syncthreads();
 
     u64 v[IPT];
-    u32 rank[IPT];
-    const bool aligned = ((begin & 1ull) == 0);
+    u32 dr[IPT];  // digit << 16 | rank  (rank < TILE <= 65536, digit < 4096)
+    if (cnt == TILE && (begin & 1ull) == 0) {  // full, 16 B aligned tile: no per-element checks
 #pragma unroll
-    for (int j = 0; j < IPT / 2; j++) {
-      const u64 i = begin + 2ull * (j * kScThreads + tid);
-      if (aligned && i + 1 < end) {
-        ulonglong2 x = ld_stream_v2(in + i);
+      for (int j = 0; j < IPT / 2; j++) {
+        const ulonglong2 x = ld_stream_v2(src + 2u * (j * kScThreads + tid));
         v[2 * j] = x.x;
         v[2 * j + 1] = x.y;
-      } else {
-        v[2 * j] = i < end ? ld_stream(in + i) : 0ull;
-        v[2 * j + 1] = i + 1 < end ? ld_stream(in + i + 1) : 0ull;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < IPT / 2; j++) {
+        const u32 i = 2u * (j * kScThreads + tid);
+        v[2 * j] = i < cnt ? ld_stream(src + i) : 0ull;
+        v[2 * j + 1] = i + 1 < cnt ? ld_stream(src + i + 1) : 0ull;
       }
     }
 #pragma unroll
-    for (int j = 0; j < IPT; j++)
-      if (v[j]) rank[j] = atomicAdd(hist + digit_of(dg, v[j]), 1u);
+    for (int j = 0; j < IPT; j++) {
+      if (v[j] != 0ull) {
+        const u32 d = sc_digit<MODE>(dg, fmask, v[j]);
+        dr[j] = (d << 16) | atomicAdd(hist + d, 1u);
+      }
+    }
     __syncthreads();
 
     // exclusive scan of hist -> lbase; one global claim per non-empty digit
@@ -288,17 +302,27 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
 
 #pragma unroll
     for (int j = 0; j < IPT; j++)
-      if (v[j]) tile[lbase[digit_of(dg, v[j])] + rank[j]] = v[j];
+      if (v[j] != 0ull) tile[lbase[dr[j] >> 16] + (dr[j] & 0xffffu)] = v[j];
     __syncthreads();
 
     // flush: element i of the digit-sorted tile goes to gdelta[digit] + i
-    for (u32 i = tid; i < cnt; i += kScThreads) {
-      const u64 x = tile[i];
-      out[gdelta[digit_of(dg, x)] + i] = x;
+    if (cnt == TILE) {
+#pragma unroll
+      for (int j = 0; j < IPT; j++) {
+        const u32 i = j * kScThreads + tid;
+        const u64 x = tile[i];
+        out[gdelta[sc_digit<MODE>(dg, fmask, x)] + i] = x;
+      }
+    } else {
+      for (u32 i = tid; i < cnt; i += kScThreads) {
+        const u64 x = tile[i];
+        out[gdelta[sc_digit<MODE>(dg, fmask, x)] + i] = x;
+      }
     }
     __syncthreads();
   }
 }
+
 
 // ---- per-partition join --------------------------------------------------------
 // Dynamic shared memory: slots * 8 bytes (slots = power of two).  R_p is inserted
