@@ -191,6 +191,7 @@ rx_scan_kernel(const u64* __restrict__ ghist, u32 nbins, u64* __restrict__ offse
 // Pass 1 / single pass: one parent covering the whole relation.
 // Dynamic shared memory: tile (TILE*8) | gdelta (F*8) | hist (F*4) | lbase (F*4).
 constexpr int kScThreads = 512;
+constexpr int kScParentCache = 256;  // parents whose offset/tile tables are cached in shared memory
 
 // MODE: compile-time digit function (0 = one radix pass on bits [shift, shift+bits),
 // which must lie below bit 32; 2 = generic digit_of, used for the G-way range split).
@@ -213,9 +214,24 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
   u32* lbase = hist + F;
   __shared__ u32 warp_tot[kScThreads / 32];
 
+  // the tile -> parent search would be a chain of dependent global loads per tile:
+  // keep both small tables in shared memory when they fit
+  __shared__ u64 s_ptiles[kScParentCache + 1], s_poff[kScParentCache + 1];
+
   const u32 tid = threadIdx.x;
   const u32 fmask = F - 1;
-  const u64 total_tiles = parent_tiles[nparent];
+  const bool cached = nparent <= kScParentCache;
+  if (cached) {
+    for (u32 i = tid; i <= nparent; i += kScThreads) {
+      s_ptiles[i] = parent_tiles[i];
+      s_poff[i] = parent_off[i];
+    }
+  }
+  for (u32 i = tid; i < F; i += kScThreads) hist[i] = 0;
+  __syncthreads();
+  const u64* pt = cached ? s_ptiles : parent_tiles;
+  const u64* po = cached ? s_poff : parent_off;
+  const u64 total_tiles = pt[nparent];
   const u32 per_thread = (F + kScThreads - 1) / kScThreads;  // bins each thread scans
 
   for (u64 t = blockIdx.x; t < total_tiles; t += gridDim.x) {
@@ -223,16 +239,13 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
     u32 lo = 0, hi = nparent;
     while (hi - lo > 1) {
       const u32 mid = (lo + hi) >> 1;
-      if (parent_tiles[mid] <= t) lo = mid; else hi = mid;
+      if (pt[mid] <= t) lo = mid; else hi = mid;
     }
     const u32 p = lo;
-    const u64 begin = parent_off[p] + (t - parent_tiles[p]) * TILE;
-    const u64 pend = parent_off[p + 1];
+    const u64 begin = po[p] + (t - pt[p]) * TILE;
+    const u64 pend = po[p + 1];
     const u32 cnt = (u32)(pend - begin < (u64)TILE ? pend - begin : (u64)TILE);
     const u64* src = in + begin;
-
-    for (u32 i = tid; i < F; i += kScThreads) hist[i] = 0;
-    __syncthreads();
 
     u64 v[IPT];
     u32 dr[IPT];  // digit << 16 | rank  (rank < TILE <= 65536, digit < 4096)
@@ -292,6 +305,7 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
         const u32 b = b0 + k;
         if (b < F) {
           const u32 c = hist[b];
+          hist[b] = 0;  // ready for the next tile (nobody reads hist after this scan)
           lbase[b] = run;
           if (c) gdelta[b] = atomicAdd(cursors + (u64)p * F + b, (u64)c) - run;
           run += c;
@@ -340,8 +354,11 @@ constexpr int kJoinBatch = 8;  // loads in flight per thread
 // keys that fills one contiguous run of slots, and a probe that must walk to the first
 // empty slot (to count duplicates) would walk the whole run.  The golden-ratio multiply
 // spreads consecutive keys evenly, so runs stay 1-2 slots long at load <= 0.5.
-__device__ __forceinline__ u32 join_slot(u64 hi_key, u32 hshift) {
-  return (u32)((hi_key * 0x9E3779B97F4A7C15ull) >> hshift);
+__device__ __forceinline__ u32 join_slot(u64 key, u32 radix_bits, u32 hshift) {
+  // keys are 32-bit in every in-scope input; fold the (normally zero) upper half in so
+  // wider keys still hash, then one 32-bit multiply
+  const u32 k32 = (u32)(key >> radix_bits) ^ (u32)(key >> 32);
+  return (k32 * 0x9E3779B1u) >> hshift;
 }
 
 __global__ void __launch_bounds__(kJoinThreads, 2)
@@ -352,7 +369,7 @@ rx_join_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const u
   u64* tab = reinterpret_cast<u64*>(smem_raw);
   const u32 tid = threadIdx.x;
   const u32 smask = slots - 1;
-  const u32 hshift = 64 - (31 - __clz(slots));  // slots is a power of two
+  const u32 hshift = 32 - (31 - __clz(slots));  // slots is a power of two
   const u32 chunk_cap = slots / 2;
   u64 matches = 0, checksum = 0, maxpart = 0, chunked = 0;
 
@@ -387,12 +404,13 @@ rx_join_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const u
 #pragma unroll
         for (int j = 0; j < kJoinBatch; j++) {
           if (rv[j] == 0ull) continue;
-          u32 slot = join_slot((rv[j] & key_mask) >> radix_bits, hshift);
+          u32 slot = join_slot(rv[j] & key_mask, radix_bits, hshift);
           while (atomicCAS(tab + slot, 0ull, rv[j]) != 0ull) slot = (slot + 1) & smask;
         }
       }
       __syncthreads();
       // probe: a batch of S loads in flight, then the home slots of the batch, then the walks
+      u32 matches32 = 0;  // < 2^32 per thread per chunk
       for (u64 b = s0; b < s1; b += (u64)kJoinThreads * kJoinBatch) {
         u64 sv[kJoinBatch], cur[kJoinBatch];
         u32 sl[kJoinBatch];
@@ -403,23 +421,22 @@ rx_join_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const u
         }
 #pragma unroll
         for (int j = 0; j < kJoinBatch; j++) {
-          sl[j] = join_slot((sv[j] & key_mask) >> radix_bits, hshift);
+          sl[j] = join_slot(sv[j] & key_mask, radix_bits, hshift);
           cur[j] = sv[j] ? tab[sl[j]] : 0ull;
         }
 #pragma unroll
         for (int j = 0; j < kJoinBatch; j++) {
           const u64 key = sv[j] & key_mask;
-          u64 c = cur[j], cnt = 0, sumr = 0;
+          u64 c = cur[j];
           u32 slot = sl[j];
           while (c != 0ull) {
-            if ((c & key_mask) == key) { ++cnt; sumr += c; }
+            if ((c & key_mask) == key) { ++matches32; checksum += c + sv[j]; }
             slot = (slot + 1) & smask;
             c = tab[slot];
           }
-          matches += cnt;
-          checksum += sumr + cnt * sv[j];
         }
       }
+      matches += matches32;
     }
   }
   u64 v[2] = {matches, checksum};
