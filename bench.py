@@ -219,6 +219,8 @@ class Rank:
             import torch.distributed as dist
             dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
             self.dist = dist
+            from htm_hashjoin_b200 import exchange
+            self.exchange = exchange
         G = self.world
         self.n, self.m = 1 << args.log_r, 1 << args.log_s
         self.domain = G * self.n
@@ -280,34 +282,27 @@ class Rank:
         if host:  # H2D of this rank's slices, then the same device pipeline
             self.h.copy(self.dR.data_ptr(), self.hR.ctypes.data, self.n * 8)
             self.h.copy(self.dS.data_ptr(), self.hS.ctypes.data, self.m * 8)
-        dom_bits = (self.domain - 1).bit_length()
+        ex = self.exchange
+        dom_bits = ex.domain_bits_for(self.domain)
         # 1. split both slices by destination GPU (high key bits of the key domain)
         self.h.exchange_partition(self.dR.data_ptr(), self.n, G, dom_bits, self.sendR.data_ptr(), self.offR.data_ptr())
         self.h.exchange_partition(self.dS.data_ptr(), self.m, G, dom_bits, self.sendS.data_ptr(), self.offS.data_ptr())
-        self.launches += 6
-        offs = torch.stack([self.offR, self.offS]).cpu()
+        self.launches += 6  # hist + scan + scatter per relation
         # 2. counts, then the tuples, all-to-all over NCCL (NVLink 5 / NVSwitch)
-        send_counts = (offs[:, 1:] - offs[:, :-1]).contiguous()  # [2, G]
-        recv_counts = torch.empty_like(send_counts)
-        sc, rc = send_counts.cuda(), recv_counts.cuda()
-        self.dist.all_to_all_single(rc[0], sc[0])
-        self.dist.all_to_all_single(rc[1], sc[1])
-        recv_counts = rc.cpu()
-        nr, ns = int(recv_counts[0].sum()), int(recv_counts[1].sum())
-        assert nr <= self.recvR.numel() and ns <= self.recvS.numel(), "exchange receive buffer too small"
-        self.dist.all_to_all_single(self.recvR[:nr], self.sendR, recv_counts[0].tolist(), send_counts[0].tolist())
-        self.dist.all_to_all_single(self.recvS[:ns], self.sendS, recv_counts[1].tolist(), send_counts[1].tolist())
+        sc_r = self.offR[1:] - self.offR[:-1]
+        sc_s = self.offS[1:] - self.offS[:-1]
+        rc_r, rc_s = ex.exchange_counts(sc_r), ex.exchange_counts(sc_s)
+        counts = torch.stack([sc_r, sc_s, rc_r, rc_s]).cpu().tolist()
+        nr = ex.exchange_tuples(self.sendR, counts[0], self.recvR, counts[2])
+        ns = ex.exchange_tuples(self.sendS, counts[1], self.recvS, counts[3])
         torch.cuda.synchronize()
-        self.nvlink_bytes += 8 * (self.n - int(send_counts[0][self.rank]) + self.m - int(send_counts[1][self.rank]))
+        self.nvlink_bytes += 8 * (self.n - counts[0][self.rank] + self.m - counts[1][self.rank])
         # 3. local join of the received partitions
         res = self.h.join((self.recvR.data_ptr(), nr), (self.recvS.data_ptr(), ns))
         self.launches += res.kernel_launches
         self.last = res
-        # 4. {matches, checksum} summed over ranks (wrapping int64 add == u64 add)
-        out = torch.from_numpy(np.array([res.matches, res.checksum], dtype=np.uint64).view(np.int64)).cuda()
-        self.dist.all_reduce(out)
-        out = out.cpu().numpy().view(np.uint64)
-        return int(out[0]), int(out[1])
+        # 4. {matches, checksum} summed over ranks
+        return ex.reduce_result(res.matches, res.checksum, "cuda")
 
     def barrier(self):
         if self.dist:

@@ -1,0 +1,87 @@
+"""World-size-2 gloo test of the multi-GPU host logic (htm_hashjoin_b200/exchange.py).
+The CUDA pieces (range split, local join) are stood in for by numpy / the oracle here;
+on the GPU box bench.py runs the same exchange code over NCCL."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _split_by_dest(a, G, dom_bits):
+    """numpy statement of hj_exchange_partition's digit (rx_kernels.cuh digit_of mode 2)."""
+    dest = np.minimum(((a - np.uint64(1)) * np.uint64(G)) >> np.uint64(dom_bits), np.uint64(G - 1)).astype(np.int64)
+    order = np.argsort(dest, kind="stable")
+    return a[order], np.bincount(dest, minlength=G)
+
+
+def _worker(rank, world, port, n, m, q):
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from htm_hashjoin_b200 import exchange
+    from tests.oracle_lib import Oracle
+    orc = Oracle()
+    # global relations: every rank can rebuild them, and keeps only its slice
+    R = orc.generate_data("shuffle", n)
+    S = orc.mc_fk(m, n)
+    r_slice = R[rank * n // world:(rank + 1) * n // world]
+    s_slice = S[rank * m // world:(rank + 1) * m // world]
+    dom_bits = exchange.domain_bits_for(n)
+    recv = []
+    for sl in (r_slice, s_slice):
+        send, counts = _split_by_dest(sl, world, dom_bits)
+        sc = torch.from_numpy(counts.astype(np.int64))
+        rc = exchange.exchange_counts(sc)
+        buf = torch.empty(int(rc.sum()) + 5, dtype=torch.int64)
+        got = exchange.exchange_tuples(torch.from_numpy(send.view(np.int64).copy()), sc.tolist(), buf, rc.tolist())
+        recv.append(buf[:got].numpy().view(np.uint64).copy())
+    # every key received belongs to this rank's range
+    lo, hi = rank * n // world, (rank + 1) * n // world
+    for a in recv:
+        assert a.size == 0 or (a.min() >= lo + 1 and a.max() <= hi)
+    mt, ck = orc.true_join(recv[0], recv[1])
+    total = exchange.reduce_result(mt, ck, "cpu")
+    if rank == 0:
+        q.put((total, orc.true_join(R, S)))
+    dist.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+def test_two_rank_exchange_matches_global_join(built):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    n, m = 1 << 14, 5 << 14
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, n, m, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    total, want = q.get(timeout=240)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert total == want
+    assert want[0] == m
+
+
+def test_reduce_wraps_mod_2_64():
+    """int64 two's-complement addition is u64 addition mod 2^64."""
+    a = np.array([2 ** 63 + 5, 2 ** 64 - 1], dtype=np.uint64).view(np.int64)
+    b = np.array([2 ** 63 + 7, 3], dtype=np.uint64).view(np.int64)
+    s = (torch.from_numpy(a.copy()) + torch.from_numpy(b.copy())).numpy().view(np.uint64)
+    assert s.tolist() == [12, 2]
