@@ -530,7 +530,9 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
   mark(h, E_JOIN0);
   {
     size_t smem = (size_t)pl.slots * 8;
-    auto k = rx_join_kernel;
+    // <loads in flight per thread, CTAs/SM the register budget is set for>
+    static const int variant = getenv("HJ_JOIN_VARIANT") ? atoi(getenv("HJ_JOIN_VARIANT")) : 0;
+    auto k = variant == 1 ? rx_join_kernel<4, 3> : variant == 2 ? rx_join_kernel<6, 3> : rx_join_kernel<8, 2>;
     CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int grid = grid_for(h, (const void*)k, kJoinThreads, smem);
     u32 nparts = 1u << pl.bits;

@@ -234,21 +234,20 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
   const u64 total_tiles = pt[nparent];
   const u32 per_thread = (F + kScThreads - 1) / kScThreads;  // bins each thread scans
 
-  for (u64 t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-    // which parent does tile t belong to: last p with parent_tiles[p] <= t
-    u32 lo = 0, hi = nparent;
+  // Locate tile t (parent, start, length) and issue its loads.  Called for the first tile
+  // and then, for tile k+1, right after tile k has been moved to shared memory: the loads
+  // fly while tile k is flushed, so the read stream never drains.
+  u64 v[IPT];
+  auto load_tile = [&](u64 t, u32& p_out, u32& cnt_out) {
+    u32 lo = 0, hi = nparent;  // last p with parent_tiles[p] <= t
     while (hi - lo > 1) {
       const u32 mid = (lo + hi) >> 1;
       if (pt[mid] <= t) lo = mid; else hi = mid;
     }
-    const u32 p = lo;
-    const u64 begin = po[p] + (t - pt[p]) * TILE;
-    const u64 pend = po[p + 1];
+    const u64 begin = po[lo] + (t - pt[lo]) * TILE;
+    const u64 pend = po[lo + 1];
     const u32 cnt = (u32)(pend - begin < (u64)TILE ? pend - begin : (u64)TILE);
     const u64* src = in + begin;
-
-    u64 v[IPT];
-    u32 dr[IPT];  // digit << 16 | rank  (rank < TILE <= 65536, digit < 4096)
     if (cnt == TILE && (begin & 1ull) == 0) {  // full, 16 B aligned tile: no per-element checks
 #pragma unroll
       for (int j = 0; j < IPT / 2; j++) {
@@ -264,6 +263,15 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
         v[2 * j + 1] = i + 1 < cnt ? ld_stream(src + i + 1) : 0ull;
       }
     }
+    p_out = lo;
+    cnt_out = cnt;
+  };
+
+  u64 t = blockIdx.x;
+  u32 p = 0, cnt = 0;
+  if (t < total_tiles) load_tile(t, p, cnt);
+  while (t < total_tiles) {
+    u32 dr[IPT];  // digit << 16 | rank  (rank < TILE <= 65536, digit < 4096)
 #pragma unroll
     for (int j = 0; j < IPT; j++) {
       if (v[j] != 0ull) {
@@ -271,7 +279,7 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
         dr[j] = (d << 16) | atomicAdd(hist + d, 1u);
       }
     }
-    __syncthreads();
+    __syncthreads();  // also: every thread has finished flushing the previous tile
 
     // exclusive scan of hist -> lbase; one global claim per non-empty digit
     {
@@ -317,10 +325,15 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
 #pragma unroll
     for (int j = 0; j < IPT; j++)
       if (v[j] != 0ull) tile[lbase[dr[j] >> 16] + (dr[j] & 0xffffu)] = v[j];
+
+    // v is dead: start the next tile's loads before flushing this one
+    const u32 cnt_cur = cnt;
+    t += gridDim.x;
+    if (t < total_tiles) load_tile(t, p, cnt);
     __syncthreads();
 
     // flush: element i of the digit-sorted tile goes to gdelta[digit] + i
-    if (cnt == TILE) {
+    if (cnt_cur == TILE) {
 #pragma unroll
       for (int j = 0; j < IPT; j++) {
         const u32 i = j * kScThreads + tid;
@@ -328,12 +341,13 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
         out[gdelta[sc_digit<MODE>(dg, fmask, x)] + i] = x;
       }
     } else {
-      for (u32 i = tid; i < cnt; i += kScThreads) {
+      for (u32 i = tid; i < cnt_cur; i += kScThreads) {
         const u64 x = tile[i];
         out[gdelta[sc_digit<MODE>(dg, fmask, x)] + i] = x;
       }
     }
-    __syncthreads();
+    // no barrier here: the one after the next tile's ranking orders this flush before the
+    // next writes to lbase/gdelta/tile
   }
 }
 
@@ -347,7 +361,6 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
 // With S == nullptr this is the build-only PRO of the reference and the result
 // is its "Results" checksum: sum of idx with N = NEXT_POW_2(|R_p|) (:239-257).
 constexpr int kJoinThreads = 512;
-constexpr int kJoinBatch = 8;  // loads in flight per thread
 
 // Fibonacci hashing of the key bits above the radix bits.  The reference indexes its
 // per-partition table with those bits directly (parallel_radix_join.c:252); with dense
@@ -361,7 +374,8 @@ __device__ __forceinline__ u32 join_slot(u64 key, u32 radix_bits, u32 hshift) {
   return (k32 * 0x9E3779B1u) >> hshift;
 }
 
-__global__ void __launch_bounds__(kJoinThreads, 2)
+template <int kJoinBatch, int MINB>
+__global__ void __launch_bounds__(kJoinThreads, MINB)
 rx_join_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const u64* __restrict__ Sp,
                const u64* __restrict__ offS, u32 nparts, u32 radix_bits, u32 slots, u64 key_mask,
                u64* __restrict__ ctr) {
