@@ -18,6 +18,7 @@
 #include "../../include/hj_b200.h"
 #include "gt_kernels.cuh"
 #include "rx_kernels.cuh"
+#include "rx_join32.cuh"
 
 using namespace hj;
 
@@ -418,6 +419,7 @@ int ensure_rel(hj_handle* h, RelBufs& rb, u64 n, const RadixPlan& pl) {
 // Histogram launch: 512-thread CTAs, or 1024 when the privatised histogram (> 64 KiB)
 // leaves room for one CTA per SM only.
 int launch_hist(hj_handle* h, const u64* in, u64 n, const Digit& dg, u32 nbins, u64* ghist) {
+  u64* ctr = h->ctr;
   const size_t smem = (size_t)nbins * 4;
   const bool big = smem > 64 * 1024;
   const int threads = big ? 1024 : 512;
@@ -426,8 +428,8 @@ int launch_hist(hj_handle* h, const u64* in, u64 n, const Digit& dg, u32 nbins, 
   int grid = grid_for(h, k, threads, smem);
   u64 tiles = (n + (u64)threads * kHistIPT - 1) / ((u64)threads * kHistIPT);
   if ((u64)grid > tiles) grid = (int)(tiles ? tiles : 1);
-  if (big) rx_hist_kernel<true, 1024><<<grid, 1024, smem, h->stream>>>(in, n, dg, nbins, ghist);
-  else rx_hist_kernel<true, 512><<<grid, 512, smem, h->stream>>>(in, n, dg, nbins, ghist);
+  if (big) rx_hist_kernel<true, 1024><<<grid, 1024, smem, h->stream>>>(in, n, dg, nbins, ghist, ctr);
+  else rx_hist_kernel<true, 512><<<grid, 512, smem, h->stream>>>(in, n, dg, nbins, ghist, ctr);
   h->launches++;
   CK(cudaGetLastError());
   return HJ_OK;
@@ -528,6 +530,52 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
     if ((rc = radix_partition_rel(h, dS, m, h->rb[1], pl, E_RX + 5))) return rc;
   }
   mark(h, E_JOIN0);
+  // 32-bit-key fast path first (returns at once if rx_hist saw wider keys), then the generic
+  // kernel (returns at once if the fast path took the join).  Build-only PRO is generic.
+  const bool try32 = dS && pl.bits >= 1 && (h->cfg.key_mask & 0xffffffffull) == 0xffffffffull &&
+                     !getenv("HJ_NO_JOIN32");
+  const u32 nparts = 1u << pl.bits;
+  if (try32) {
+    static const int variant = getenv("HJ_J32_VARIANT") ? atoi(getenv("HJ_J32_VARIANT")) : 0;
+    const void* k;
+    int threads, ctas;
+    int W = 4;
+#define J32V(T, B, M, WW) k = (const void*)rx_join32_kernel<T, B, M, WW>; threads = T; ctas = M; W = WW; break
+    switch (variant) {
+      case 1: J32V(512, 4, 3, 4);
+      case 2: J32V(512, 4, 3, 2);
+      case 3: J32V(512, 8, 2, 2);
+      case 4: J32V(256, 8, 4, 4);
+      case 5: J32V(256, 8, 4, 2);
+      case 6: J32V(384, 4, 4, 4);
+      case 7: J32V(384, 4, 4, 2);
+      case 8: J32V(768, 4, 2, 4);
+      case 9: J32V(768, 4, 2, 2);
+      default: J32V(512, 8, 2, 4);
+    }
+#undef J32V
+    // table: 4 slots per expected R tuple if shared memory allows `ctas` CTAs per SM with it
+    cudaFuncAttributes fa;
+    CK(cudaFuncGetAttributes(&fa, k));
+    const size_t per_sm = 228 * 1024, reserved = 1024;
+    size_t avail = per_sm / ctas - reserved - fa.sharedSizeBytes;
+    if (avail > h->smem_optin - fa.sharedSizeBytes) avail = h->smem_optin - fa.sharedSizeBytes;
+    u64 want = (n >> pl.bits) + 1;
+    if (want < 64) want = 64;
+    // want = expected R tuples per partition -> 4 slots each; buckets hold W slots in 8*W bytes
+    u32 nbuckets = (u32)(want * 32 <= avail ? want * 4 / W : avail / (8 * W));
+    nbuckets &= ~1u;  // key array = whole 16-byte words for either W
+    const size_t smem = (size_t)nbuckets * 8 * W;
+    CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int grid = grid_for(h, k, threads, smem);
+    if ((u32)grid > nparts) grid = (int)nparts;
+    const u64 *aR = h->rb[0].out.p, *aoR = h->rb[0].offsets.p, *aS = h->rb[1].out.p, *aoS = h->rb[1].offsets.p;
+    u32 a_np = nparts, a_bits = pl.bits;
+    u64* a_ctr = h->ctr;
+    void* args[] = {&aR, &aoR, &aS, &aoS, &a_np, &a_bits, &nbuckets, &a_ctr};
+    CK(cudaLaunchKernel(k, dim3(grid), dim3(threads), args, smem, h->stream));
+    h->launches++;
+  }
   {
     size_t smem = (size_t)pl.slots * 8;
     // <loads in flight per thread, CTAs/SM the register budget is set for>
@@ -535,11 +583,10 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
     auto k = variant == 1 ? rx_join_kernel<4, 3> : variant == 2 ? rx_join_kernel<6, 3> : rx_join_kernel<8, 2>;
     CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int grid = grid_for(h, (const void*)k, kJoinThreads, smem);
-    u32 nparts = 1u << pl.bits;
     if ((u32)grid > nparts) grid = (int)nparts;
     k<<<grid, kJoinThreads, smem, h->stream>>>(h->rb[0].out.p, h->rb[0].offsets.p, dS ? h->rb[1].out.p : nullptr,
                                                dS ? h->rb[1].offsets.p : nullptr, nparts, pl.bits, pl.slots,
-                                               h->cfg.key_mask, h->ctr);
+                                               h->cfg.key_mask, h->ctr, try32 ? 1 : 0);
     h->launches++;
     CK(cudaGetLastError());
   }

@@ -26,6 +26,7 @@ enum Counter {
   C_TOO_BIG,         // R partitions processed in >1 shared-memory chunk
   C_SPAN,            // sum over sampled CTA chunks of (max home - min home + 1), in slots
   C_CHUNKS,          // number of sampled CTA chunks
+  C_KEY_HI,          // OR of the key bits above bit 31 over every tuple rx_hist saw (0: rx_join32 applies)
   C_COUNT = 16
 };
 

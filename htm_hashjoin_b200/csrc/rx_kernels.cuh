@@ -49,9 +49,11 @@ constexpr int kHistIPT = 8;  // threads per CTA: 512, or 1024 when the privatise
 // nbins*4 bytes of dynamic shared memory when SMEM, else straight global atomics
 template <bool SMEM, int kHistThreads>
 __global__ void __launch_bounds__(kHistThreads)
-rx_hist_kernel(const u64* __restrict__ in, u64 n, Digit dg, u32 nbins, u64* __restrict__ ghist) {
+rx_hist_kernel(const u64* __restrict__ in, u64 n, Digit dg, u32 nbins, u64* __restrict__ ghist,
+               u64* __restrict__ ctr) {
   extern __shared__ u32 shist[];
   const u32 tid = threadIdx.x;
+  u32 key_hi = 0;  // key bits above bit 31, ORed over every tuple: picks the join kernel (rx_join32.cuh)
   if (SMEM) {
     for (u32 i = tid; i < nbins; i += kHistThreads) shist[i] = 0;
     __syncthreads();
@@ -76,6 +78,7 @@ rx_hist_kernel(const u64* __restrict__ in, u64 n, Digit dg, u32 nbins, u64* __re
 #pragma unroll
     for (int j = 0; j < kHistIPT; j++) {
       const bool valid = v[j] != 0ull;
+      key_hi |= (u32)((v[j] & dg.key_mask) >> 32);
       const u32 d = valid ? digit_of(dg, v[j]) : 0xffffffffu;
       // sorted input on high bits puts a whole warp in one bin: add once
       const u32 d0 = __shfl_sync(0xffffffffu, d, 0);
@@ -97,6 +100,8 @@ rx_hist_kernel(const u64* __restrict__ in, u64 n, Digit dg, u32 nbins, u64* __re
       if (c) atomicAdd(ghist + i, (u64)c);
     }
   }
+  key_hi = __reduce_or_sync(0xffffffffu, key_hi);
+  if (key_hi && lane_id() == 0) atomicOr(ctr + C_KEY_HI, (u64)key_hi);
 }
 
 // ---- scan ----------------------------------------------------------------------
@@ -378,7 +383,9 @@ template <int kJoinBatch, int MINB>
 __global__ void __launch_bounds__(kJoinThreads, MINB)
 rx_join_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const u64* __restrict__ Sp,
                const u64* __restrict__ offS, u32 nparts, u32 radix_bits, u32 slots, u64 key_mask,
-               u64* __restrict__ ctr) {
+               u64* __restrict__ ctr, int narrow_keys_elsewhere) {
+  // launched behind rx_join32_kernel: exactly one of the two does the work
+  if (narrow_keys_elsewhere && ctr[C_KEY_HI] == 0ull) return;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   u64* tab = reinterpret_cast<u64*>(smem_raw);
   const u32 tid = threadIdx.x;
