@@ -536,22 +536,16 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
                      !getenv("HJ_NO_JOIN32");
   const u32 nparts = 1u << pl.bits;
   if (try32) {
-    static const int variant = getenv("HJ_J32_VARIANT") ? atoi(getenv("HJ_J32_VARIANT")) : 0;
+    static const int variant = getenv("HJ_J32_VARIANT") ? atoi(getenv("HJ_J32_VARIANT")) : 7;
     const void* k;
     int threads, ctas;
     int W = 4;
 #define J32V(T, B, M, WW) k = (const void*)rx_join32_kernel<T, B, M, WW>; threads = T; ctas = M; W = WW; break
-    switch (variant) {
-      case 1: J32V(512, 4, 3, 4);
+    switch (variant) {  // measured at C3 (profiles/r01_join32_variants.jsonl): 7 is the fastest
+      case 0: J32V(512, 8, 2, 4);
       case 2: J32V(512, 4, 3, 2);
-      case 3: J32V(512, 8, 2, 2);
-      case 4: J32V(256, 8, 4, 4);
       case 5: J32V(256, 8, 4, 2);
-      case 6: J32V(384, 4, 4, 4);
-      case 7: J32V(384, 4, 4, 2);
-      case 8: J32V(768, 4, 2, 4);
-      case 9: J32V(768, 4, 2, 2);
-      default: J32V(512, 8, 2, 4);
+      default: J32V(384, 4, 4, 2);
     }
 #undef J32V
     // table: 4 slots per expected R tuple if shared memory allows `ctas` CTAs per SM with it

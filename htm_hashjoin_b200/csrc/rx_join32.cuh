@@ -187,9 +187,14 @@ rx_join32_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ u32 s_dup;
   J32Tab tab;
+  // pinned in registers: left alone, the compiler rebuilds the shared window base (4 uniform
+  // instructions) and reloads the parameters from the constant bank around every access
   tab.base = (u32)__cvta_generic_to_shared(smem_raw);
+  asm volatile("mov.u32 %0, %0;" : "+r"(tab.base));
   tab.pay_delta = nbuckets * (4u * W);
+  asm volatile("mov.u32 %0, %0;" : "+r"(tab.pay_delta));
   tab.nbuckets = nbuckets;
+  asm volatile("mov.u32 %0, %0;" : "+r"(tab.nbuckets));
   tab.radix_bits = radix_bits;
   const u32 tab_end = tab.base + tab.pay_delta;  // end of the key array
 
