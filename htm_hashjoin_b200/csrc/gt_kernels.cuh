@@ -32,33 +32,6 @@ struct SegMap {
   u64 nslices;
 };
 
-template <bool NOCC, bool PEEK>
-__device__ __forceinline__ bool gt_insert_from(u64* __restrict__ table, u64 mask, u64 v, u64 slot, u32 budget,
-                                               u32& steps, u32& retries) {
-#pragma unroll 1
-  while (budget) {
-    if (NOCC) {
-      // NoCCHashBuild.hpp:45-49: look, then store without synchronisation (racy by design)
-      if (ld_relaxed(table + slot) == 0) {
-        table[slot] = v;
-        return true;
-      }
-    } else if (PEEK) {
-      // AtomicHashBuild.hpp:47-51: relaxed load, CAS only on an empty slot
-      if (ld_relaxed(table + slot) == 0) {
-        if (atomicCAS(table + slot, 0ull, v) == 0ull) return true;
-        ++retries;
-      }
-    } else {
-      if (atomicCAS(table + slot, 0ull, v) == 0ull) return true;
-    }
-    ++steps;
-    slot = (slot + 1) & mask;
-    --budget;
-  }
-  return false;
-}
-
 // IPT tuples per thread ("transaction size": how many inserts a thread has in
 // flight before it looks at any outcome).  IPT == 1 is the scalar variant used
 // for unaligned inputs.
@@ -126,45 +99,80 @@ gt_build_kernel(const u64* __restrict__ R, SegMap sm, u64* __restrict__ table, u
       __syncthreads();
     }
 
-    // first attempt for every tuple of the batch, all in flight together
-    u64 first[IPT];
+    u32 att[IPT];  // attempts used so far == offset from home of the next slot to try
+    u32 pend = 0;  // bit j: tuple j still has to be placed
 #pragma unroll
     for (int j = 0; j < IPT; j++) {
-      first[j] = 1;  // "occupied" for invalid lanes; never examined
-      if (v[j]) {
-        u64* p = table + ((v[j] & key_mask) & mask);
-        if (NOCC || PEEK) first[j] = ld_relaxed(p);
-        else first[j] = atomicCAS(p, 0ull, v[j]);
-      }
+      att[j] = 0;
+      if (v[j]) pend |= 1u << j;
     }
+    u32 failed_bits = 0;
+    bool ranked = NOCC;  // NoCC keeps the reference's unsynchronised behaviour (NoCCHashBuild.hpp:45-49)
+
+    // Rounds: every pending tuple of the batch issues its next attempt, all in flight
+    // together (IPT independent L2 atomics per thread), then the outcomes are examined.
+    // A lost CAS moves on to the next slot (the reference burns the attempt in place, 9-5).
+#pragma unroll 1
+    while (__any_sync(0xffffffffu, pend != 0)) {  // warp-uniform: the ranking below is a warp collective
+      u64 res[IPT];
 #pragma unroll
-    for (int j = 0; j < IPT; j++) {
-      bool failed = false;
-      if (v[j]) {
-        const u64 home = (v[j] & key_mask) & mask;
-        if (NOCC || PEEK) {
-          bool placed = false;
-          if (first[j] == 0ull) {
-            if (NOCC) {
-              table[home] = v[j];
-              placed = true;
-            } else if (atomicCAS(table + home, 0ull, v[j]) == 0ull) {
-              placed = true;
-            } else {
-              ++retries;
-            }
-          }
-          if (!placed) {
-            ++steps;
-            failed = (L <= 1) ||
-                     !gt_insert_from<NOCC, PEEK>(table, mask, v[j], (home + 1) & mask, L - 1, steps, retries);
-          }
-        } else if (first[j] != 0ull) {
-          ++steps;
-          failed = (L <= 1) || !gt_insert_from<NOCC, PEEK>(table, mask, v[j], (home + 1) & mask, L - 1, steps, retries);
+      for (int j = 0; j < IPT; j++) {
+        if (pend >> j & 1u) {
+          u64* p = table + ((((v[j] & key_mask) & mask) + att[j]) & mask);
+          if (NOCC || PEEK) res[j] = ld_relaxed(p);
+          else res[j] = atomicCAS(p, 0ull, v[j]);
         }
       }
-      if (STATS) {
+      if (PEEK) {  // second stage: CAS where the peek saw an empty slot
+#pragma unroll
+        for (int j = 0; j < IPT; j++) {
+          if ((pend >> j & 1u) && res[j] == 0ull) {
+            res[j] = atomicCAS(table + ((((v[j] & key_mask) & mask) + att[j]) & mask), 0ull, v[j]);
+            if (res[j] != 0ull) ++retries;
+          }
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < IPT; j++) {
+        if (pend >> j & 1u) {
+          if (res[j] == 0ull) {
+            if (NOCC) table[(((v[j] & key_mask) & mask) + att[j]) & mask] = v[j];
+            pend &= ~(1u << j);
+          } else {
+            ++steps;
+            ++att[j];
+          }
+        }
+      }
+      // Warp-cooperative restart after the first lost round: lanes of one load instruction
+      // whose tuples share a home slot (duplicate keys sit next to each other in sorted /
+      // locally shuffled inputs) would chase each other down the window one CAS round trip at
+      // a time.  Rank the losers of a home slot (__match_any_sync) and let rank i continue at
+      // home+1+i with i more attempts spent: the lower ranks each try home+1..home+i first,
+      // so those slots are occupied when the build ends and the probe's walk from home never
+      // meets a gap.  Inputs without duplicates never get here.
+      if (!ranked && __any_sync(0xffffffffu, pend != 0)) {
+        ranked = true;
+#pragma unroll
+        for (int j = 0; j < IPT; j++) {
+          const bool lost = pend >> j & 1u;
+          const u64 home = lost ? ((v[j] & key_mask) & mask) : (~0ull - lane_id());
+          const u32 peers = __match_any_sync(0xffffffffu, home);
+          if (lost) att[j] += __popc(peers & ((1u << lane_id()) - 1u));
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < IPT; j++) {
+        if ((pend >> j & 1u) && att[j] >= L) {
+          pend &= ~(1u << j);
+          failed_bits |= 1u << j;
+        }
+      }
+    }
+
+    if (STATS) {
+#pragma unroll
+      for (int j = 0; j < IPT; j++) {
         // locality signal: distinct 32 B table sectors this warp's inserts start in
         const u64 sec = v[j] ? (((v[j] & key_mask) & mask) >> 2) : ~0ull;
         const u32 peers = __match_any_sync(0xffffffffu, sec);
@@ -176,15 +184,25 @@ gt_build_kernel(const u64* __restrict__ R, SegMap sm, u64* __restrict__ table, u
           sampled += __popc(valid);
         }
       }
-      // AtomicHashBuild.hpp:62-63: budget exhausted -> conflicts[]; one atomic per warp
-      const u32 bal = __ballot_sync(0xffffffffu, failed);
-      if (bal) {
-        const int leader = __ffs(bal) - 1;
-        u64 b = 0;
-        if ((int)lane_id() == leader) b = atomicAdd(ctr + C_CONFLICTS, (u64)__popc(bal));
-        b = __shfl_sync(0xffffffffu, b, leader);
-        if (failed) ovf_list[b + __popc(bal & ((1u << lane_id()) - 1u))] = v[j];
+    }
+    // AtomicHashBuild.hpp:62-63: budget exhausted -> conflicts[].  One atomicAdd per warp and
+    // tile claims the range (a claim per load instruction put ~n/32 atomics on one address:
+    // the uniform build spent most of its 1.1 ms queueing there).
+    if (__any_sync(0xffffffffu, failed_bits != 0)) {
+      const u32 mine = __popc(failed_bits);
+      u32 incl = mine;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const u32 y = __shfl_up_sync(0xffffffffu, incl, o);
+        if ((int)lane_id() >= o) incl += y;
       }
+      u64 base = 0;
+      if (lane_id() == 31) base = atomicAdd(ctr + C_CONFLICTS, (u64)incl);
+      base = __shfl_sync(0xffffffffu, base, 31);
+      u64 dst = base + (incl - mine);
+#pragma unroll
+      for (int j = 0; j < IPT; j++)
+        if (failed_bits >> j & 1u) ovf_list[dst++] = v[j];
     }
   }
 
@@ -248,7 +266,7 @@ gt_probe_kernel(const u64* __restrict__ S, u64 m, const u64* __restrict__ table,
     if (slots > ovf_capacity) slots = ovf_capacity;
     omask = slots - 1;
   }
-  u64 matches = 0, checksum = 0, wmatches = 0;
+  u64 matches = 0, checksum = 0, wmatches = 0, omatches = 0;
   const u64 nchunks = (m + TILE - 1) / TILE;
 
   for (u64 c = blockIdx.x; c < nchunks; c += gridDim.x) {
@@ -271,44 +289,49 @@ gt_probe_kernel(const u64* __restrict__ S, u64 m, const u64* __restrict__ table,
         }
       }
     }
-    // home slot of every tuple first: IPT independent loads in flight
-    u64 w0[IPT];
+    // Window walk in rounds: slot home+r of every tuple still walking, IPT independent loads
+    // in flight per thread (a per-tuple walk is a chain of dependent L2 round trips).
+    u32 pend = 0, full = 0;  // bit j: still walking / window exhausted without an empty slot
 #pragma unroll
-    for (int j = 0; j < IPT; j++) w0[j] = s[j] ? __ldg(table + ((s[j] & key_mask) & mask)) : 0ull;
-
+    for (int j = 0; j < IPT; j++)
+      if (s[j]) pend |= 1u << j;
+#pragma unroll 1
+    for (u32 r = 0; r < L && pend; r++) {
+      u64 cur[IPT];
 #pragma unroll
-    for (int j = 0; j < IPT; j++) {
-      if (s[j] == 0ull) continue;
-      const u64 key = s[j] & key_mask;
-      u64 slot = key & mask;
-      u64 cnt = 0, sumr = 0;
-      bool saw_empty = false;
-      u64 cur = w0[j];
-      u32 b = 0;
-#pragma unroll 1
-      while (true) {
-        if (cur == 0ull) { saw_empty = true; break; }
-        if ((cur & key_mask) == key) { ++cnt; sumr += cur; }
-        if (++b >= L) break;
-        slot = (slot + 1) & mask;
-        cur = __ldg(table + slot);
-      }
-      wmatches += cnt;
-      if (!saw_empty && ovf_count) {
-        // the window is full: tuples of this home slot may have overflowed
-        u64 os = ovf_hash(key, omask);
-#pragma unroll 1
-        while (true) {
-          const u64 o = __ldg(ovf_table + os);
-          if (o == 0ull) break;
-          if ((o & key_mask) == key) { ++cnt; sumr += o; }
-          os = (os + 1) & omask;
+      for (int j = 0; j < IPT; j++)
+        if (pend >> j & 1u) cur[j] = __ldg(table + ((((s[j] & key_mask) & mask) + r) & mask));
+#pragma unroll
+      for (int j = 0; j < IPT; j++) {
+        if (pend >> j & 1u) {
+          if (cur[j] == 0ull) {
+            pend &= ~(1u << j);
+          } else {
+            if ((cur[j] & key_mask) == (s[j] & key_mask)) { ++wmatches; checksum += cur[j] + s[j]; }
+            if (r + 1 >= L) { pend &= ~(1u << j); full |= 1u << j; }
+          }
         }
       }
-      matches += cnt;
-      checksum += sumr + cnt * s[j];
+    }
+    // the window is full: tuples of this home slot may have overflowed
+    if (ovf_count && full) {
+#pragma unroll
+      for (int j = 0; j < IPT; j++) {
+        if (full >> j & 1u) {
+          const u64 key = s[j] & key_mask;
+          u64 os = ovf_hash(key, omask);
+#pragma unroll 1
+          while (true) {
+            const u64 o = __ldg(ovf_table + os);
+            if (o == 0ull) break;
+            if ((o & key_mask) == key) { ++omatches; checksum += o + s[j]; }
+            os = (os + 1) & omask;
+          }
+        }
+      }
     }
   }
+  matches = wmatches + omatches;
   u64 v[3] = {matches, checksum, wmatches};
   u64* const d[3] = {ctr + C_MATCHES, ctr + C_CHECKSUM, ctr + C_WINDOW_MATCHES};
   block_sum_atomic<3, kGtThreads>(v, d);
