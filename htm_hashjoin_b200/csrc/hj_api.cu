@@ -19,6 +19,7 @@
 #include "gt_kernels.cuh"
 #include "rx_kernels.cuh"
 #include "rx_join32.cuh"
+#include "rx_joinl2.cuh"
 
 using namespace hj;
 
@@ -375,8 +376,12 @@ int plan_radix(hj_handle* h, u64 n, RadixPlan* pl) {
     if (f & (f - 1)) return HJ_EINVAL;
     while ((1u << bits) < f) bits++;
   } else {
-    // default: R partitions of <= 4096 tuples -> 8192-slot (64 KiB) tables, 3 CTAs per SM
-    while (bits < kMaxTotalBits && (n >> bits) > 4096) bits++;
+    // default: R partitions of <= 16384 tuples -- the largest rx_join32 joins in one piece (one
+    // 1024-thread CTA per SM); measured at C3: 13 bits (6+7) 11.9 ms, 14 bits 12.2, 15 bits 12.7
+    // (cheaper scatter passes outweigh the slower 1-CTA join).  Mid-size inputs get at least 2048
+    // partitions so every SM has several.
+    while (bits < kMaxTotalBits && (n >> bits) > 16384) bits++;
+    while (bits < 11 && (n >> bits) > 2048) bits++;
     if (bits < 4) bits = 4;
   }
   if (bits < 1 || bits > kMaxTotalBits) return HJ_EINVAL;
@@ -460,7 +465,8 @@ int launch_scatter_t(hj_handle* h, const u64* in, u64* out, const Digit& dg, u32
 
 // Partition `in` (device, n tuples) by pl into rb.out; rb.offsets gets 2^bits+1 offsets.
 // evb = first of this relation's five phase events (or -1: untimed).
-int radix_partition_rel(hj_handle* h, const u64* in, u64 n, RelBufs& rb, const RadixPlan& pl, int evb) {
+int radix_partition_rel(hj_handle* h, const u64* in, u64 n, RelBufs& rb, const RadixPlan& pl, int evb,
+                        u64* max_bin = nullptr) {
   const u32 nb = 1u << pl.bits;
   const u32 F1 = 1u << pl.b1, F2 = 1u << pl.b2;
   const u32 tile = kScThreads * pl.tile_ipt;
@@ -481,7 +487,7 @@ int radix_partition_rel(hj_handle* h, const u64* in, u64 n, RelBufs& rb, const R
   // Single pass: f2 = nb makes parent 0 span every bin.
   rx_scan_kernel<<<1, kScanThreads, 0, h->stream>>>(rb.ghist.p, nb, rb.offsets.p, rb.cursors.p,
                                                     pl.passes == 2 ? F2 : nb, rb.poff.p, rb.pcur.p, rb.ptiles.p,
-                                                    rb.one.p, tile, nullptr);
+                                                    rb.one.p, tile, max_bin);
   h->launches++;
   CK(cudaGetLastError());
   if (evb >= 0) mark(h, evb + 2);
@@ -524,19 +530,51 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
   if (dS && (rc = ensure_rel(h, h->rb[1], m, pl))) return rc;
   CK(cudaMemsetAsync(h->ctr, 0, C_COUNT * sizeof(u64), h->stream));
   if ((rc = wait_staged(h, E_CPR, pendR))) return rc;
-  if ((rc = radix_partition_rel(h, dR, n, h->rb[0], pl, E_RX))) return rc;
+  if ((rc = radix_partition_rel(h, dR, n, h->rb[0], pl, E_RX, h->ctr + C_MAX_PART))) return rc;
   if (dS) {
     if ((rc = wait_staged(h, E_CPS, pendS))) return rc;
     if ((rc = radix_partition_rel(h, dS, m, h->rb[1], pl, E_RX + 5))) return rc;
   }
   mark(h, E_JOIN0);
+  // Which join: shared memory while an R partition (plus 8 sigma of a random split) fits the
+  // largest table one CTA can hold, else the L2-resident partition-local table (rx_joinl2.cuh).
+  const u32 nparts = 1u << pl.bits;
+  const u64 per = (n >> pl.bits) + 1;
+  u64 need = per + 64;
+  for (u64 r = 1; r * r < per * 64; r++) need = per + 64 + r;  // + 8*sqrt(per)
+  const bool use_l2 = dS && (getenv("HJ_FORCE_L2JOIN") || need > 21000) && !getenv("HJ_NO_L2JOIN");
+  if (use_l2) {
+    Digit full;
+    memset(&full, 0, sizeof(full));
+    full.key_mask = h->cfg.key_mask;
+    if (pl.passes == 2) { full.mode = 1; full.b1 = pl.b1; full.b2 = pl.b2; }
+    else { full.mode = 0; full.shift = 0; full.bits = pl.bits; }
+    const u64 tslots = l2_table_slots(n, nparts);
+    if ((rc = ensure(h, h->table, tslots))) return rc;
+    h->built = false;
+    CK(cudaMemsetAsync(h->table.p, 0, tslots * sizeof(u64), h->stream));
+    constexpr int IPT = 4;
+    int gb = grid_for(h, (const void*)rx_l2_build_kernel<IPT>, kL2Threads, 0);
+    const int narrow_possible = (h->cfg.key_mask & 0xffffffffull) == 0xffffffffull ? 1 : 0;
+    rx_l2_build_kernel<IPT><<<gb, kL2Threads, 0, h->stream>>>(h->rb[0].out.p, n, h->rb[0].offsets.p, full, pl.bits,
+                                                              h->table.p, h->ctr + C_TILE0);
+    int gp = grid_for(h, (const void*)rx_l2_probe_kernel<IPT, true>, kL2Threads, 0);
+    rx_l2_probe_kernel<IPT, true><<<gp, kL2Threads, 0, h->stream>>>(h->rb[1].out.p, m, h->rb[0].offsets.p, full,
+                                                                    pl.bits, h->table.p, h->ctr, narrow_possible);
+    gp = grid_for(h, (const void*)rx_l2_probe_kernel<IPT, false>, kL2Threads, 0);
+    rx_l2_probe_kernel<IPT, false><<<gp, kL2Threads, 0, h->stream>>>(h->rb[1].out.p, m, h->rb[0].offsets.p, full,
+                                                                     pl.bits, h->table.p, h->ctr, narrow_possible);
+    h->launches += 3;
+    CK(cudaGetLastError());
+  }
   // 32-bit-key fast path first (returns at once if rx_hist saw wider keys), then the generic
   // kernel (returns at once if the fast path took the join).  Build-only PRO is generic.
-  const bool try32 = dS && pl.bits >= 1 && (h->cfg.key_mask & 0xffffffffull) == 0xffffffffull &&
+  const bool try32 = !use_l2 && dS && pl.bits >= 1 && (h->cfg.key_mask & 0xffffffffull) == 0xffffffffull &&
                      !getenv("HJ_NO_JOIN32");
-  const u32 nparts = 1u << pl.bits;
   if (try32) {
-    static const int variant = getenv("HJ_J32_VARIANT") ? atoi(getenv("HJ_J32_VARIANT")) : 7;
+    static const int forced = getenv("HJ_J32_VARIANT") ? atoi(getenv("HJ_J32_VARIANT")) : -1;
+    // CTAs/SM by table size (chunk capacity = 0.75 * slots): 4 -> 5.3k, 2 -> 10.8k, 1 -> 21.7k tuples
+    const int variant = forced >= 0 ? forced : need <= 5300 ? 7 : need <= 10800 ? 3 : 10;
     const void* k;
     int threads, ctas;
     int W = 4;
@@ -544,7 +582,9 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
     switch (variant) {  // measured at C3 (profiles/r01_join32_variants.jsonl): 7 is the fastest
       case 0: J32V(512, 8, 2, 4);
       case 2: J32V(512, 4, 3, 2);
+      case 3: J32V(512, 8, 2, 2);
       case 5: J32V(256, 8, 4, 2);
+      case 10: J32V(1024, 4, 1, 2);
       default: J32V(384, 4, 4, 2);
     }
 #undef J32V
@@ -570,7 +610,7 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
     CK(cudaLaunchKernel(k, dim3(grid), dim3(threads), args, smem, h->stream));
     h->launches++;
   }
-  {
+  if (!use_l2) {
     size_t smem = (size_t)pl.slots * 8;
     // <loads in flight per thread, CTAs/SM the register budget is set for>
     static const int variant = getenv("HJ_JOIN_VARIANT") ? atoi(getenv("HJ_JOIN_VARIANT")) : 0;

@@ -27,7 +27,8 @@ enum Counter {
   C_SPAN,            // sum over sampled CTA chunks of (max home - min home + 1), in slots
   C_CHUNKS,          // number of sampled CTA chunks
   C_KEY_HI,          // OR of the key bits above bit 31 over every tuple rx_hist saw (0: rx_join32 applies)
-  C_COUNT = 16
+  C_TILE0, C_TILE1,  // tile tickets of the L2 join kernels (rx_joinl2.cuh)
+  C_COUNT = 24
 };
 
 constexpr u64 kOvfMul = 0x9E3779B97F4A7C15ull;  // Fibonacci hashing for the overflow table

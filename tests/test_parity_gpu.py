@@ -124,14 +124,55 @@ def test_radix_payloads_and_duplicates(hj, oracle):
             assert (res.matches, res.checksum) == want, algo
 
 
-def test_radix_oversized_partitions_chunked(hj, oracle):
-    """Fan-out too small for shared memory: R partitions are joined in chunks."""
+def test_radix_oversized_partitions_l2_table(hj, oracle):
+    """Fan-out too small for shared memory: partition-local table in global memory (rx_joinl2.cuh)."""
     n = 1 << 18
     R, S = _inputs(hj, "shuffle", 16, n)
     with hj.HashJoin("radix", num_partitions=2, passes=1) as h:
         res = h.join(R, S)
         assert (res.matches, res.checksum) == oracle.true_join(R, S)
         assert res.max_partition == n // 2
+
+
+def test_radix_oversized_partitions_chunked(hj, oracle, monkeypatch):
+    """Same with the L2 path switched off: R partitions go through shared memory in chunks."""
+    monkeypatch.setenv("HJ_NO_L2JOIN", "1")
+    n = 1 << 18
+    R, S = _inputs(hj, "shuffle", 16, n)
+    with hj.HashJoin("radix", num_partitions=2, passes=1) as h:
+        res = h.join(R, S)
+        assert (res.matches, res.checksum) == oracle.true_join(R, S)
+        assert res.max_partition == n // 2
+
+
+@pytest.mark.parametrize("dist,rng", [("uniform", 16), ("random", 16), ("shuffle", 16)])
+@pytest.mark.parametrize("bits,passes", [(3, 1), (8, 2)])
+def test_radix_l2_join_duplicates_and_payloads(hj, oracle, monkeypatch, dist, rng, bits, passes):
+    """The L2 join forced at fan-outs that would fit shared memory: duplicate keys on both sides, payloads."""
+    monkeypatch.setenv("HJ_FORCE_L2JOIN", "1")
+    n = (1 << 17) + 5
+    R, S = _inputs(hj, dist, rng, n)
+    R = R | (np.arange(n, dtype=np.uint64) << np.uint64(32))
+    S = S | ((np.arange(n, dtype=np.uint64) * np.uint64(7)) << np.uint64(32))
+    want = oracle.true_join(R, S, key_mask=0xFFFFFFFF)
+    with hj.HashJoin("radix", key_mask=0xFFFFFFFF, num_partitions=1 << bits, passes=passes) as h:
+        res = h.join(R, S)
+        assert (res.matches, res.checksum) == want
+
+
+@pytest.mark.parametrize("force_l2", [False, True])
+def test_radix_wide_keys_take_generic_kernels(hj, oracle, monkeypatch, force_l2):
+    """Keys above 2^32: rx_hist flags them, rx_join32 steps aside, rx_join_kernel / the L2 join do the work."""
+    if force_l2:
+        monkeypatch.setenv("HJ_FORCE_L2JOIN", "1")
+    n = 1 << 16
+    R = hj.generate_data("shuffle", n) + (np.uint64(1) << np.uint64(40))
+    S = np.concatenate([R[: n // 2], hj.generate_data("sorted", n // 2)])
+    want = oracle.true_join(R, S)
+    assert want[0] == n // 2
+    with hj.HashJoin("radix", num_partitions=1 << 6, passes=1) as h:
+        res = h.join(R, S)
+        assert (res.matches, res.checksum) == want
 
 
 def test_pro_build_only_checksum(hj, oracle):
