@@ -41,6 +41,8 @@ def parse_args():
     ap.add_argument("--passes", type=int, default=0)
     ap.add_argument("--algo", default="radix", choices=["radix", "atomic", "adaptive", "nocc"])
     ap.add_argument("--r-dist", default="shuffle", help="DataGen distribution of R at N=1 (host generated)")
+    ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
+                    help="N>1: exchange fused with radix pass 1 over peer memory, or partition + NCCL all-to-all")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--extras", action="store_true", help="also time configs[0] (atomic 16M uniform) etc.")
@@ -246,9 +248,25 @@ class Rank:
         self.s_desc = "counter-based FK (hj_generate kind 1, seed 54321: |S|/|R| permutations of 1..|R|)"
         self.hS = None
         self.gen_s = time.time() - t0
+        self.fused = G > 1 and args.exchange == "fused"
         if G > 1:
             cap_r = self.n + self.n // 32 + 65536
             cap_s = self.m + self.m // 32 + 65536
+        if self.fused:
+            # exchange == radix pass 1: every rank stores straight into the owners' pass-1 buffers
+            # (CUDA IPC over NVLink).  The fan-out is fixed so all ranks agree on b1.
+            bits, self.b1, _, passes = self.h.radix_plan(self.n)
+            assert passes == 2, "the fused exchange needs the 2-pass plan"
+            self.h.close()
+            self.h = hj.HashJoin(args.algo, device=self.local, num_partitions=1 << bits, passes=2)
+            self.f1 = 1 << self.b1
+            self.recvR, self.recvS = self.h.device_alloc(cap_r * 8), self.h.device_alloc(cap_s * 8)
+            self.cap = (cap_r, cap_s)
+            handles = self.exchange.exchange_ipc_handles((self.h.ipc_export(self.recvR), self.h.ipc_export(self.recvS)))
+            self.peerR = [self.recvR if g == self.rank else self.h.ipc_open(handles[g][0]) for g in range(G)]
+            self.peerS = [self.recvS if g == self.rank else self.h.ipc_open(handles[g][1]) for g in range(G)]
+            self.cnt = torch.zeros(2 * G * self.f1, dtype=torch.int64, device=dev)
+        elif G > 1:
             self.sendR = torch.empty(self.n, dtype=torch.int64, device=dev)
             self.sendS = torch.empty(self.m, dtype=torch.int64, device=dev)
             self.recvR = torch.empty(cap_r, dtype=torch.int64, device=dev)
@@ -284,6 +302,8 @@ class Rank:
             self.h.copy(self.dS.data_ptr(), self.hS.ctypes.data, self.m * 8)
         ex = self.exchange
         dom_bits = ex.domain_bits_for(self.domain)
+        if self.fused:
+            return self.step_fused(dom_bits)
         # 1. split both slices by destination GPU (high key bits of the key domain)
         self.h.exchange_partition(self.dR.data_ptr(), self.n, G, dom_bits, self.sendR.data_ptr(), self.offR.data_ptr())
         self.h.exchange_partition(self.dS.data_ptr(), self.m, G, dom_bits, self.sendS.data_ptr(), self.offS.data_ptr())
@@ -303,6 +323,42 @@ class Rank:
         self.last = res
         # 4. {matches, checksum} summed over ranks
         return ex.reduce_result(res.matches, res.checksum, "cuda")
+
+    def step_fused(self, dom_bits):
+        """Exchange fused with radix pass 1 (include/hj_b200.h, hj_peer_*)."""
+        torch, G, ex, gf = self.torch, self.world, self.exchange, self.world * self.f1
+        t = [time.perf_counter()]
+        # 1. per (owner GPU, low b1 bits) counts of the local slices; all ranks learn all counts
+        self.h.peer_hist(self.dR.data_ptr(), self.n, G, dom_bits, self.b1, self.cnt.data_ptr())
+        self.h.peer_hist(self.dS.data_ptr(), self.m, G, dom_bits, self.b1, self.cnt.data_ptr() + 8 * gf)
+        t.append(time.perf_counter())
+        allc = ex.gather_counts(self.cnt)
+        cur_r, recv_r = ex.peer_cursors(allc[:, :gf].contiguous(), self.rank, G, self.f1)
+        cur_s, recv_s = ex.peer_cursors(allc[:, gf:].contiguous(), self.rank, G, self.f1)
+        own = allc[self.rank, self.rank * self.f1:(self.rank + 1) * self.f1].sum() + \
+            allc[self.rank, gf + self.rank * self.f1:gf + (self.rank + 1) * self.f1].sum()
+        nr, ns, own = torch.stack([recv_r[self.rank], recv_s[self.rank], own]).tolist()  # one sync: cursors ready too
+        if nr > self.cap[0] or ns > self.cap[1]:
+            raise RuntimeError("exchange receive buffer too small")
+        t.append(time.perf_counter())
+        # 2. scatter into the owners' pass-1 buffers: plain stores over NVLink
+        self.h.peer_scatter(self.dR.data_ptr(), self.n, G, dom_bits, self.b1, self.peerR, cur_r.data_ptr())
+        self.h.peer_scatter(self.dS.data_ptr(), self.m, G, dom_bits, self.b1, self.peerS, cur_s.data_ptr())
+        t.append(time.perf_counter())
+        self.launches += 4
+        self.nvlink_bytes += 8 * (self.n + self.m - own)
+        # 3. everybody's stores have landed -> histogram + pass 2 + join of what arrived
+        self.dist.barrier()
+        torch.cuda.synchronize()
+        t.append(time.perf_counter())
+        res = self.h.join_pass1(self.recvR, nr, self.recvS, ns)
+        t.append(time.perf_counter())
+        self.launches += res.kernel_launches
+        self.last = res
+        out = ex.reduce_result(res.matches, res.checksum, "cuda")
+        t.append(time.perf_counter())
+        self.fused_ms = [round((b - a) * 1e3, 3) for a, b in zip(t, t[1:])]  # hist, counts, scatter, barrier, join, reduce
+        return out
 
     def barrier(self):
         if self.dist:
@@ -402,6 +458,11 @@ def run_b200(args):
         n_loc, m_loc = rk.n, rk.m  # per-GPU tuples (exact at N=1, +-0.1% after the exchange)
         sc_us = ph["us_scatter1"] + ph["us_scatter2"]
         sc_bytes = 16.0 * P * (n_loc + m_loc)  # every scatter launch reads 8 B and writes 8 B per tuple
+        if getattr(rk, "fused", False):
+            # pass 1 ran as the peer scatter (NVLink-bound, timed on the host as fused_ms[2]); the
+            # HBM roofline line is pass 2 alone
+            P = 1
+            sc_us, sc_bytes = ph["us_scatter2"], 16.0 * (n_loc + m_loc)
         roof = {"bound": "hbm", "kernel": f"rx_scatter_kernel<8> ({2 * P} launches/step: R and S x {P} passes)",
                 "achieved": round(sc_bytes / (sc_us * 1e-6) / 1e9, 1), "peak": peak, "unit": "GB/s",
                 "frac": round(sc_bytes / (sc_us * 1e-6) / 1e9 / peak, 4), "traffic": None,
@@ -424,13 +485,19 @@ def run_b200(args):
                                f"(BASELINE configs[2] at N=1; x8 = configs[4])",
                    "algo": args.algo, "radix_bits": int(last.radix_bits), "passes": int(last.passes),
                    "tuples_per_step": tuples, "l2": "inputs (9 GiB/GPU) larger than L2, no flush needed",
-                   "exchange": "none" if G == 1 else "range partition + torch.distributed all_to_all_single (NCCL)"},
+                   "exchange": "none" if G == 1 else ("fused with radix pass 1: stores into the owners' pass-1 buffers over NVLink (CUDA IPC)"
+                                                      if args.exchange == "fused" else
+                                                      "range partition + torch.distributed all_to_all_single (NCCL)")},
         "phases_us": {k: round(v, 1) for k, v in ph.items()},
         "roofline": roof, "gpu_launches": int(launches), "clocks": clocks, "e2e": e2e,
         "result": {"matches": want[0], "checksum": want[1], "verified_every_step": True},
     }
     if G > 1:
         line["nvlink_bytes_per_gpu_per_step"] = int(nvl)
+        if getattr(rk, "fused", False):
+            line["fused_exchange_ms_last_step"] = dict(zip(
+                ["peer_hist", "counts+cursors", "peer_scatter", "barrier", "hist+pass2+join", "allreduce"], rk.fused_ms))
+            line["nvlink_gbs_in_peer_scatter"] = round(nvl / (rk.fused_ms[2] * 1e-3) / 1e9, 1)
     if G == 1 and not args.no_cpu_baseline:
         v, desc, _ = cpu_reference_join(24, 27, 1, 1)
         line["cpu_baseline"] = dict(desc, value=round(v, 2), unit=UNIT)

@@ -162,6 +162,40 @@ class HashJoin:
         self._check(lib.hj_exchange_partition(self._h, int(d_in), int(n), n_dest, domain_bits, int(d_out),
                                               int(d_offsets)), "hj_exchange_partition")
 
+    # ---- exchange fused with radix pass 1 (multi-GPU; see include/hj_b200.h) ----
+    def radix_plan(self, n_build):
+        """(bits, b1, b2, passes) the radix join would use for a build side of n_build tuples."""
+        v = [C.c_uint32() for _ in range(4)]
+        self._check(lib.hj_radix_plan(self._h, int(n_build), *[C.byref(x) for x in v]), "hj_radix_plan")
+        return tuple(x.value for x in v)
+
+    def ipc_export(self, dptr):
+        buf = C.create_string_buffer(64)
+        self._check(lib.hj_ipc_export(self._h, int(dptr), buf), "hj_ipc_export")
+        return buf.raw
+
+    def ipc_open(self, handle):
+        p = C.c_void_p()
+        self._check(lib.hj_ipc_open(self._h, C.create_string_buffer(handle, 64), C.byref(p)), "hj_ipc_open")
+        return p.value
+
+    def ipc_close(self, dptr):
+        self._check(lib.hj_ipc_close(self._h, dptr), "hj_ipc_close")
+
+    def peer_hist(self, d_in, n, n_dest, domain_bits, b1, d_counts):
+        self._check(lib.hj_peer_hist(self._h, int(d_in), int(n), n_dest, domain_bits, b1, int(d_counts)),
+                    "hj_peer_hist")
+
+    def peer_scatter(self, d_in, n, n_dest, domain_bits, b1, peer_bufs, d_cursors):
+        arr = (C.c_uint64 * n_dest)(*[int(p) for p in peer_bufs])
+        self._check(lib.hj_peer_scatter(self._h, int(d_in), int(n), n_dest, domain_bits, b1, arr, int(d_cursors)),
+                    "hj_peer_scatter")
+
+    def join_pass1(self, d_R1, n, d_S1, m):
+        res = hj_result()
+        self._check(lib.hj_join_pass1(self._h, int(d_R1), int(n), int(d_S1), int(m), C.byref(res)), "hj_join_pass1")
+        return res
+
     def generate(self, kind, first, count, domain, seed, d_out):
         self._check(lib.hj_generate(self._h, kind, int(first), int(count), int(domain), int(seed), int(d_out)),
                     "hj_generate")

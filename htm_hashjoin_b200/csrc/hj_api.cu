@@ -35,7 +35,7 @@ struct DevBuf {
 };
 
 struct RelBufs {  // radix-side buffers for one relation
-  DevBuf tmp, out, ghist, offsets, cursors, poff, pcur, ptiles, one;
+  DevBuf tmp, out, ghist, offsets, cursors, poff, pcur, ptiles, one, pend;
 };
 
 }  // namespace
@@ -55,11 +55,13 @@ struct hj_handle {
   DevBuf table, ovf_table, ovf_list;
   u64 slots = 0, mask = 0;
   bool built = false;
+  bool no_optimistic = false;  // a histogram-free attempt overflowed on this handle: stay on the exact path
   // staging for host inputs
   DevBuf stageR, stageS;
   // radix
   RelBufs rb[2];
   DevBuf flush;
+  DevBuf peer_ptrs;  // device copy of the peers' pass-1 buffer pointers (fused exchange)
   u32 launches = 0;
   char err[256];
 };
@@ -405,12 +407,24 @@ int plan_radix(hj_handle* h, u64 n, RadixPlan* pl) {
   return HJ_OK;
 }
 
-int ensure_rel(hj_handle* h, RelBufs& rb, u64 n, const RadixPlan& pl) {
+// region capacity of the histogram-free layout for a relation of n tuples in 2^bits partitions:
+// mean + 8 sigma of a random split + 64, even
+u64 opt_region_cap(u64 n, u32 bits) {
+  const u64 avg = (n >> bits) + 1;
+  u64 r = 1;
+  while (r * r < avg * 64) r++;  // 8 * sqrt(avg)
+  return (avg + r + 64 + 1) & ~1ull;
+}
+
+int ensure_rel(hj_handle* h, RelBufs& rb, u64 n, const RadixPlan& pl, bool pre1 = false, bool opt = false) {
   int rc;
   u64 nb = 1ull << pl.bits;
   u64 np = 1ull << pl.b1;
-  if ((rc = ensure(h, rb.out, n + 2))) return rc;
-  if (pl.passes == 2 && (rc = ensure(h, rb.tmp, n + 2))) return rc;
+  // histogram-free layout: 2^bits regions + one scatter tile of scratch for diverted claims
+  const u64 elems = opt ? nb * opt_region_cap(n, pl.bits) + kScThreads * 8 + 2 : n + 2;
+  if ((rc = ensure(h, rb.out, elems))) return rc;
+  if (pl.passes == 2 && !pre1 && (rc = ensure(h, rb.tmp, elems))) return rc;
+  if (opt && (rc = ensure(h, rb.pend, np + 2))) return rc;
   if ((rc = ensure(h, rb.ghist, nb))) return rc;
   if ((rc = ensure(h, rb.offsets, nb + 1))) return rc;
   if ((rc = ensure(h, rb.cursors, nb))) return rc;
@@ -448,7 +462,7 @@ int launch_scatter_tm(hj_handle* h, const u64* in, u64* out, const Digit& dg, u3
   CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int grid = grid_for(h, (const void*)k, kScThreads, smem);
   if ((u64)grid > max_tiles) grid = (int)(max_tiles ? max_tiles : 1);
-  k<<<grid, kScThreads, smem, h->stream>>>(in, out, dg, F, nparent, poff, ptiles, cursors);
+  k<<<grid, kScThreads, smem, h->stream>>>(in, out, dg, F, nparent, poff, ptiles, cursors, nullptr, ScOpt{});
   h->launches++;
   CK(cudaGetLastError());
   return HJ_OK;
@@ -465,8 +479,10 @@ int launch_scatter_t(hj_handle* h, const u64* in, u64* out, const Digit& dg, u32
 
 // Partition `in` (device, n tuples) by pl into rb.out; rb.offsets gets 2^bits+1 offsets.
 // evb = first of this relation's five phase events (or -1: untimed).
+// pre1: `in` already IS the pass-1 output (partitioned by the low b1 bits, partition-major, no
+// gaps -- written by the peers' fused exchange scatter): histogram it, skip pass 1, run pass 2 on it.
 int radix_partition_rel(hj_handle* h, const u64* in, u64 n, RelBufs& rb, const RadixPlan& pl, int evb,
-                        u64* max_bin = nullptr) {
+                        u64* max_bin = nullptr, bool pre1 = false) {
   const u32 nb = 1u << pl.bits;
   const u32 F1 = 1u << pl.b1, F2 = 1u << pl.b2;
   const u32 tile = kScThreads * pl.tile_ipt;
@@ -503,22 +519,71 @@ int radix_partition_rel(hj_handle* h, const u64* in, u64 n, RelBufs& rb, const R
     Digit d1;
     memset(&d1, 0, sizeof(d1));
     d1.key_mask = h->cfg.key_mask; d1.mode = 0; d1.shift = 0; d1.bits = pl.b1;
-    if ((rc = launch_scatter_t<8>(h, in, rb.tmp.p, d1, F1, 1, rb.one.p, rb.one.p + 2, rb.pcur.p, max_tiles1)))
+    if (!pre1 &&
+        (rc = launch_scatter_t<8>(h, in, rb.tmp.p, d1, F1, 1, rb.one.p, rb.one.p + 2, rb.pcur.p, max_tiles1)))
       return rc;
     if (evb >= 0) mark(h, evb + 3);
     // pass 2: every pass-1 partition by the next b2 bits into out (radix_cluster, :402-440)
     Digit d2;
     memset(&d2, 0, sizeof(d2));
     d2.key_mask = h->cfg.key_mask; d2.mode = 0; d2.shift = pl.b1; d2.bits = pl.b2;
-    if ((rc = launch_scatter_t<8>(h, rb.tmp.p, rb.out.p, d2, F2, F1, rb.poff.p, rb.ptiles.p, rb.cursors.p,
-                                  max_tiles1 + F1)))
+    if ((rc = launch_scatter_t<8>(h, pre1 ? in : rb.tmp.p, rb.out.p, d2, F2, F1, rb.poff.p, rb.ptiles.p,
+                                  rb.cursors.p, max_tiles1 + F1)))
       return rc;
     if (evb >= 0) mark(h, evb + 4);
   }
   return HJ_OK;
 }
 
-int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS, u64 m, bool pendS, hj_result* res) {
+// Histogram-free 2-pass partitioning (ScOpt in rx_kernels.cuh): both passes write into
+// fixed-capacity regions, rb.cursors ends up holding the fill level of every final region.
+int radix_partition_rel_opt(hj_handle* h, const u64* in, u64 n, RelBufs& rb, const RadixPlan& pl, int evb) {
+  const u32 nb = 1u << pl.bits, F1 = 1u << pl.b1, F2 = 1u << pl.b2;
+  const u32 tile = kScThreads * pl.tile_ipt;
+  const u64 C2 = opt_region_cap(n, pl.bits), C1 = C2 * F2;
+  const u64 ntiles = (n + tile - 1) / tile;
+  if (evb >= 0) { mark(h, evb); mark(h, evb + 1); }
+  rx_opt_init_kernel<<<(nb + 255) / 256, 256, 0, h->stream>>>(rb.pcur.p, F1, C1, rb.cursors.p, nb, C2);
+  const u64 one[4] = {0, n, 0, ntiles};  // pass 1: one parent [0, n) of ntiles tiles
+  CK(cudaMemcpyAsync(rb.one.p, one, sizeof(one), cudaMemcpyHostToDevice, h->stream));
+  h->launches++;
+  if (evb >= 0) mark(h, evb + 2);
+  auto k = rx_scatter_kernel<8, 0, false, 1>;
+  auto k2 = rx_scatter_kernel<8, 0, false, 2>;
+  Digit d1, d2;
+  memset(&d1, 0, sizeof(d1));
+  d1.key_mask = h->cfg.key_mask; d1.mode = 0; d1.shift = 0; d1.bits = pl.b1;
+  d2 = d1; d2.shift = pl.b1; d2.bits = pl.b2;
+  {
+    size_t smem = (size_t)tile * 8 + (size_t)F1 * 16;
+    CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int grid = grid_for(h, (const void*)k, kScThreads, smem);
+    if ((u64)grid > ntiles) grid = (int)(ntiles ? ntiles : 1);
+    ScOpt o{rb.one.p + 1, C1, (u64)F1 * C1, h->ctr};
+    k<<<grid, kScThreads, smem, h->stream>>>(in, rb.tmp.p, d1, F1, 1, rb.one.p, rb.one.p + 2, rb.pcur.p, nullptr, o);
+    h->launches++;
+    CK(cudaGetLastError());
+  }
+  if (evb >= 0) mark(h, evb + 3);
+  rx_opt_parents_kernel<<<1, 1024, 0, h->stream>>>(rb.pcur.p, F1, C1, tile, rb.poff.p, rb.pend.p, rb.ptiles.p);
+  h->launches++;
+  {
+    size_t smem = (size_t)tile * 8 + (size_t)F2 * 16;
+    CK(cudaFuncSetAttribute(k2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int grid = grid_for(h, (const void*)k2, kScThreads, smem);
+    if ((u64)grid > ntiles + F1) grid = (int)(ntiles + F1);
+    ScOpt o{rb.pend.p, C2, (u64)nb * C2, h->ctr};
+    k2<<<grid, kScThreads, smem, h->stream>>>(rb.tmp.p, rb.out.p, d2, F2, F1, rb.poff.p, rb.ptiles.p, rb.cursors.p,
+                                             nullptr, o);
+    h->launches++;
+    CK(cudaGetLastError());
+  }
+  if (evb >= 0) mark(h, evb + 4);
+  return HJ_OK;
+}
+
+int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS, u64 m, bool pendS, hj_result* res,
+                   bool pre1 = false, bool force_exact = false) {
   RadixPlan pl;
   int rc;
   if ((rc = plan_radix(h, n, &pl))) {
@@ -526,16 +591,7 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
              kMaxTotalBits, kMaxBitsPerPass);
     return rc;
   }
-  if ((rc = ensure_rel(h, h->rb[0], n, pl))) return rc;
-  if (dS && (rc = ensure_rel(h, h->rb[1], m, pl))) return rc;
-  CK(cudaMemsetAsync(h->ctr, 0, C_COUNT * sizeof(u64), h->stream));
-  if ((rc = wait_staged(h, E_CPR, pendR))) return rc;
-  if ((rc = radix_partition_rel(h, dR, n, h->rb[0], pl, E_RX, h->ctr + C_MAX_PART))) return rc;
-  if (dS) {
-    if ((rc = wait_staged(h, E_CPS, pendS))) return rc;
-    if ((rc = radix_partition_rel(h, dS, m, h->rb[1], pl, E_RX + 5))) return rc;
-  }
-  mark(h, E_JOIN0);
+  if (pre1 && pl.passes != 2) return HJ_EINVAL;
   // Which join: shared memory while an R partition (plus 8 sigma of a random split) fits the
   // largest table one CTA can hold, else the L2-resident partition-local table (rx_joinl2.cuh).
   const u32 nparts = 1u << pl.bits;
@@ -543,6 +599,25 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
   u64 need = per + 64;
   for (u64 r = 1; r * r < per * 64; r++) need = per + 64 + r;  // + 8*sqrt(per)
   const bool use_l2 = dS && (getenv("HJ_FORCE_L2JOIN") || need > 21000) && !getenv("HJ_NO_L2JOIN");
+  // Histogram-free partitioning (ScOpt, rx_kernels.cuh) for the 2-pass shared-memory join; the
+  // exact, histogram-based layout everywhere else and after an overflow on this handle.
+  const bool opt = dS && !pre1 && !use_l2 && pl.passes == 2 && !h->no_optimistic && !force_exact &&
+                   !getenv("HJ_NO_OPTIMISTIC");
+  const u64 capR = opt ? opt_region_cap(n, pl.bits) : 0, capS = opt ? opt_region_cap(m, pl.bits) : 0;
+  if ((rc = ensure_rel(h, h->rb[0], n, pl, pre1, opt))) return rc;
+  if (dS && (rc = ensure_rel(h, h->rb[1], m, pl, pre1, opt))) return rc;
+  CK(cudaMemsetAsync(h->ctr, 0, C_COUNT * sizeof(u64), h->stream));
+  if ((rc = wait_staged(h, E_CPR, pendR))) return rc;
+  if (opt) rc = radix_partition_rel_opt(h, dR, n, h->rb[0], pl, E_RX);
+  else rc = radix_partition_rel(h, dR, n, h->rb[0], pl, E_RX, h->ctr + C_MAX_PART, pre1);
+  if (rc) return rc;
+  if (dS) {
+    if ((rc = wait_staged(h, E_CPS, pendS))) return rc;
+    if (opt) rc = radix_partition_rel_opt(h, dS, m, h->rb[1], pl, E_RX + 5);
+    else rc = radix_partition_rel(h, dS, m, h->rb[1], pl, E_RX + 5, nullptr, pre1);
+    if (rc) return rc;
+  }
+  mark(h, E_JOIN0);
   if (use_l2) {
     Digit full;
     memset(&full, 0, sizeof(full));
@@ -603,10 +678,13 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
     CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int grid = grid_for(h, k, threads, smem);
     if ((u32)grid > nparts) grid = (int)nparts;
-    const u64 *aR = h->rb[0].out.p, *aoR = h->rb[0].offsets.p, *aS = h->rb[1].out.p, *aoS = h->rb[1].offsets.p;
+    // histogram-free layout: the partitions' ends are the scatter's final cursors
+    const u64 *aR = h->rb[0].out.p, *aoR = opt ? h->rb[0].cursors.p : h->rb[0].offsets.p, *aS = h->rb[1].out.p,
+              *aoS = opt ? h->rb[1].cursors.p : h->rb[1].offsets.p;
     u32 a_np = nparts, a_bits = pl.bits;
     u64* a_ctr = h->ctr;
-    void* args[] = {&aR, &aoR, &aS, &aoS, &a_np, &a_bits, &nbuckets, &a_ctr};
+    u64 a_capR = capR, a_capS = capS;
+    void* args[] = {&aR, &aoR, &aS, &aoS, &a_np, &a_bits, &nbuckets, &a_ctr, &a_capR, &a_capS};
     CK(cudaLaunchKernel(k, dim3(grid), dim3(threads), args, smem, h->stream));
     h->launches++;
   }
@@ -618,15 +696,21 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
     CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int grid = grid_for(h, (const void*)k, kJoinThreads, smem);
     if ((u32)grid > nparts) grid = (int)nparts;
-    k<<<grid, kJoinThreads, smem, h->stream>>>(h->rb[0].out.p, h->rb[0].offsets.p, dS ? h->rb[1].out.p : nullptr,
-                                               dS ? h->rb[1].offsets.p : nullptr, nparts, pl.bits, pl.slots,
-                                               h->cfg.key_mask, h->ctr, try32 ? 1 : 0);
+    k<<<grid, kJoinThreads, smem, h->stream>>>(h->rb[0].out.p, opt ? h->rb[0].cursors.p : h->rb[0].offsets.p,
+                                               dS ? h->rb[1].out.p : nullptr,
+                                               dS ? (opt ? h->rb[1].cursors.p : h->rb[1].offsets.p) : nullptr, nparts,
+                                               pl.bits, pl.slots, h->cfg.key_mask, h->ctr, try32 ? 1 : 0, capR, capS);
     h->launches++;
     CK(cudaGetLastError());
   }
   mark(h, E_JOIN);
   mark(h, E_END);
   if ((rc = fetch_counters(h))) return rc;
+  if (opt && h->h_ctr[C_OPT_OVF]) {
+    // a region overflowed (skewed partition sizes): nothing was lost -- redo on the exact path
+    h->no_optimistic = true;
+    return run_radix_join(h, dR, n, false, dS, m, false, res, pre1, true);
+  }
   if (res) {
     fill_common(h, res);
     res->path_taken = HJ_PATH_RADIX;
@@ -749,11 +833,11 @@ void hj_destroy(hj_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
   if (h->stream) cudaStreamSynchronize(h->stream);
-  DevBuf* bufs[] = {&h->table, &h->ovf_table, &h->ovf_list, &h->stageR, &h->stageS, &h->flush};
+  DevBuf* bufs[] = {&h->table, &h->ovf_table, &h->ovf_list, &h->stageR, &h->stageS, &h->flush, &h->peer_ptrs};
   for (DevBuf* b : bufs)
     if (b->p) cudaFree(b->p);
   for (RelBufs& rb : h->rb) {
-    DevBuf* rbufs[] = {&rb.tmp, &rb.out, &rb.ghist, &rb.offsets, &rb.cursors, &rb.poff, &rb.pcur, &rb.ptiles, &rb.one};
+    DevBuf* rbufs[] = {&rb.tmp, &rb.out, &rb.ghist, &rb.offsets, &rb.cursors, &rb.poff, &rb.pcur, &rb.ptiles, &rb.one, &rb.pend};
     for (DevBuf* b : rbufs)
       if (b->p) cudaFree(b->p);
   }
@@ -1033,6 +1117,112 @@ int hj_exchange_partition(hj_handle* h, const uint64_t* in, uint64_t n, uint32_t
     return rc;
   CK(cudaStreamSynchronize(h->stream));
   return HJ_OK;
+}
+
+// ---- exchange fused with radix pass 1 (multi-GPU) ------------------------------
+// Each rank scatters its slice by (owner GPU of the key range, low b1 bits) straight into the
+// owners' pass-1 buffers over NVLink (peer memory mapped through CUDA IPC), so the all-to-all IS
+// radix pass 1: no send buffer, no separate collective, no extra pass over the data.
+
+int hj_radix_plan(hj_handle* h, uint64_t n_build, uint32_t* bits, uint32_t* b1, uint32_t* b2, uint32_t* passes) {
+  if (!h) return HJ_EINVAL;
+  RadixPlan pl;
+  int rc = plan_radix(h, n_build, &pl);
+  if (rc) return rc;
+  if (bits) *bits = pl.bits;
+  if (b1) *b1 = pl.b1;
+  if (b2) *b2 = pl.b2;
+  if (passes) *passes = pl.passes;
+  return HJ_OK;
+}
+
+int hj_ipc_export(hj_handle* h, const void* dptr, void* handle64) {
+  if (!h || !dptr || !handle64) return HJ_EINVAL;
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "handle travels as 64 bytes");
+  CK(cudaSetDevice(h->device));
+  CK(cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(handle64), const_cast<void*>(dptr)));
+  return HJ_OK;
+}
+int hj_ipc_open(hj_handle* h, const void* handle64, void** dptr) {
+  if (!h || !handle64 || !dptr) return HJ_EINVAL;
+  CK(cudaSetDevice(h->device));
+  cudaIpcMemHandle_t hd;
+  memcpy(&hd, handle64, sizeof(hd));
+  CK(cudaIpcOpenMemHandle(dptr, hd, cudaIpcMemLazyEnablePeerAccess));
+  return HJ_OK;
+}
+int hj_ipc_close(hj_handle* h, void* dptr) {
+  if (!h || !dptr) return HJ_EINVAL;
+  CK(cudaSetDevice(h->device));
+  CK(cudaIpcCloseMemHandle(dptr));
+  return HJ_OK;
+}
+
+static int peer_digit(hj_handle* h, uint32_t n_dest, uint32_t domain_bits, uint32_t b1, Digit* dg) {
+  if (n_dest < 1 || n_dest > (uint32_t)kScMaxPeers || domain_bits > 62 || b1 > 8 || (n_dest << b1) > 4096) return HJ_EINVAL;
+  memset(dg, 0, sizeof(*dg));
+  dg->key_mask = h->cfg.key_mask;
+  dg->mode = 3; dg->ndest = n_dest; dg->domain_bits = domain_bits; dg->b1 = b1;
+  return HJ_OK;
+}
+
+// counts[(dest << b1) | low bits] += tuples of `in`; counts is a DEVICE array of n_dest << b1 u64, zeroed here.
+int hj_peer_hist(hj_handle* h, const uint64_t* in, uint64_t n, uint32_t n_dest, uint32_t domain_bits, uint32_t b1,
+                 uint64_t* counts) {
+  if (!h || !in || !counts || !is_device_ptr(in) || !is_device_ptr(counts)) return HJ_EINVAL;
+  Digit dg;
+  int rc = peer_digit(h, n_dest, domain_bits, b1, &dg);
+  if (rc) return rc;
+  CK(cudaSetDevice(h->device));
+  const u32 F = n_dest << b1;
+  CK(cudaMemsetAsync(counts, 0, F * sizeof(u64), h->stream));
+  if ((rc = launch_hist(h, (const u64*)in, n, dg, F, (u64*)counts))) return rc;
+  CK(cudaStreamSynchronize(h->stream));
+  return HJ_OK;
+}
+
+// peer_bufs: HOST array of n_dest device pointers (entry `self` = the local buffer, the others
+// opened with hj_ipc_open); cursors: DEVICE array of n_dest << b1 u64, on entry the first element
+// of this rank's exclusive range for every (dest, low bits), advanced by the claims.
+int hj_peer_scatter(hj_handle* h, const uint64_t* in, uint64_t n, uint32_t n_dest, uint32_t domain_bits, uint32_t b1,
+                    uint64_t* const* peer_bufs, uint64_t* cursors) {
+  if (!h || !in || !peer_bufs || !cursors || !is_device_ptr(in) || !is_device_ptr(cursors)) return HJ_EINVAL;
+  Digit dg;
+  int rc = peer_digit(h, n_dest, domain_bits, b1, &dg);
+  if (rc) return rc;
+  CK(cudaSetDevice(h->device));
+  RelBufs& rb = h->rb[0];
+  if ((rc = ensure(h, rb.one, 4))) return rc;
+  if ((rc = ensure(h, h->peer_ptrs, kScMaxPeers))) return rc;
+  const u32 F = n_dest << b1;
+  const u32 tile = kScThreads * 8;
+  const u64 ntiles = (n + tile - 1) / tile;
+  const u64 one[4] = {0, n, 0, ntiles};  // the one-parent view: offsets {0, n}, tiles {0, ntiles}
+  CK(cudaMemcpyAsync(rb.one.p, one, sizeof(one), cudaMemcpyHostToDevice, h->stream));
+  CK(cudaMemcpyAsync(h->peer_ptrs.p, peer_bufs, n_dest * sizeof(u64*), cudaMemcpyHostToDevice, h->stream));
+  auto k = rx_scatter_kernel<8, 2, true>;
+  size_t smem = (size_t)tile * 8 + (size_t)F * 16;
+  CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int grid = grid_for(h, (const void*)k, kScThreads, smem);
+  if (getenv("HJ_PEER_CTAS")) grid = h->sm_count * atoi(getenv("HJ_PEER_CTAS"));
+  if ((u64)grid > ntiles) grid = (int)(ntiles ? ntiles : 1);
+  k<<<grid, kScThreads, smem, h->stream>>>((const u64*)in, nullptr, dg, F, 1, rb.one.p, rb.one.p + 2, (u64*)cursors,
+                                           reinterpret_cast<u64* const*>(h->peer_ptrs.p), ScOpt{});
+  h->launches++;
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(h->stream));
+  return HJ_OK;
+}
+
+// Join of relations that are already pass-1 partitioned (by the low b1 bits of hj_radix_plan,
+// partition-major, contiguous): histogram, pass 2, per-partition join.  Device pointers only.
+int hj_join_pass1(hj_handle* h, const uint64_t* R1, uint64_t n, const uint64_t* S1, uint64_t m, hj_result* res) {
+  if (!h || !R1 || !S1 || !is_device_ptr(R1) || !is_device_ptr(S1)) return HJ_EINVAL;
+  CK(cudaSetDevice(h->device));
+  if (res) memset(res, 0, sizeof(*res));
+  reset_events(h);
+  mark(h, E_T0);
+  return run_radix_join(h, (const u64*)R1, n, false, (const u64*)S1, m, false, res, true);
 }
 
 int hj_generate(hj_handle* h, int kind, uint64_t first, uint64_t count, uint64_t domain, uint64_t seed,

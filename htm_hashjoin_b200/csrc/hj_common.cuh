@@ -27,6 +27,7 @@ enum Counter {
   C_SPAN,            // sum over sampled CTA chunks of (max home - min home + 1), in slots
   C_CHUNKS,          // number of sampled CTA chunks
   C_KEY_HI,          // OR of the key bits above bit 31 over every tuple rx_hist saw (0: rx_join32 applies)
+  C_OPT_OVF,         // a region of the histogram-free layout overflowed: redo on the exact path
   C_TILE0, C_TILE1,  // tile tickets of the L2 join kernels (rx_joinl2.cuh)
   C_COUNT = 24
 };

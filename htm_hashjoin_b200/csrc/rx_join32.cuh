@@ -180,7 +180,8 @@ __device__ __noinline__ u64 j32_probe_multi(u32 base, u32 nbuckets, u32 k) {
 template <int THREADS, int BATCH, int MINB, int W>
 __global__ void __launch_bounds__(THREADS, MINB)
 rx_join32_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const u64* __restrict__ Sp,
-                 const u64* __restrict__ offS, u32 nparts, u32 radix_bits, u32 nbuckets, u64* __restrict__ ctr) {
+                 const u64* __restrict__ offS, u32 nparts, u32 radix_bits, u32 nbuckets, u64* __restrict__ ctr,
+                 u64 capR, u64 capS) {
   static_assert(BATCH % 2 == 0, "BATCH tuples = BATCH/2 16-byte loads");
   static_assert(W == 2 || W == 4, "bucket of 2 or 4 keys");
   if (ctr[C_KEY_HI] != 0ull) return;  // keys wider than 32 bits: rx_join_kernel handles this join
@@ -205,8 +206,12 @@ rx_join32_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const
   u32 pay_sum = 0;
 
   for (u32 p = blockIdx.x; p < nparts; p += gridDim.x) {
-    const u64 r0 = offR[p], r1 = offR[p + 1];
-    const u64 s0 = offS[p], s1 = offS[p + 1];
+    // exact layout: partition p = [off[p], off[p+1]); histogram-free layout (cap != 0, see ScOpt
+    // in rx_kernels.cuh): [p*cap, min(off[p], (p+1)*cap)) with off = the scatter's final cursors
+    const u64 r0 = capR ? p * capR : offR[p];
+    const u64 r1 = capR ? (offR[p] < r0 + capR ? offR[p] : r0 + capR) : offR[p + 1];
+    const u64 s0 = capS ? p * capS : offS[p];
+    const u64 s1 = capS ? (offS[p] < s0 + capS ? offS[p] : s0 + capS) : offS[p + 1];
     const u64 nr = r1 - r0;
     maxpart = nr > maxpart ? nr : maxpart;
     if (nr == 0 || s1 == s0) continue;

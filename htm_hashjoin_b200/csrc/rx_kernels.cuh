@@ -31,6 +31,7 @@ namespace hj {
 //           (pass 1 = low b1 bits, pass 2 = next b2 bits: prj_params.h:76-78,
 //            parallel_radix_join.c:870-871,960-961)
 //   mode 2: range split for the G-way exchange: min(G-1, ((key-1)*G) >> domain_bits)
+//   mode 3: exchange fused with radix pass 1: (dest << b1) | (key & (F1-1)), dest as in mode 2
 struct Digit {
   u32 mode, shift, bits, b1, b2, ndest, domain_bits, pad;
   u64 key_mask;
@@ -40,7 +41,9 @@ __device__ __forceinline__ u32 digit_of(const Digit& d, u64 v) {
   if (d.mode == 0) return (u32)((key >> d.shift) & ((1u << d.bits) - 1u));
   if (d.mode == 1) return (u32)(((key & ((1u << d.b1) - 1u)) << d.b2) | ((key >> d.b1) & ((1u << d.b2) - 1u)));
   u64 q = ((key - 1) * (u64)d.ndest) >> d.domain_bits;
-  return (u32)(q < d.ndest ? q : d.ndest - 1);
+  const u32 dest = (u32)(q < d.ndest ? q : d.ndest - 1);
+  if (d.mode == 2) return dest;
+  return (dest << d.b1) | ((u32)key & ((1u << d.b1) - 1u));
 }
 
 // ---- histogram ---------------------------------------------------------------
@@ -206,11 +209,36 @@ __device__ __forceinline__ u32 sc_digit(const Digit& dg, u32 fmask, u64 v) {
   return digit_of(dg, v);
 }
 
-template <int IPT, int MODE>
+// PEER: the run of digit d goes to peer_out[d >> dg.b1] (the pass-1 buffer of the GPU that owns
+// the key range, mapped through CUDA IPC: plain stores over NVLink) instead of `out`; cursors[d]
+// then holds this rank's own, exclusive range inside that buffer, so the claims stay local atomics.
+constexpr int kScMaxPeers = 16;
+
+// OPT ("optimistic", histogram-free partitioning): the output is not laid out from exact
+// histogram offsets but in fixed-capacity regions, region q = [q*region_cap, (q+1)*region_cap)
+// with q = parent*F + digit, claimed from cursors[q] (initialised to q*region_cap); the regions'
+// fill levels (the cursors) are what the next stage reads.  A claim that would run over its
+// region is diverted to a scratch area at trash_off and sets ctr[C_OPT_OVF]: the host then redoes
+// the join on the exact, histogram-based path.  Saves the full read of both relations that
+// rx_hist costs (8 of the 48 B/tuple the 2-pass join moves).  Parents are [parent_off[p],
+// parent_end[p]) (gaps between regions), and since rx_hist is gone the key-width flag
+// ctr[C_KEY_HI] is gathered here.
+struct ScOpt {
+  const u64* parent_end;
+  u64 region_cap, trash_off;
+  u64* ctr;
+};
+
+// OPT: 0 = exact layout, 1 = histogram-free + key-width flag (pass 1), 2 = histogram-free (pass 2)
+template <int IPT, int MODE, bool PEER = false, int OPT = 0>
 __global__ void __launch_bounds__(kScThreads, 3)
 rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u32 F, u32 nparent,
                   const u64* __restrict__ parent_off, const u64* __restrict__ parent_tiles,
-                  u64* __restrict__ cursors) {
+                  u64* __restrict__ cursors, u64* const* __restrict__ peer_out, ScOpt opt) {
+  __shared__ u64* s_peer[PEER ? kScMaxPeers : 1];
+  if (PEER && threadIdx.x < dg.ndest) s_peer[threadIdx.x] = peer_out[threadIdx.x];
+  __shared__ u64 s_pend[OPT ? kScParentCache + 1 : 1];
+  u32 key_hi = 0;
   constexpr int TILE = kScThreads * IPT;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   u64* tile = reinterpret_cast<u64*>(smem_raw);
@@ -232,25 +260,27 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
       s_poff[i] = parent_off[i];
     }
   }
+  if (OPT)
+    for (u32 i = tid; i < nparent; i += kScThreads) s_pend[i] = opt.parent_end[i];
   for (u32 i = tid; i < F; i += kScThreads) hist[i] = 0;
   __syncthreads();
   const u64* pt = cached ? s_ptiles : parent_tiles;
   const u64* po = cached ? s_poff : parent_off;
-  const u64 total_tiles = pt[nparent];
+  const u32 total_tiles = (u32)pt[nparent];  // < 2^32 tiles of 4096 tuples
   const u32 per_thread = (F + kScThreads - 1) / kScThreads;  // bins each thread scans
 
   // Locate tile t (parent, start, length) and issue its loads.  Called for the first tile
   // and then, for tile k+1, right after tile k has been moved to shared memory: the loads
   // fly while tile k is flushed, so the read stream never drains.
   u64 v[IPT];
-  auto load_tile = [&](u64 t, u32& p_out, u32& cnt_out) {
+  auto load_tile = [&](u32 t, u32& p_out, u32& cnt_out) {
     u32 lo = 0, hi = nparent;  // last p with parent_tiles[p] <= t
     while (hi - lo > 1) {
       const u32 mid = (lo + hi) >> 1;
       if (pt[mid] <= t) lo = mid; else hi = mid;
     }
     const u64 begin = po[lo] + (t - pt[lo]) * TILE;
-    const u64 pend = po[lo + 1];
+    const u64 pend = OPT ? s_pend[lo] : po[lo + 1];  // OPT: nparent <= kScParentCache (host)
     const u32 cnt = (u32)(pend - begin < (u64)TILE ? pend - begin : (u64)TILE);
     const u64* src = in + begin;
     if (cnt == TILE && (begin & 1ull) == 0) {  // full, 16 B aligned tile: no per-element checks
@@ -272,7 +302,7 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
     cnt_out = cnt;
   };
 
-  u64 t = blockIdx.x;
+  u32 t = blockIdx.x;
   u32 p = 0, cnt = 0;
   if (t < total_tiles) load_tile(t, p, cnt);
   while (t < total_tiles) {
@@ -282,6 +312,7 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
       if (v[j] != 0ull) {
         const u32 d = sc_digit<MODE>(dg, fmask, v[j]);
         dr[j] = (d << 16) | atomicAdd(hist + d, 1u);
+        if (OPT == 1) key_hi |= (u32)(v[j] >> 32);
       }
     }
     __syncthreads();  // also: every thread has finished flushing the previous tile
@@ -320,7 +351,15 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
           const u32 c = hist[b];
           hist[b] = 0;  // ready for the next tile (nobody reads hist after this scan)
           lbase[b] = run;
-          if (c) gdelta[b] = atomicAdd(cursors + (u64)p * F + b, (u64)c) - run;
+          if (c) {
+            const u64 q = (u64)p * F + b;
+            u64 g = atomicAdd(cursors + q, (u64)c);
+            if (OPT && g + c > (q + 1) * opt.region_cap) {  // region full: divert, flag, host falls back
+              g = opt.trash_off;
+              opt.ctr[C_OPT_OVF] = 1ull;
+            }
+            gdelta[b] = g - run;
+          }
           run += c;
         }
       }
@@ -343,16 +382,53 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
       for (int j = 0; j < IPT; j++) {
         const u32 i = j * kScThreads + tid;
         const u64 x = tile[i];
-        out[gdelta[sc_digit<MODE>(dg, fmask, x)] + i] = x;
+        const u32 d = sc_digit<MODE>(dg, fmask, x);
+        u64* o = PEER ? s_peer[d >> dg.b1] : out;
+        o[gdelta[d] + i] = x;
       }
     } else {
       for (u32 i = tid; i < cnt_cur; i += kScThreads) {
         const u64 x = tile[i];
-        out[gdelta[sc_digit<MODE>(dg, fmask, x)] + i] = x;
+        const u32 d = sc_digit<MODE>(dg, fmask, x);
+        u64* o = PEER ? s_peer[d >> dg.b1] : out;
+        o[gdelta[d] + i] = x;
       }
     }
     // no barrier here: the one after the next tile's ranking orders this flush before the
     // next writes to lbase/gdelta/tile
+  }
+  if (OPT == 1) {
+    key_hi = __reduce_or_sync(0xffffffffu, key_hi) & (u32)(dg.key_mask >> 32);
+    if (key_hi && lane_id() == 0) atomicOr(opt.ctr + C_KEY_HI, (u64)key_hi);
+  }
+}
+
+// ---- optimistic (histogram-free) layout helpers -----------------------------------------------
+// cursors[q] = q * cap for q < count
+__global__ void __launch_bounds__(256) rx_opt_init_kernel(u64* __restrict__ a, u32 na, u64 capa, u64* __restrict__ b,
+                                                           u32 nb, u64 capb) {
+  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < na) a[i] = (u64)i * capa;
+  if (i < nb) b[i] = (u64)i * capb;
+}
+// after pass 1: parent p = [p*cap, cur[p]); tiles[p] = scatter tiles before parent p (one CTA)
+__global__ void __launch_bounds__(1024) rx_opt_parents_kernel(const u64* __restrict__ cur, u32 nparent, u64 cap,
+                                                               u32 tile, u64* __restrict__ poff,
+                                                               u64* __restrict__ pend, u64* __restrict__ ptiles) {
+  for (u32 p = threadIdx.x; p < nparent; p += blockDim.x) {
+    poff[p] = (u64)p * cap;
+    const u64 e = cur[p], lim = (u64)(p + 1) * cap;
+    pend[p] = e < lim ? e : lim;  // an overflowed region (the host falls back anyway) must not be read past its end
+  }
+  if (threadIdx.x == 0) poff[nparent] = (u64)nparent * cap;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    u64 t = 0;
+    for (u32 p = 0; p < nparent; p++) {
+      ptiles[p] = t;
+      t += (pend[p] - poff[p] + tile - 1) / tile;
+    }
+    ptiles[nparent] = t;
   }
 }
 
@@ -383,7 +459,7 @@ template <int kJoinBatch, int MINB>
 __global__ void __launch_bounds__(kJoinThreads, MINB)
 rx_join_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const u64* __restrict__ Sp,
                const u64* __restrict__ offS, u32 nparts, u32 radix_bits, u32 slots, u64 key_mask,
-               u64* __restrict__ ctr, int narrow_keys_elsewhere) {
+               u64* __restrict__ ctr, int narrow_keys_elsewhere, u64 capR, u64 capS) {
   // launched behind rx_join32_kernel: exactly one of the two does the work
   if (narrow_keys_elsewhere && ctr[C_KEY_HI] == 0ull) return;
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -395,7 +471,10 @@ rx_join_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const u
   u64 matches = 0, checksum = 0, maxpart = 0, chunked = 0;
 
   for (u32 p = blockIdx.x; p < nparts; p += gridDim.x) {
-    const u64 r0 = offR[p], r1 = offR[p + 1];
+    // exact layout: partition p = [off[p], off[p+1]); histogram-free layout (cap != 0):
+    // [p*cap, min(off[p], (p+1)*cap)) with off = the scatter's final cursors
+    const u64 r0 = capR ? p * capR : offR[p];
+    const u64 r1 = capR ? (offR[p] < r0 + capR ? offR[p] : r0 + capR) : offR[p + 1];
     const u64 nr = r1 - r0;
     maxpart = nr > maxpart ? nr : maxpart;
     if (Sp == nullptr) {
@@ -406,7 +485,8 @@ rx_join_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const u
       for (u64 i = r0 + tid; i < r1; i += kJoinThreads) checksum += ((u32)Rp[i] & msk) >> radix_bits;
       continue;
     }
-    const u64 s0 = offS[p], s1 = offS[p + 1];
+    const u64 s0 = capS ? p * capS : offS[p];
+    const u64 s1 = capS ? (offS[p] < s0 + capS ? offS[p] : s0 + capS) : offS[p + 1];
     if (nr == 0 || s1 == s0) continue;
     if (nr > chunk_cap) chunked++;
     for (u64 c0 = r0; c0 < r1; c0 += chunk_cap) {

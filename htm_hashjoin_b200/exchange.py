@@ -44,3 +44,37 @@ def reduce_result(matches, checksum, device):
 def domain_bits_for(domain):
     """Bits of the key domain [1, domain] used by the range split."""
     return max(1, int(domain - 1).bit_length())
+
+
+# ---- exchange fused with radix pass 1 (hj_peer_hist / hj_peer_scatter / hj_join_pass1) ----
+
+def peer_cursors(counts_all, rank, n_dest, f1):
+    """counts_all: int64 tensor [G, G*f1], row s = hj_peer_hist of rank s
+    (entry dest*f1 + d1 = tuples rank s holds for pass-1 partition d1 of GPU dest).
+
+    Layout of GPU dest's pass-1 buffer: partitions d1 = 0..f1-1 back to back, inside a partition
+    the contributions of source ranks 0..G-1 back to back.  Returns (cursors, recv_counts):
+    cursors [G*f1] = first element of `rank`'s exclusive range for every (dest, d1);
+    recv_counts [G] = tuples every GPU receives in total."""
+    G = n_dest
+    c = counts_all.view(G, G, f1)                      # [src, dest, d1]
+    per_part = c.sum(0)                                # [dest, d1]
+    part_off = per_part.cumsum(1) - per_part           # exclusive over d1
+    src_prefix = c.cumsum(0) - c                       # exclusive over src
+    start = part_off.unsqueeze(0) + src_prefix         # [src, dest, d1]
+    return start[rank].reshape(-1).contiguous(), per_part.sum(1)
+
+
+def gather_counts(local_counts):
+    """All-gather of the per-rank hj_peer_hist vectors -> [G, len]."""
+    G = dist.get_world_size()
+    out = torch.empty(G * local_counts.numel(), dtype=local_counts.dtype, device=local_counts.device)
+    dist.all_gather_into_tensor(out, local_counts.contiguous().view(-1))
+    return out.view(G, local_counts.numel())
+
+
+def exchange_ipc_handles(handle_bytes):
+    """All-gather of one 64-byte CUDA IPC handle per rank -> list of G handles."""
+    out = [None] * dist.get_world_size()
+    dist.all_gather_object(out, handle_bytes)
+    return out

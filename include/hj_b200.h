@@ -152,6 +152,32 @@ int hj_exchange_partition(hj_handle *h, const uint64_t *in, uint64_t n,
                           uint32_t n_dest, uint32_t domain_bits, uint64_t *out,
                           uint64_t *offsets);
 
+/* ---- exchange fused with radix pass 1 (multi-GPU, one process per GPU) ----
+ * Replaces "partition by destination, all-to-all, then partition again": every rank scatters
+ * its slice by (owner GPU of the key range, low b1 key bits) straight into the owners' pass-1
+ * buffers over NVLink (peer memory mapped with CUDA IPC), i.e. the exchange IS
+ * parallel_radix_partition's first pass (parallel_radix_join.c:559-627) with remote output.
+ * Protocol (the collectives are the caller's: torch.distributed in exchange.py):
+ *   1. hj_radix_plan            -> b1 of the local join (same on every rank)
+ *   2. hj_peer_hist             -> counts[(dest << b1) | low bits] of the local slice
+ *   3. all-gather the counts; every rank derives, for every (dest, low bits), the first element
+ *      of ITS exclusive range in dest's buffer (exchange.peer_cursors)
+ *   4. hj_peer_scatter          -> plain stores into the peers' buffers; claims are local atomics
+ *   5. barrier; hj_join_pass1   -> histogram + pass 2 + per-partition join of what arrived */
+int hj_radix_plan(hj_handle *h, uint64_t n_build, uint32_t *bits, uint32_t *b1,
+                  uint32_t *b2, uint32_t *passes);
+/* 64-byte CUDA IPC handle of a buffer from hj_device_alloc / open it in another process. */
+int hj_ipc_export(hj_handle *h, const void *dptr, void *handle64);
+int hj_ipc_open(hj_handle *h, const void *handle64, void **dptr);
+int hj_ipc_close(hj_handle *h, void *dptr);
+int hj_peer_hist(hj_handle *h, const uint64_t *in, uint64_t n, uint32_t n_dest,
+                 uint32_t domain_bits, uint32_t b1, uint64_t *counts);
+int hj_peer_scatter(hj_handle *h, const uint64_t *in, uint64_t n, uint32_t n_dest,
+                    uint32_t domain_bits, uint32_t b1, uint64_t *const *peer_bufs,
+                    uint64_t *cursors);
+int hj_join_pass1(hj_handle *h, const uint64_t *R1, uint64_t n, const uint64_t *S1,
+                  uint64_t m, hj_result *res);
+
 /* ---- device-side input synthesis (sizes beyond uint32_t/rand()) --
  * Counter-based generators with a bit-identical CPU restatement in oracle/:
  *   kind 0: out[i] = first + i + 1                       (sorted slice)

@@ -85,3 +85,76 @@ def test_reduce_wraps_mod_2_64():
     b = np.array([2 ** 63 + 7, 3], dtype=np.uint64).view(np.int64)
     s = (torch.from_numpy(a.copy()) + torch.from_numpy(b.copy())).numpy().view(np.uint64)
     assert s.tolist() == [12, 2]
+
+
+def _peer_digit(a, G, dom_bits, b1):
+    """numpy statement of digit_of mode 3 (exchange fused with radix pass 1)."""
+    dest = np.minimum(((a - np.uint64(1)) * np.uint64(G)) >> np.uint64(dom_bits), np.uint64(G - 1)).astype(np.int64)
+    return (dest << b1) | (a & np.uint64((1 << b1) - 1)).astype(np.int64)
+
+
+def _fused_worker(rank, world, port, n, m, q):
+    """The fused protocol with numpy standing in for hj_peer_hist / hj_peer_scatter: every rank
+    'stores' its runs into the owners' buffers (gathered over gloo here instead of NVLink stores)
+    at the offsets exchange.peer_cursors hands out; the owners' buffers must come out exactly
+    tiled, pass-1 partitioned, and join to the global result."""
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from htm_hashjoin_b200 import exchange
+    from tests.oracle_lib import Oracle
+    orc = Oracle()
+    R = orc.generate_data("shuffle", n)
+    S = orc.mc_fk(m, n)
+    b1, f1 = 3, 8
+    dom_bits = exchange.domain_bits_for(n)
+    bufs = []
+    for rel, tot in ((R, n), (S, m)):
+        sl = rel[rank * tot // world:(rank + 1) * tot // world]
+        dig = _peer_digit(sl, world, dom_bits, b1)
+        counts = torch.from_numpy(np.bincount(dig, minlength=world * f1).astype(np.int64))
+        allc = exchange.gather_counts(counts)
+        cur, recv = exchange.peer_cursors(allc, rank, world, f1)
+        # what this rank would store where: (dest, absolute offset, tuples)
+        writes = []
+        for d in range(world * f1):
+            t = sl[dig == d]
+            if t.size:
+                writes.append((d // f1, int(cur[d]), t))
+        gathered = [None] * world
+        dist.all_gather_object(gathered, writes)
+        buf = np.zeros(int(recv[rank]), dtype=np.uint64)
+        filled = np.zeros(buf.size, dtype=np.int64)
+        for w in gathered:
+            for dest, off, t in w:
+                if dest == rank:
+                    buf[off:off + t.size] = t
+                    filled[off:off + t.size] += 1
+        assert (filled == 1).all()                                   # exact tiling, no overlap, no gap
+        low = (buf & np.uint64(f1 - 1)).astype(np.int64)
+        assert (np.diff(low) >= 0).all()                             # partition-major by the low b1 bits
+        lo, hi = rank * n // world, (rank + 1) * n // world
+        assert buf.min() >= lo + 1 and buf.max() <= hi               # only this rank's key range
+        bufs.append(buf)
+    mt, ck = orc.true_join(bufs[0], bufs[1])
+    total = exchange.reduce_result(mt, ck, "cpu")
+    if rank == 0:
+        q.put((total, orc.true_join(R, S)))
+    dist.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+def test_two_rank_fused_exchange_protocol(built):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    n, m = 1 << 13, 3 << 13
+    procs = [ctx.Process(target=_fused_worker, args=(r, 2, port, n, m, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    total, want = q.get(timeout=240)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert total == want and want[0] == m

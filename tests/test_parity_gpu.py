@@ -175,6 +175,38 @@ def test_radix_wide_keys_take_generic_kernels(hj, oracle, monkeypatch, force_l2)
         assert (res.matches, res.checksum) == want
 
 
+def test_radix_histogram_free_overflow_falls_back(hj, oracle):
+    """2-pass joins partition without a histogram into fixed-capacity regions (ScOpt, rx_kernels.cuh).
+    Skewed keys overflow a region: the library must notice and redo the join on the exact path."""
+    n = 1 << 17
+    k = np.arange(1, n + 1, dtype=np.uint64)
+    R = k << np.uint64(10)                 # every key in radix partition 0 of 2^10
+    S = np.concatenate([R, R[: n // 2], k])  # plus keys spread over all partitions
+    want = oracle.true_join(R, S)
+    assert want[0] == n + n // 2 + np.count_nonzero((k & np.uint64(1023)) == 0)
+    with hj.HashJoin("radix", num_partitions=1 << 10, passes=2) as h:
+        for _ in range(2):                 # second call: the handle stays on the exact path
+            res = h.join(R, S)
+            assert (res.matches, res.checksum) == want
+        # a well-behaved input on the same handle still joins correctly
+        R2, S2 = _inputs(hj, "shuffle", 16, n)
+        res = h.join(R2, S2)
+        assert (res.matches, res.checksum) == oracle.true_join(R2, S2)
+
+
+def test_radix_histogram_free_equals_exact(hj, oracle, monkeypatch):
+    n = (1 << 18) + 77
+    R = hj.generate_data("uniform", n, n, 16)
+    S = hj.generate_data("shuffle", 3 * n)
+    want = oracle.true_join(R, S)
+    for env in (None, "1"):
+        if env:
+            monkeypatch.setenv("HJ_NO_OPTIMISTIC", env)
+        with hj.HashJoin("radix", num_partitions=1 << 9, passes=2) as h:
+            res = h.join(R, S)
+            assert (res.matches, res.checksum) == want
+
+
 def test_pro_build_only_checksum(hj, oracle):
     """PRO as shipped by the reference: partition + build, Results = sum idx
     (parallel_radix_join.c:231-283); closed form (n/2)(n/2^B - 1), SURVEY 8c."""
@@ -215,6 +247,52 @@ def test_exchange_partition_ranges(hj):
         for g in range(G):
             seg = out[off[g]:off[g + 1]]
             assert seg.min() == g * (n // G) + 1 and seg.max() == (g + 1) * (n // G)
+
+
+def test_fused_exchange_logical_ranks(hj, oracle):
+    """hj_peer_hist / hj_peer_scatter / hj_join_pass1 with two logical ranks on one GPU: both
+    'peer' buffers are local, the protocol and kernels are the ones the NVLink path runs."""
+    import torch
+    from htm_hashjoin_b200 import exchange
+    G, n, m = 2, 1 << 18, 3 << 18
+    R = hj.generate_data("shuffle", n)
+    S = np.concatenate([hj.generate_data("shuffle", n), hj.generate_data("sorted", n), hj.generate_data("uniform", n)])
+    want = oracle.true_join(R, S)
+    dom_bits = exchange.domain_bits_for(n)
+    with hj.HashJoin("radix", num_partitions=1 << 8, passes=2) as h:
+        bits, b1, b2, passes = h.radix_plan(n // G)
+        assert (bits, passes) == (8, 2) and b1 + b2 == 8
+        f1 = 1 << b1
+        total = [0, 0]
+        recv_bufs, recv_n = {}, {}
+        for name, rel in (("R", R), ("S", S)):
+            slices = [rel[g * rel.size // G:(g + 1) * rel.size // G] for g in range(G)]
+            d_slices = [h.to_device(sl) for sl in slices]
+            counts = []
+            for g in range(G):
+                c = torch.zeros(G * f1, dtype=torch.int64, device="cuda")
+                h.peer_hist(d_slices[g][0], slices[g].size, G, dom_bits, b1, c.data_ptr())
+                counts.append(c)
+            allc = torch.stack(counts)
+            assert int(allc.sum()) == rel.size
+            bufs = None
+            for g in range(G):
+                cur, recv = exchange.peer_cursors(allc, g, G, f1)
+                if bufs is None:
+                    bufs = [h.device_alloc((int(recv[d]) + 2) * 8) for d in range(G)]
+                cur = cur.contiguous()
+                torch.cuda.synchronize()
+                h.peer_scatter(d_slices[g][0], slices[g].size, G, dom_bits, b1, bufs, cur.data_ptr())
+            recv_bufs[name], recv_n[name] = bufs, [int(x) for x in recv]
+            # what arrived at logical rank 0 is pass-1 partitioned and in its key range
+            got = h.to_host(bufs[0], recv_n[name][0])
+            assert (np.diff((got & np.uint64(f1 - 1)).astype(np.int64)) >= 0).all()
+            assert got.min() >= 1 and got.max() <= n // G
+        for g in range(G):
+            res = h.join_pass1(recv_bufs["R"][g], recv_n["R"][g], recv_bufs["S"][g], recv_n["S"][g])
+            total[0] += res.matches
+            total[1] = (total[1] + res.checksum) % (1 << 64)
+        assert tuple(total) == want
 
 
 def test_device_generator_matches_oracle(hj, oracle):
