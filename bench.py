@@ -333,8 +333,8 @@ class Rank:
         self.h.peer_hist(self.dS.data_ptr(), self.m, G, dom_bits, self.b1, self.cnt.data_ptr() + 8 * gf)
         t.append(time.perf_counter())
         allc = ex.gather_counts(self.cnt)
-        cur_r, recv_r = ex.peer_cursors(allc[:, :gf].contiguous(), self.rank, G, self.f1)
-        cur_s, recv_s = ex.peer_cursors(allc[:, gf:].contiguous(), self.rank, G, self.f1)
+        cur_r, recv_r, off_r = ex.peer_cursors(allc[:, :gf].contiguous(), self.rank, G, self.f1)
+        cur_s, recv_s, off_s = ex.peer_cursors(allc[:, gf:].contiguous(), self.rank, G, self.f1)
         own = allc[self.rank, self.rank * self.f1:(self.rank + 1) * self.f1].sum() + \
             allc[self.rank, gf + self.rank * self.f1:gf + (self.rank + 1) * self.f1].sum()
         nr, ns, own = torch.stack([recv_r[self.rank], recv_s[self.rank], own]).tolist()  # one sync: cursors ready too
@@ -351,7 +351,7 @@ class Rank:
         self.dist.barrier()
         torch.cuda.synchronize()
         t.append(time.perf_counter())
-        res = self.h.join_pass1(self.recvR, nr, self.recvS, ns)
+        res = self.h.join_pass1(self.recvR, nr, self.recvS, ns, off_r.data_ptr(), off_s.data_ptr())
         t.append(time.perf_counter())
         self.launches += res.kernel_launches
         self.last = res
@@ -465,7 +465,12 @@ def run_b200(args):
             sc_us, sc_bytes = ph["us_scatter2"], 16.0 * (n_loc + m_loc)
         roof = {"bound": "hbm", "kernel": f"rx_scatter_kernel<8> ({2 * P} launches/step: R and S x {P} passes)",
                 "achieved": round(sc_bytes / (sc_us * 1e-6) / 1e9, 1), "peak": peak, "unit": "GB/s",
-                "frac": round(sc_bytes / (sc_us * 1e-6) / 1e9 / peak, 4), "traffic": None,
+                "frac": round(sc_bytes / (sc_us * 1e-6) / 1e9 / peak, 4),
+                # ncu --set full, profiles/r01_ncu_radix_v3_raw.csv: the S pass-2 launch over 2^28 tuples moved
+                # dram__bytes_read 2.148 GB + dram__bytes_write 2.090 GB = 15.79 B/tuple (algorithmic: 16)
+                "traffic": int(15.79 * sc_bytes / 16.0 / (2 * P)),
+                "traffic_source": "15.79 B/tuple measured by ncu at |S|=2^28 (profiles/r01_ncu_radix_v3_raw.csv), "
+                                  "scaled to this launch size",
                 "peak_source": peak_src, "avg_launch_us": round(sc_us / (2 * P), 1),
                 "algorithmic_bytes_per_launch": int(sc_bytes / (2 * P)),
                 "whole_join": {"algorithmic_bytes": int(last.hbm_bytes),
@@ -496,7 +501,7 @@ def run_b200(args):
         line["nvlink_bytes_per_gpu_per_step"] = int(nvl)
         if getattr(rk, "fused", False):
             line["fused_exchange_ms_last_step"] = dict(zip(
-                ["peer_hist", "counts+cursors", "peer_scatter", "barrier", "hist+pass2+join", "allreduce"], rk.fused_ms))
+                ["peer_hist", "counts+cursors", "peer_scatter", "barrier", "pass2+join", "allreduce"], rk.fused_ms))
             line["nvlink_gbs_in_peer_scatter"] = round(nvl / (rk.fused_ms[2] * 1e-3) / 1e9, 1)
     if G == 1 and not args.no_cpu_baseline:
         v, desc, _ = cpu_reference_join(24, 27, 1, 1)

@@ -191,9 +191,10 @@ class HashJoin:
         self._check(lib.hj_peer_scatter(self._h, int(d_in), int(n), n_dest, domain_bits, b1, arr, int(d_cursors)),
                     "hj_peer_scatter")
 
-    def join_pass1(self, d_R1, n, d_S1, m):
+    def join_pass1(self, d_R1, n, d_S1, m, d_offR1=None, d_offS1=None):
         res = hj_result()
-        self._check(lib.hj_join_pass1(self._h, int(d_R1), int(n), int(d_S1), int(m), C.byref(res)), "hj_join_pass1")
+        self._check(lib.hj_join_pass1(self._h, int(d_R1), int(n), int(d_offR1) if d_offR1 else None, int(d_S1), int(m),
+                                      int(d_offS1) if d_offS1 else None, C.byref(res)), "hj_join_pass1")
         return res
 
     def generate(self, kind, first, count, domain, seed, d_out):

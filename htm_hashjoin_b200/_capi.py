@@ -95,7 +95,7 @@ def load():
         "hj_peer_hist": (C.c_int, [H, u64p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, u64p]),
         "hj_peer_scatter": (C.c_int, [H, u64p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32,
                                       C.POINTER(C.c_uint64), u64p]),
-        "hj_join_pass1": (C.c_int, [H, u64p, C.c_uint64, u64p, C.c_uint64, C.POINTER(hj_result)]),
+        "hj_join_pass1": (C.c_int, [H, u64p, C.c_uint64, u64p, u64p, C.c_uint64, u64p, C.POINTER(hj_result)]),
         "hj_generate": (C.c_int, [H, C.c_int, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, u64p]),
         "hj_device_alloc": (C.c_int, [H, C.c_uint64, C.POINTER(vp)]),
         "hj_device_free": (C.c_int, [H, vp]),

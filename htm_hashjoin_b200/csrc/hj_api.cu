@@ -537,7 +537,10 @@ int radix_partition_rel(hj_handle* h, const u64* in, u64 n, RelBufs& rb, const R
 
 // Histogram-free 2-pass partitioning (ScOpt in rx_kernels.cuh): both passes write into
 // fixed-capacity regions, rb.cursors ends up holding the fill level of every final region.
-int radix_partition_rel_opt(hj_handle* h, const u64* in, u64 n, RelBufs& rb, const RadixPlan& pl, int evb) {
+// pre1_off != nullptr: `in` is already the pass-1 output (fused exchange) with exact parent offsets
+// pre1_off[0..F1]: only pass 2 runs, and it gathers the key-width flag.
+int radix_partition_rel_opt(hj_handle* h, const u64* in, u64 n, RelBufs& rb, const RadixPlan& pl, int evb,
+                            const u64* pre1_off = nullptr) {
   const u32 nb = 1u << pl.bits, F1 = 1u << pl.b1, F2 = 1u << pl.b2;
   const u32 tile = kScThreads * pl.tile_ipt;
   const u64 C2 = opt_region_cap(n, pl.bits), C1 = C2 * F2;
@@ -554,7 +557,7 @@ int radix_partition_rel_opt(hj_handle* h, const u64* in, u64 n, RelBufs& rb, con
   memset(&d1, 0, sizeof(d1));
   d1.key_mask = h->cfg.key_mask; d1.mode = 0; d1.shift = 0; d1.bits = pl.b1;
   d2 = d1; d2.shift = pl.b1; d2.bits = pl.b2;
-  {
+  if (!pre1_off) {
     size_t smem = (size_t)tile * 8 + (size_t)F1 * 16;
     CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int grid = grid_for(h, (const void*)k, kScThreads, smem);
@@ -565,16 +568,18 @@ int radix_partition_rel_opt(hj_handle* h, const u64* in, u64 n, RelBufs& rb, con
     CK(cudaGetLastError());
   }
   if (evb >= 0) mark(h, evb + 3);
-  rx_opt_parents_kernel<<<1, 1024, 0, h->stream>>>(rb.pcur.p, F1, C1, tile, rb.poff.p, rb.pend.p, rb.ptiles.p);
+  if (pre1_off) rx_pre1_parents_kernel<<<1, 1024, 0, h->stream>>>(pre1_off, F1, tile, rb.poff.p, rb.pend.p, rb.ptiles.p);
+  else rx_opt_parents_kernel<<<1, 1024, 0, h->stream>>>(rb.pcur.p, F1, C1, tile, rb.poff.p, rb.pend.p, rb.ptiles.p);
   h->launches++;
   {
+    auto kp2 = pre1_off ? k : k2;  // after the fused exchange nobody has looked at the key width yet
     size_t smem = (size_t)tile * 8 + (size_t)F2 * 16;
-    CK(cudaFuncSetAttribute(k2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int grid = grid_for(h, (const void*)k2, kScThreads, smem);
+    CK(cudaFuncSetAttribute(kp2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int grid = grid_for(h, (const void*)kp2, kScThreads, smem);
     if ((u64)grid > ntiles + F1) grid = (int)(ntiles + F1);
     ScOpt o{rb.pend.p, C2, (u64)nb * C2, h->ctr};
-    k2<<<grid, kScThreads, smem, h->stream>>>(rb.tmp.p, rb.out.p, d2, F2, F1, rb.poff.p, rb.ptiles.p, rb.cursors.p,
-                                             nullptr, o);
+    kp2<<<grid, kScThreads, smem, h->stream>>>(pre1_off ? in : rb.tmp.p, rb.out.p, d2, F2, F1, rb.poff.p, rb.ptiles.p,
+                                               rb.cursors.p, nullptr, o);
     h->launches++;
     CK(cudaGetLastError());
   }
@@ -583,7 +588,8 @@ int radix_partition_rel_opt(hj_handle* h, const u64* in, u64 n, RelBufs& rb, con
 }
 
 int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS, u64 m, bool pendS, hj_result* res,
-                   bool pre1 = false, bool force_exact = false) {
+                   bool pre1 = false, bool force_exact = false, const u64* offR1 = nullptr,
+                   const u64* offS1 = nullptr) {
   RadixPlan pl;
   int rc;
   if ((rc = plan_radix(h, n, &pl))) {
@@ -601,19 +607,19 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
   const bool use_l2 = dS && (getenv("HJ_FORCE_L2JOIN") || need > 21000) && !getenv("HJ_NO_L2JOIN");
   // Histogram-free partitioning (ScOpt, rx_kernels.cuh) for the 2-pass shared-memory join; the
   // exact, histogram-based layout everywhere else and after an overflow on this handle.
-  const bool opt = dS && !pre1 && !use_l2 && pl.passes == 2 && !h->no_optimistic && !force_exact &&
+  const bool opt = dS && (!pre1 || (offR1 && offS1)) && !use_l2 && pl.passes == 2 && !h->no_optimistic && !force_exact &&
                    !getenv("HJ_NO_OPTIMISTIC");
   const u64 capR = opt ? opt_region_cap(n, pl.bits) : 0, capS = opt ? opt_region_cap(m, pl.bits) : 0;
   if ((rc = ensure_rel(h, h->rb[0], n, pl, pre1, opt))) return rc;
   if (dS && (rc = ensure_rel(h, h->rb[1], m, pl, pre1, opt))) return rc;
   CK(cudaMemsetAsync(h->ctr, 0, C_COUNT * sizeof(u64), h->stream));
   if ((rc = wait_staged(h, E_CPR, pendR))) return rc;
-  if (opt) rc = radix_partition_rel_opt(h, dR, n, h->rb[0], pl, E_RX);
+  if (opt) rc = radix_partition_rel_opt(h, dR, n, h->rb[0], pl, E_RX, pre1 ? offR1 : nullptr);
   else rc = radix_partition_rel(h, dR, n, h->rb[0], pl, E_RX, h->ctr + C_MAX_PART, pre1);
   if (rc) return rc;
   if (dS) {
     if ((rc = wait_staged(h, E_CPS, pendS))) return rc;
-    if (opt) rc = radix_partition_rel_opt(h, dS, m, h->rb[1], pl, E_RX + 5);
+    if (opt) rc = radix_partition_rel_opt(h, dS, m, h->rb[1], pl, E_RX + 5, pre1 ? offS1 : nullptr);
     else rc = radix_partition_rel(h, dS, m, h->rb[1], pl, E_RX + 5, nullptr, pre1);
     if (rc) return rc;
   }
@@ -1215,14 +1221,19 @@ int hj_peer_scatter(hj_handle* h, const uint64_t* in, uint64_t n, uint32_t n_des
 }
 
 // Join of relations that are already pass-1 partitioned (by the low b1 bits of hj_radix_plan,
-// partition-major, contiguous): histogram, pass 2, per-partition join.  Device pointers only.
-int hj_join_pass1(hj_handle* h, const uint64_t* R1, uint64_t n, const uint64_t* S1, uint64_t m, hj_result* res) {
+// partition-major, contiguous): pass 2 + per-partition join.  Device pointers only.  offR1/offS1:
+// the 2^b1 + 1 pass-1 partition offsets (known from the exchange protocol) -- with them pass 2
+// runs histogram-free; without them (nullptr) the arrived data is histogrammed first.
+int hj_join_pass1(hj_handle* h, const uint64_t* R1, uint64_t n, const uint64_t* offR1, const uint64_t* S1,
+                  uint64_t m, const uint64_t* offS1, hj_result* res) {
   if (!h || !R1 || !S1 || !is_device_ptr(R1) || !is_device_ptr(S1)) return HJ_EINVAL;
   CK(cudaSetDevice(h->device));
   if (res) memset(res, 0, sizeof(*res));
   reset_events(h);
   mark(h, E_T0);
-  return run_radix_join(h, (const u64*)R1, n, false, (const u64*)S1, m, false, res, true);
+  if ((offR1 && !is_device_ptr(offR1)) || (offS1 && !is_device_ptr(offS1))) return HJ_EINVAL;
+  return run_radix_join(h, (const u64*)R1, n, false, (const u64*)S1, m, false, res, true, false, (const u64*)offR1,
+                        (const u64*)offS1);
 }
 
 int hj_generate(hj_handle* h, int kind, uint64_t first, uint64_t count, uint64_t domain, uint64_t seed,

@@ -411,6 +411,24 @@ __global__ void __launch_bounds__(256) rx_opt_init_kernel(u64* __restrict__ a, u
   if (i < na) a[i] = (u64)i * capa;
   if (i < nb) b[i] = (u64)i * capb;
 }
+// pass-1 output that arrived through the fused exchange: parent p = [off[p], off[p+1]) exactly
+__global__ void __launch_bounds__(1024) rx_pre1_parents_kernel(const u64* __restrict__ off, u32 nparent, u32 tile,
+                                                                u64* __restrict__ poff, u64* __restrict__ pend,
+                                                                u64* __restrict__ ptiles) {
+  for (u32 p = threadIdx.x; p <= nparent; p += blockDim.x) {
+    poff[p] = off[p];
+    if (p < nparent) pend[p] = off[p + 1];
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    u64 t = 0;
+    for (u32 p = 0; p < nparent; p++) {
+      ptiles[p] = t;
+      t += (pend[p] - poff[p] + tile - 1) / tile;
+    }
+    ptiles[nparent] = t;
+  }
+}
 // after pass 1: parent p = [p*cap, cur[p]); tiles[p] = scatter tiles before parent p (one CTA)
 __global__ void __launch_bounds__(1024) rx_opt_parents_kernel(const u64* __restrict__ cur, u32 nparent, u64 cap,
                                                                u32 tile, u64* __restrict__ poff,

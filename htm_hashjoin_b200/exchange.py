@@ -53,16 +53,19 @@ def peer_cursors(counts_all, rank, n_dest, f1):
     (entry dest*f1 + d1 = tuples rank s holds for pass-1 partition d1 of GPU dest).
 
     Layout of GPU dest's pass-1 buffer: partitions d1 = 0..f1-1 back to back, inside a partition
-    the contributions of source ranks 0..G-1 back to back.  Returns (cursors, recv_counts):
+    the contributions of source ranks 0..G-1 back to back.  Returns (cursors, recv_counts, part_off):
     cursors [G*f1] = first element of `rank`'s exclusive range for every (dest, d1);
-    recv_counts [G] = tuples every GPU receives in total."""
+    recv_counts [G] = tuples every GPU receives in total;
+    part_off [f1+1] = offsets of the pass-1 partitions inside `rank`'s own buffer (for hj_join_pass1)."""
     G = n_dest
     c = counts_all.view(G, G, f1)                      # [src, dest, d1]
     per_part = c.sum(0)                                # [dest, d1]
     part_off = per_part.cumsum(1) - per_part           # exclusive over d1
     src_prefix = c.cumsum(0) - c                       # exclusive over src
     start = part_off.unsqueeze(0) + src_prefix         # [src, dest, d1]
-    return start[rank].reshape(-1).contiguous(), per_part.sum(1)
+    recv = per_part.sum(1)
+    own_off = torch.cat([part_off[rank], recv[rank:rank + 1]]).contiguous()
+    return start[rank].reshape(-1).contiguous(), recv, own_off
 
 
 def gather_counts(local_counts):

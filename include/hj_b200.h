@@ -175,8 +175,10 @@ int hj_peer_hist(hj_handle *h, const uint64_t *in, uint64_t n, uint32_t n_dest,
 int hj_peer_scatter(hj_handle *h, const uint64_t *in, uint64_t n, uint32_t n_dest,
                     uint32_t domain_bits, uint32_t b1, uint64_t *const *peer_bufs,
                     uint64_t *cursors);
-int hj_join_pass1(hj_handle *h, const uint64_t *R1, uint64_t n, const uint64_t *S1,
-                  uint64_t m, hj_result *res);
+/* offR1/offS1: DEVICE arrays of the 2^b1 + 1 pass-1 partition offsets inside R1/S1 (or NULL:
+ * the library histograms what arrived). */
+int hj_join_pass1(hj_handle *h, const uint64_t *R1, uint64_t n, const uint64_t *offR1,
+                  const uint64_t *S1, uint64_t m, const uint64_t *offS1, hj_result *res);
 
 /* ---- device-side input synthesis (sizes beyond uint32_t/rand()) --
  * Counter-based generators with a bit-identical CPU restatement in oracle/:

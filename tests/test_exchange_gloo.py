@@ -115,7 +115,7 @@ def _fused_worker(rank, world, port, n, m, q):
         dig = _peer_digit(sl, world, dom_bits, b1)
         counts = torch.from_numpy(np.bincount(dig, minlength=world * f1).astype(np.int64))
         allc = exchange.gather_counts(counts)
-        cur, recv = exchange.peer_cursors(allc, rank, world, f1)
+        cur, recv, own_off = exchange.peer_cursors(allc, rank, world, f1)
         # what this rank would store where: (dest, absolute offset, tuples)
         writes = []
         for d in range(world * f1):
@@ -134,6 +134,7 @@ def _fused_worker(rank, world, port, n, m, q):
         assert (filled == 1).all()                                   # exact tiling, no overlap, no gap
         low = (buf & np.uint64(f1 - 1)).astype(np.int64)
         assert (np.diff(low) >= 0).all()                             # partition-major by the low b1 bits
+        assert np.array_equal(np.searchsorted(low, np.arange(f1 + 1)), own_off.numpy())  # offsets for hj_join_pass1
         lo, hi = rank * n // world, (rank + 1) * n // world
         assert buf.min() >= lo + 1 and buf.max() <= hi               # only this rank's key range
         bufs.append(buf)

@@ -264,7 +264,7 @@ def test_fused_exchange_logical_ranks(hj, oracle):
         assert (bits, passes) == (8, 2) and b1 + b2 == 8
         f1 = 1 << b1
         total = [0, 0]
-        recv_bufs, recv_n = {}, {}
+        recv_bufs, recv_n, recv_off = {}, {}, {}
         for name, rel in (("R", R), ("S", S)):
             slices = [rel[g * rel.size // G:(g + 1) * rel.size // G] for g in range(G)]
             d_slices = [h.to_device(sl) for sl in slices]
@@ -276,8 +276,10 @@ def test_fused_exchange_logical_ranks(hj, oracle):
             allc = torch.stack(counts)
             assert int(allc.sum()) == rel.size
             bufs = None
+            recv_off[name] = []
             for g in range(G):
-                cur, recv = exchange.peer_cursors(allc, g, G, f1)
+                cur, recv, own_off = exchange.peer_cursors(allc, g, G, f1)
+                recv_off[name].append(own_off.contiguous())
                 if bufs is None:
                     bufs = [h.device_alloc((int(recv[d]) + 2) * 8) for d in range(G)]
                 cur = cur.contiguous()
@@ -288,11 +290,15 @@ def test_fused_exchange_logical_ranks(hj, oracle):
             got = h.to_host(bufs[0], recv_n[name][0])
             assert (np.diff((got & np.uint64(f1 - 1)).astype(np.int64)) >= 0).all()
             assert got.min() >= 1 and got.max() <= n // G
-        for g in range(G):
-            res = h.join_pass1(recv_bufs["R"][g], recv_n["R"][g], recv_bufs["S"][g], recv_n["S"][g])
-            total[0] += res.matches
-            total[1] = (total[1] + res.checksum) % (1 << 64)
-        assert tuple(total) == want
+        for with_offsets in (False, True):   # histogram of what arrived / histogram-free pass 2
+            total = [0, 0]
+            for g in range(G):
+                offs = (recv_off["R"][g].data_ptr(), recv_off["S"][g].data_ptr()) if with_offsets else (None, None)
+                torch.cuda.synchronize()
+                res = h.join_pass1(recv_bufs["R"][g], recv_n["R"][g], recv_bufs["S"][g], recv_n["S"][g], *offs)
+                total[0] += res.matches
+                total[1] = (total[1] + res.checksum) % (1 << 64)
+            assert tuple(total) == want
 
 
 def test_device_generator_matches_oracle(hj, oracle):

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Small fixed workload for ncu captures: two identical joins (the first is warm-up).
 
-  python tools/profile_join.py radix   # |R|=2^25 PK, |S|=2^28 FK, 2^15 partitions in 2 passes (C3's 7+8 bit split)
+  python tools/profile_join.py radix   # |R|=2^25 PK, |S|=2^28 FK, 2^11 partitions in 2 passes (C3's partition size)
   python tools/profile_join.py global  # atomic table, |R|=|S|=2^24, uniform then sorted
 """
 import sys
@@ -13,7 +13,8 @@ import htm_hashjoin_b200 as hj  # noqa: E402
 what = sys.argv[1] if len(sys.argv) > 1 else "radix"
 if what == "radix":
     n, m = 1 << 25, 1 << 28
-    with hj.HashJoin("radix", num_partitions=1 << 15, passes=2) as h:
+    # 2^11 partitions: R partitions of 16384 tuples like the default plan at C3 (2^27 / 2^13)
+    with hj.HashJoin("radix", num_partitions=1 << 11, passes=2) as h:
         dR, dS = h.device_alloc(n * 8), h.device_alloc(m * 8)
         h.generate(1, 0, n, n, 12345, dR)
         h.generate(1, 0, m, n, 54321, dS)
