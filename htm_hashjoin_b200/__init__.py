@@ -82,7 +82,8 @@ class HashJoin:
     """One hj_handle: owns the device buffers of one GPU."""
 
     def __init__(self, algo="atomic", device=0, probe_length=4, scale_output=2, num_partitions=0, passes=0,
-                 transaction_size=16, enable_probe=True, sample_rounds=5, key_mask=0, adaptive_threshold=0.0):
+                 transaction_size=16, enable_probe=True, sample_rounds=5, key_mask=0, adaptive_threshold=0.0,
+                 pass1_bits=0):
         cfg = hj_config()
         lib.hj_config_default(C.byref(cfg))
         cfg.algo = ALGOS[algo] if isinstance(algo, str) else int(algo)
@@ -96,6 +97,7 @@ class HashJoin:
         cfg.sample_rounds = sample_rounds
         cfg.key_mask = key_mask if key_mask else 0xFFFFFFFFFFFFFFFF
         cfg.adaptive_threshold = adaptive_threshold
+        cfg.pass1_bits = pass1_bits
         self.cfg = cfg
         self._h = C.c_void_p()
         rc = lib.hj_create(C.byref(cfg), C.byref(self._h))

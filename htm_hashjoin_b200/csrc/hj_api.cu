@@ -395,6 +395,11 @@ int plan_radix(hj_handle* h, u64 n, RadixPlan* pl) {
   pl->bits = bits;
   pl->passes = passes;
   pl->b1 = passes == 2 ? bits / 2 : bits;  // prj_params.h:76-78: pass 1 gets floor(b/2)
+  if (passes == 2 && h->cfg.pass1_bits) {
+    const u32 want = (u32)h->cfg.pass1_bits;
+    if (want < 1 || want >= bits || bits - want > kMaxBitsPerPass) return HJ_EINVAL;
+    pl->b1 = want;
+  }
   pl->b2 = bits - pl->b1;
   // join table: expected partition * 2, power of two, capped by shared memory
   u64 per = (n >> bits) + 1;
@@ -1201,13 +1206,16 @@ int hj_peer_scatter(hj_handle* h, const uint64_t* in, uint64_t n, uint32_t n_des
   if ((rc = ensure(h, rb.one, 4))) return rc;
   if ((rc = ensure(h, h->peer_ptrs, kScMaxPeers))) return rc;
   const u32 F = n_dest << b1;
-  const u32 tile = kScThreads * 8;
+  constexpr int kPeerIPT = 32;
+  const u32 tile = kScThreads * kPeerIPT;
   const u64 ntiles = (n + tile - 1) / tile;
   const u64 one[4] = {0, n, 0, ntiles};  // the one-parent view: offsets {0, n}, tiles {0, ntiles}
   CK(cudaMemcpyAsync(rb.one.p, one, sizeof(one), cudaMemcpyHostToDevice, h->stream));
   CK(cudaMemcpyAsync(h->peer_ptrs.p, peer_bufs, n_dest * sizeof(u64*), cudaMemcpyHostToDevice, h->stream));
-  auto k = rx_scatter_kernel<8, 2, true>;
-  size_t smem = (size_t)tile * 8 + (size_t)F * 16;
+  // runs leave through bulk async copies (TMA) unless HJ_PEER_NO_BULK is set (then: 8-byte stores)
+  const bool bulk = !getenv("HJ_PEER_NO_BULK") && (F % 2 == 0);
+  auto k = bulk ? rx_scatter_kernel<kPeerIPT, 2, true, 0, true> : rx_scatter_kernel<kPeerIPT, 2, true, 0, false>;
+  size_t smem = (size_t)tile * 8 + (size_t)F * 16 + (bulk ? (size_t)(F + 2) * 8 + (size_t)F * 4 : 0);
   CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int grid = grid_for(h, (const void*)k, kScThreads, smem);
   if (getenv("HJ_PEER_CTAS")) grid = h->sm_count * atoi(getenv("HJ_PEER_CTAS"));

@@ -230,8 +230,14 @@ struct ScOpt {
 };
 
 // OPT: 0 = exact layout, 1 = histogram-free + key-width flag (pass 1), 2 = histogram-free (pass 2)
-template <int IPT, int MODE, bool PEER = false, int OPT = 0>
-__global__ void __launch_bounds__(kScThreads, 3)
+// PEER launches use big tiles (IPT = 32: 16384 tuples, 128 KB) and one CTA per SM: NVLink, not the SM,
+// bounds them (same time with 1 or 3 CTAs/SM), and 4x longer runs mean 4x larger NVLink writes.
+// BULK (with PEER): a run leaves through ONE bulk async copy (cp.async.bulk shared -> global, the
+// TMA engine) instead of 8-byte stores from 32 lanes.  Bulk copies need 16-byte aligned source,
+// destination and size: every digit gets one spare slot in the shared-memory tile so its run can
+// start on the parity of its global offset; an odd head / tail tuple goes out as a scalar store.
+template <int IPT, int MODE, bool PEER = false, int OPT = 0, bool BULK = false>
+__global__ void __launch_bounds__(kScThreads, PEER ? 1 : 3)
 rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u32 F, u32 nparent,
                   const u64* __restrict__ parent_off, const u64* __restrict__ parent_tiles,
                   u64* __restrict__ cursors, u64* const* __restrict__ peer_out, ScOpt opt) {
@@ -240,11 +246,13 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
   __shared__ u64 s_pend[OPT ? kScParentCache + 1 : 1];
   u32 key_hi = 0;
   constexpr int TILE = kScThreads * IPT;
+  static_assert(TILE <= 65536, "rank is packed into 16 bits");
   extern __shared__ __align__(16) unsigned char smem_raw[];
   u64* tile = reinterpret_cast<u64*>(smem_raw);
-  u64* gdelta = tile + TILE;
+  u64* gdelta = tile + TILE + (BULK ? F + 2 : 0);  // BULK: one spare slot per digit (F even)
   u32* hist = reinterpret_cast<u32*>(gdelta + F);
   u32* lbase = hist + F;
+  u32* rcnt = lbase + F;  // BULK only: run lengths of the tile being flushed
   __shared__ u32 warp_tot[kScThreads / 32];
 
   // the tile -> parent search would be a chain of dependent global loads per tile:
@@ -315,6 +323,8 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
         if (OPT == 1) key_hi |= (u32)(v[j] >> 32);
       }
     }
+    // BULK: the previous tile's bulk copies have finished READING shared memory
+    if (BULK) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
     __syncthreads();  // also: every thread has finished flushing the previous tile
 
     // exclusive scan of hist -> lbase; one global claim per non-empty digit
@@ -358,8 +368,15 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
               g = opt.trash_off;
               opt.ctr[C_OPT_OVF] = 1ull;
             }
-            gdelta[b] = g - run;
+            if (BULK) {
+              const u32 sm = run + b + (((run + b) ^ (u32)g) & 1u);  // same parity as the global offset
+              lbase[b] = sm;
+              gdelta[b] = g;
+            } else {
+              gdelta[b] = g - run;
+            }
           }
+          if (BULK) rcnt[b] = c;
           run += c;
         }
       }
@@ -376,6 +393,27 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
     if (t < total_tiles) load_tile(t, p, cnt);
     __syncthreads();
 
+    if (BULK) {
+      // flush: one thread per run; generic-proxy writes of the tile made visible to the async proxy
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      for (u32 b = tid; b < F; b += kScThreads) {
+        u32 c = rcnt[b];
+        if (c == 0) continue;
+        u32 sm = lbase[b];
+        u64 g = gdelta[b];
+        u64* o = PEER ? s_peer[b >> dg.b1] : out;
+        if (g & 1ull) { o[g] = tile[sm]; ++sm; ++g; --c; }
+        const u32 n2 = c & ~1u;
+        if (n2) {
+          const u32 src = (u32)__cvta_generic_to_shared(tile + sm);
+          asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(o + g), "r"(src),
+                       "r"(n2 * 8u)
+                       : "memory");
+        }
+        if (c & 1u) o[g + n2] = tile[sm + n2];
+      }
+      asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    } else
     // flush: element i of the digit-sorted tile goes to gdelta[digit] + i
     if (cnt_cur == TILE) {
 #pragma unroll
@@ -397,6 +435,7 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
     // no barrier here: the one after the next tile's ranking orders this flush before the
     // next writes to lbase/gdelta/tile
   }
+  if (BULK) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   if (OPT == 1) {
     key_hi = __reduce_or_sync(0xffffffffu, key_hi) & (u32)(dg.key_mask >> 32);
     if (key_hi && lane_id() == 0) atomicOr(opt.ctr + C_KEY_HI, (u64)key_hi);

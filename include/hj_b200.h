@@ -68,7 +68,10 @@ typedef struct hj_config {
   uint64_t key_mask;         /* key = tuple & key_mask; 0 = all 64 bits (main binary),
                                 0xffffffff for mc tuples                                */
   double adaptive_threshold; /* contention above this -> radix path; <=0 = default     */
-  uint64_t reserved[4];
+  uint64_t pass1_bits;       /* 2-pass plans: radix bits of pass 1; 0 = floor(bits/2) as
+                                prj_params.h:76-78.  The fused multi-GPU exchange uses a
+                                smaller pass 1 so that G << pass1_bits stays ~128 bins    */
+  uint64_t reserved[3];
 } hj_config;
 
 /* Per-call outcome.  The first block mirrors the JSON the reference prints
