@@ -459,11 +459,20 @@ int launch_hist(hj_handle* h, const u64* in, u64 n, const Digit& dg, u32 nbins, 
   return HJ_OK;
 }
 
+bool sc_bulk() {
+  static const bool on = !getenv("HJ_SC_NO_BULK");
+  return on;
+}
+// BULK shared memory on top of tile + F*16: one spare tile slot per digit (+2) and the run lengths
+size_t sc_bulk_extra(u32 F) { return (size_t)(F + 2) * 8 + (size_t)F * 4; }
+
 template <int IPT, int MODE>
 int launch_scatter_tm(hj_handle* h, const u64* in, u64* out, const Digit& dg, u32 F, u32 nparent, const u64* poff,
                       const u64* ptiles, u64* cursors, u64 max_tiles) {
-  auto k = rx_scatter_kernel<IPT, MODE>;
-  size_t smem = (size_t)kScThreads * IPT * 8 + (size_t)F * 16;
+  // runs leave through bulk async copies (TMA) when the fan-out is even; HJ_SC_NO_BULK: 8-byte stores
+  const bool bulk = sc_bulk() && F % 2 == 0;
+  auto k = bulk ? rx_scatter_kernel<IPT, MODE, false, 0, true> : rx_scatter_kernel<IPT, MODE, false, 0, false>;
+  size_t smem = (size_t)kScThreads * IPT * 8 + (size_t)F * 16 + (bulk ? sc_bulk_extra(F) : 0);
   CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int grid = grid_for(h, (const void*)k, kScThreads, smem);
   if ((u64)grid > max_tiles) grid = (int)(max_tiles ? max_tiles : 1);
@@ -556,14 +565,15 @@ int radix_partition_rel_opt(hj_handle* h, const u64* in, u64 n, RelBufs& rb, con
   CK(cudaMemcpyAsync(rb.one.p, one, sizeof(one), cudaMemcpyHostToDevice, h->stream));
   h->launches++;
   if (evb >= 0) mark(h, evb + 2);
-  auto k = rx_scatter_kernel<8, 0, false, 1>;
-  auto k2 = rx_scatter_kernel<8, 0, false, 2>;
+  const bool bulk = sc_bulk() && F1 % 2 == 0 && F2 % 2 == 0;
+  auto k = bulk ? rx_scatter_kernel<8, 0, false, 1, true> : rx_scatter_kernel<8, 0, false, 1, false>;
+  auto k2 = bulk ? rx_scatter_kernel<8, 0, false, 2, true> : rx_scatter_kernel<8, 0, false, 2, false>;
   Digit d1, d2;
   memset(&d1, 0, sizeof(d1));
   d1.key_mask = h->cfg.key_mask; d1.mode = 0; d1.shift = 0; d1.bits = pl.b1;
   d2 = d1; d2.shift = pl.b1; d2.bits = pl.b2;
   if (!pre1_off) {
-    size_t smem = (size_t)tile * 8 + (size_t)F1 * 16;
+    size_t smem = (size_t)tile * 8 + (size_t)F1 * 16 + (bulk ? sc_bulk_extra(F1) : 0);
     CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int grid = grid_for(h, (const void*)k, kScThreads, smem);
     if ((u64)grid > ntiles) grid = (int)(ntiles ? ntiles : 1);
@@ -578,7 +588,7 @@ int radix_partition_rel_opt(hj_handle* h, const u64* in, u64 n, RelBufs& rb, con
   h->launches++;
   {
     auto kp2 = pre1_off ? k : k2;  // after the fused exchange nobody has looked at the key width yet
-    size_t smem = (size_t)tile * 8 + (size_t)F2 * 16;
+    size_t smem = (size_t)tile * 8 + (size_t)F2 * 16 + (bulk ? sc_bulk_extra(F2) : 0);
     CK(cudaFuncSetAttribute(kp2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int grid = grid_for(h, (const void*)kp2, kScThreads, smem);
     if ((u64)grid > ntiles + F1) grid = (int)(ntiles + F1);
@@ -1215,7 +1225,7 @@ int hj_peer_scatter(hj_handle* h, const uint64_t* in, uint64_t n, uint32_t n_des
   // runs leave through bulk async copies (TMA) unless HJ_PEER_NO_BULK is set (then: 8-byte stores)
   const bool bulk = !getenv("HJ_PEER_NO_BULK") && (F % 2 == 0);
   auto k = bulk ? rx_scatter_kernel<kPeerIPT, 2, true, 0, true> : rx_scatter_kernel<kPeerIPT, 2, true, 0, false>;
-  size_t smem = (size_t)tile * 8 + (size_t)F * 16 + (bulk ? (size_t)(F + 2) * 8 + (size_t)F * 4 : 0);
+  size_t smem = (size_t)tile * 8 + (size_t)F * 16 + (bulk ? sc_bulk_extra(F) : 0);
   CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int grid = grid_for(h, (const void*)k, kScThreads, smem);
   if (getenv("HJ_PEER_CTAS")) grid = h->sm_count * atoi(getenv("HJ_PEER_CTAS"));
