@@ -463,6 +463,13 @@ bool sc_bulk() {
   static const bool on = !getenv("HJ_SC_NO_BULK");
   return on;
 }
+// Input tiles staged by TMA: measured SLOWER than register loads at C3 (scatter 1: 4.49 vs 3.80 ms,
+// scatter 2: 4.86 vs 4.16 ms, 3 CTAs/SM in both): the staging pass adds a shared-memory write and a
+// read per tuple to a kernel whose shared-memory pipe is already the busiest unit.  Opt-in only.
+bool sc_tmain() {
+  static const bool on = getenv("HJ_SC_TMAIN") != nullptr;
+  return on;
+}
 // BULK shared memory on top of tile + F*16: one spare tile slot per digit (+2) and the run lengths
 size_t sc_bulk_extra(u32 F) { return (size_t)(F + 2) * 8 + (size_t)F * 4; }
 
@@ -566,14 +573,21 @@ int radix_partition_rel_opt(hj_handle* h, const u64* in, u64 n, RelBufs& rb, con
   h->launches++;
   if (evb >= 0) mark(h, evb + 2);
   const bool bulk = sc_bulk() && F1 % 2 == 0 && F2 % 2 == 0;
-  auto k = bulk ? rx_scatter_kernel<8, 0, false, 1, true> : rx_scatter_kernel<8, 0, false, 1, false>;
-  auto k2 = bulk ? rx_scatter_kernel<8, 0, false, 2, true> : rx_scatter_kernel<8, 0, false, 2, false>;
+  // input tiles staged through shared memory by one bulk copy each (TMAIN), with the bulk flush only
+  const bool tmain = bulk && sc_tmain() && F1 <= 128 && F2 <= 128;  // beyond: the staging buffer costs a CTA per SM
+  auto k = tmain  ? rx_scatter_kernel<8, 0, false, 1, true, true>
+           : bulk ? rx_scatter_kernel<8, 0, false, 1, true>
+                  : rx_scatter_kernel<8, 0, false, 1, false>;
+  auto k2 = tmain  ? rx_scatter_kernel<8, 0, false, 2, true, true>
+            : bulk ? rx_scatter_kernel<8, 0, false, 2, true>
+                   : rx_scatter_kernel<8, 0, false, 2, false>;
+  const size_t stage = tmain ? (size_t)tile * 8 : 0;
   Digit d1, d2;
   memset(&d1, 0, sizeof(d1));
   d1.key_mask = h->cfg.key_mask; d1.mode = 0; d1.shift = 0; d1.bits = pl.b1;
   d2 = d1; d2.shift = pl.b1; d2.bits = pl.b2;
   if (!pre1_off) {
-    size_t smem = (size_t)tile * 8 + (size_t)F1 * 16 + (bulk ? sc_bulk_extra(F1) : 0);
+    size_t smem = stage + (size_t)tile * 8 + (size_t)F1 * 16 + (bulk ? sc_bulk_extra(F1) : 0);
     CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int grid = grid_for(h, (const void*)k, kScThreads, smem);
     if ((u64)grid > ntiles) grid = (int)(ntiles ? ntiles : 1);
@@ -588,7 +602,7 @@ int radix_partition_rel_opt(hj_handle* h, const u64* in, u64 n, RelBufs& rb, con
   h->launches++;
   {
     auto kp2 = pre1_off ? k : k2;  // after the fused exchange nobody has looked at the key width yet
-    size_t smem = (size_t)tile * 8 + (size_t)F2 * 16 + (bulk ? sc_bulk_extra(F2) : 0);
+    size_t smem = stage + (size_t)tile * 8 + (size_t)F2 * 16 + (bulk ? sc_bulk_extra(F2) : 0);
     CK(cudaFuncSetAttribute(kp2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int grid = grid_for(h, (const void*)kp2, kScThreads, smem);
     if ((u64)grid > ntiles + F1) grid = (int)(ntiles + F1);

@@ -230,13 +230,45 @@ struct ScOpt {
 };
 
 // OPT: 0 = exact layout, 1 = histogram-free + key-width flag (pass 1), 2 = histogram-free (pass 2)
+// ---- TMA (bulk async copy) input staging: mbarrier + cp.async.bulk global -> shared ----------
+__device__ __forceinline__ void mbar_init(u32 a, u32 count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(a), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(u32 a, u32 bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(a), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_1d(u32 dst, const void* src, u32 bytes, u32 mbar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(mbar)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(u32 a, u32 parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred P1;\n"
+      "LAB_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+      "@P1 bra DONE;\n"
+      "bra LAB_WAIT;\n"
+      "DONE:\n"
+      "}" ::"r"(a),
+      "r"(parity)
+      : "memory");
+}
+
 // PEER launches use big tiles (IPT = 32: 16384 tuples, 128 KB) and one CTA per SM: NVLink, not the SM,
 // bounds them (same time with 1 or 3 CTAs/SM), and 4x longer runs mean 4x larger NVLink writes.
 // BULK (with PEER): a run leaves through ONE bulk async copy (cp.async.bulk shared -> global, the
 // TMA engine) instead of 8-byte stores from 32 lanes.  Bulk copies need 16-byte aligned source,
 // destination and size: every digit gets one spare slot in the shared-memory tile so its run can
 // start on the parity of its global offset; an odd head / tail tuple goes out as a scalar store.
-template <int IPT, int MODE, bool PEER = false, int OPT = 0, bool BULK = false>
+// TMAIN: full, 16-byte aligned input tiles are fetched by ONE bulk async copy (TMA) into a
+// shared-memory staging buffer, issued a whole tile ahead (right after the scan of the previous tile,
+// when every thread holds its tuples in registers): no registers are tied up by loads in flight and
+// the copy has the placement and the flush to complete.  Measured at C3: 18 % SLOWER than the
+// register loads (profiles/r01_scatter_tmain_vs_regs.jsonl) -- the extra shared-memory write + read
+// per tuple costs more than the exposed load latency it removes; kept opt-in (HJ_SC_TMAIN=1).
+template <int IPT, int MODE, bool PEER = false, int OPT = 0, bool BULK = false, bool TMAIN = false>
 __global__ void __launch_bounds__(kScThreads, PEER ? 1 : 3)
 rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u32 F, u32 nparent,
                   const u64* __restrict__ parent_off, const u64* __restrict__ parent_tiles,
@@ -248,8 +280,15 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
   constexpr int TILE = kScThreads * IPT;
   static_assert(TILE <= 65536, "rank is packed into 16 bits");
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  u64* tile = reinterpret_cast<u64*>(smem_raw);
+  u64* inbuf = reinterpret_cast<u64*>(smem_raw);  // TMAIN: staging buffer of the next input tile
+  u64* tile = inbuf + (TMAIN ? TILE : 0);
   u64* gdelta = tile + TILE + (BULK ? F + 2 : 0);  // BULK: one spare slot per digit (F even)
+  __shared__ __align__(8) u64 s_mbar;
+  const u32 mbar = (u32)__cvta_generic_to_shared(&s_mbar);
+  if (TMAIN && threadIdx.x == 0) {
+    mbar_init(mbar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
   u32* hist = reinterpret_cast<u32*>(gdelta + F);
   u32* lbase = hist + F;
   u32* rcnt = lbase + F;  // BULK only: run lengths of the tile being flushed
@@ -277,19 +316,23 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
   const u32 total_tiles = (u32)pt[nparent];  // < 2^32 tiles of 4096 tuples
   const u32 per_thread = (F + kScThreads - 1) / kScThreads;  // bins each thread scans
 
-  // Locate tile t (parent, start, length) and issue its loads.  Called for the first tile
-  // and then, for tile k+1, right after tile k has been moved to shared memory: the loads
-  // fly while tile k is flushed, so the read stream never drains.
+  // locate: tile t -> (parent, first element, length).  fetch: its loads, either register loads
+  // (issued right after tile k has been moved to shared memory, so they fly while tile k is flushed)
+  // or, TMAIN, one bulk copy issued by thread 0 a whole phase earlier.
   u64 v[IPT];
-  auto load_tile = [&](u32 t, u32& p_out, u32& cnt_out) {
+  u64 begin = 0;
+  auto locate = [&](u32 t, u32& p_out, u32& cnt_out) {
     u32 lo = 0, hi = nparent;  // last p with parent_tiles[p] <= t
     while (hi - lo > 1) {
       const u32 mid = (lo + hi) >> 1;
       if (pt[mid] <= t) lo = mid; else hi = mid;
     }
-    const u64 begin = po[lo] + (t - pt[lo]) * TILE;
+    begin = po[lo] + (t - pt[lo]) * TILE;
     const u64 pend = OPT ? s_pend[lo] : po[lo + 1];  // OPT: nparent <= kScParentCache (host)
-    const u32 cnt = (u32)(pend - begin < (u64)TILE ? pend - begin : (u64)TILE);
+    cnt_out = (u32)(pend - begin < (u64)TILE ? pend - begin : (u64)TILE);
+    p_out = lo;
+  };
+  auto fetch_regs = [&](u32 cnt) {
     const u64* src = in + begin;
     if (cnt == TILE && (begin & 1ull) == 0) {  // full, 16 B aligned tile: no per-element checks
 #pragma unroll
@@ -306,14 +349,34 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
         v[2 * j + 1] = i + 1 < cnt ? ld_stream(src + i + 1) : 0ull;
       }
     }
-    p_out = lo;
-    cnt_out = cnt;
+  };
+  auto tma_ok = [&](u32 cnt) { return TMAIN && cnt == TILE && (begin & 1ull) == 0; };
+  auto fetch_tma = [&]() {
+    if (tid == 0) {
+      mbar_expect_tx(mbar, TILE * 8u);
+      tma_load_1d((u32)__cvta_generic_to_shared(inbuf), in + begin, TILE * 8u, mbar);
+    }
   };
 
   u32 t = blockIdx.x;
-  u32 p = 0, cnt = 0;
-  if (t < total_tiles) load_tile(t, p, cnt);
+  u32 p = 0, cnt = 0, ph = 0;
+  bool via_tma = false;
+  if (t < total_tiles) {
+    locate(t, p, cnt);
+    via_tma = tma_ok(cnt);
+    if (via_tma) fetch_tma(); else fetch_regs(cnt);
+  }
   while (t < total_tiles) {
+    if (TMAIN && via_tma) {
+      mbar_wait(mbar, ph);
+      ph ^= 1u;
+#pragma unroll
+      for (int j = 0; j < IPT / 2; j++) {
+        const ulonglong2 x = *reinterpret_cast<const ulonglong2*>(inbuf + 2u * (j * kScThreads + tid));
+        v[2 * j] = x.x;
+        v[2 * j + 1] = x.y;
+      }
+    }
     u32 dr[IPT];  // digit << 16 | rank  (rank < TILE <= 65536, digit < 4096)
 #pragma unroll
     for (int j = 0; j < IPT; j++) {
@@ -383,14 +446,22 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
     }
     __syncthreads();
 
+    // the scan is done with p: locate the next tile; TMAIN: its bulk copy starts now (the staging
+    // buffer is free: every thread passed the barrier above with its tuples in registers)
+    const u32 cnt_cur = cnt;
+    t += gridDim.x;
+    if (t < total_tiles) {
+      locate(t, p, cnt);
+      via_tma = tma_ok(cnt);
+      if (via_tma) fetch_tma();
+    }
+
 #pragma unroll
     for (int j = 0; j < IPT; j++)
       if (v[j] != 0ull) tile[lbase[dr[j] >> 16] + (dr[j] & 0xffffu)] = v[j];
 
-    // v is dead: start the next tile's loads before flushing this one
-    const u32 cnt_cur = cnt;
-    t += gridDim.x;
-    if (t < total_tiles) load_tile(t, p, cnt);
+    // v is dead: start the next tile's register loads before flushing this one
+    if (t < total_tiles && !via_tma) fetch_regs(cnt);
     __syncthreads();
 
     if (BULK) {
