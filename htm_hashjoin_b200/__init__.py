@@ -21,8 +21,8 @@ import json
 import numpy as np
 
 from . import _capi
-from ._capi import (HJ_ALGO_ADAPTIVE, HJ_ALGO_ATOMIC, HJ_ALGO_NOCC, HJ_ALGO_RADIX, HJ_OK, HJ_PATH_GLOBAL,
-                    HJ_PATH_RADIX, hj_config, hj_result)
+from ._capi import (HJ_ALGO_ADAPTIVE, HJ_ALGO_ATOMIC, HJ_ALGO_NOCC, HJ_ALGO_RADIX, HJ_EINVAL, HJ_EOVERFLOW, HJ_OK,
+                    HJ_PATH_GLOBAL, HJ_PATH_RADIX, hj_config, hj_result)
 
 lib = _capi.load()  # raises ImportError if libhj_b200.so is missing
 
@@ -143,6 +143,22 @@ class HashJoin:
         res = hj_result()
         self._check(lib.hj_join(self._h, pr, n, ps, m, C.byref(res)), "hj_join")
         return res
+
+    def join_materialize(self, R, S, d_out=None, capacity=0):
+        """hj_join_materialize: every matching pair {r tuple, s tuple} into the device buffer d_out
+        (raw pointer, `capacity` pairs of 16 bytes).  d_out=None: count only.  Returns (result, n_pairs);
+        raises HJError(HJ_EOVERFLOW) when the buffer is too small (e.n_pairs tells the size needed)."""
+        pr, n = _ptr(R)
+        ps, m = _ptr(S)
+        res = hj_result()
+        need = C.c_uint64(0)
+        rc = lib.hj_join_materialize(self._h, pr, n, ps, m, int(d_out) if d_out else None, int(capacity),
+                                     C.byref(need), C.byref(res))
+        if rc != HJ_OK:
+            e = HJError(rc, "hj_join_materialize", lib.hj_last_error(self._h).decode())
+            e.n_pairs = need.value
+            raise e
+        return res, need.value
 
     def sample(self, R):
         p, n = _ptr(R)

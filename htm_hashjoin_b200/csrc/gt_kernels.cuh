@@ -250,6 +250,59 @@ __global__ void __launch_bounds__(256) gt_ovf_insert_kernel(const u64* __restric
   }
 }
 
+// Locality pre-check of the adaptive switch: the span signal of the sampling round WITHOUT the table
+// (read-only, same chunk geometry as gt_build_kernel<2, false, true>).  If the slots of a CTA chunk
+// already lie too far apart the radix join is taken at once and the table is never cleared -- at
+// |R| = 2^27 the clear of the 2 GiB table alone cost 330 us of a 2.6 ms join.
+__global__ void __launch_bounds__(kGtThreads)
+gt_span_kernel(const u64* __restrict__ R, SegMap sm, u64 mask, u64 key_mask, u64* __restrict__ ctr) {
+  constexpr int IPT = 2, TILE = kGtThreads * IPT;
+  const u32 tid = threadIdx.x;
+  const u64 chunks_per_seg = (sm.seg_len + TILE - 1) / TILE;
+  const u64 nchunks = chunks_per_seg * sm.nslices;
+  __shared__ u64 smin[kGtThreads / 32], smax[kGtThreads / 32];
+  u64 span = 0, chunks = 0, sampled = 0;
+  for (u64 c = blockIdx.x; c < nchunks; c += gridDim.x) {
+    const u64 slice = c / chunks_per_seg;
+    const u64 w = c - slice * chunks_per_seg;
+    const u64 seg_begin = slice * sm.slice_stride + sm.slice_off;
+    u64 seg_end = seg_begin + sm.seg_len;
+    if (seg_end > sm.n) seg_end = sm.n;
+    const u64 base = seg_begin + w * TILE;
+    u64 lo = ~0ull, hi = 0ull;
+#pragma unroll
+    for (int j = 0; j < IPT; j++) {
+      const u64 i = base + (u64)j * kGtThreads + tid;
+      const u64 v = i < seg_end ? ld_stream(R + i) : 0ull;
+      if (v) {
+        const u64 hm = (v & key_mask) & mask;
+        lo = hm < lo ? hm : lo;
+        hi = hm > hi ? hm : hi;
+        sampled++;
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+      hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+    }
+    if (lane_id() == 0) { smin[tid >> 5] = lo; smax[tid >> 5] = hi; }
+    __syncthreads();
+    if (tid == 0) {
+      for (int w2 = 1; w2 < kGtThreads / 32; w2++) { lo = min(lo, smin[w2]); hi = max(hi, smax[w2]); }
+      if (hi >= lo) { span += hi - lo + 1; chunks += 1; }
+    }
+    __syncthreads();
+  }
+  u64 sv[1] = {sampled};
+  u64* const d[1] = {ctr + C_SAMPLED};
+  block_sum_atomic<1, kGtThreads>(sv, d);
+  if (tid == 0 && chunks) {
+    atomicAdd(ctr + C_SPAN, span);
+    atomicAdd(ctr + C_CHUNKS, chunks);
+  }
+}
+
 // ---- probe --------------------------------------------------------------------
 // AtomicHashBuild.hpp:75-83 per S tuple, plus the overflow table.  Per-thread
 // counts are reduced warp -> CTA -> one atomicAdd per CTA ("warp-aggregated").

@@ -20,6 +20,7 @@
 #include "rx_kernels.cuh"
 #include "rx_join32.cuh"
 #include "rx_joinl2.cuh"
+#include "rx_joinmat.cuh"
 
 using namespace hj;
 
@@ -62,6 +63,7 @@ struct hj_handle {
   RelBufs rb[2];
   DevBuf flush;
   DevBuf peer_ptrs;  // device copy of the peers' pass-1 buffer pointers (fused exchange)
+  DevBuf mat_cnt;    // per-partition pair counts / offsets of the materialising join
   u32 launches = 0;
   char err[256];
 };
@@ -287,6 +289,19 @@ double contention_of(hj_handle* h) {
   return locality + retry;
 }
 
+// Default switch point.  The span signal says how far apart the slots of one CTA chunk lie; what that
+// costs depends on how much of the table the 126 MB L2 holds anyway: a table of up to ~2x L2 (|R| = 2^24)
+// stays cheaper than the radix join until the input is fully shuffled (threshold 0.25), while at
+// |R| = 2^27 (2 GiB table) the radix join wins from W = 2^11 on, where the signal is only 3e-4
+// (experiments/results/w_sweep*.jsonl).  Between the two the threshold falls with the cube of
+// 2*L2 / table bytes -- fitted to those two sizes, checked at 2^25 and 2^26.
+double default_threshold(const hj_handle* h) {
+  const double table_bytes = 8.0 * (double)h->slots;
+  double r = 2.0 * (double)h->l2_bytes / (table_bytes > 0 ? table_bytes : 1.0);
+  if (r > 1.0) r = 1.0;
+  return 0.25 * r * r * r;
+}
+
 SegMap whole(u64 n) {
   SegMap sm;
   sm.n = n;
@@ -325,6 +340,22 @@ int run_sample(hj_handle* h, const u64* dR, u64 n, u64* stride_out, u64* len_out
   *stride_out = stride;
   *len_out = slen;
   return launch_build(h, dR, sm, false, true, 2);
+}
+
+// locality pre-check (gt_span_kernel): same sample geometry, no table
+int run_span(hj_handle* h, const u64* dR, u64 n) {
+  u64 stride, slen;
+  sample_geometry(h, n, &stride, &slen);
+  SegMap sm;
+  sm.n = n; sm.seg_len = slen; sm.slice_stride = stride; sm.slice_off = 0; sm.nslices = stride ? 64 : 1;
+  const u64 chunks = ((slen + kGtThreads * 2 - 1) / (kGtThreads * 2)) * sm.nslices;
+  if (chunks == 0) return HJ_OK;
+  int grid = grid_for(h, (const void*)gt_span_kernel, kGtThreads, 0);
+  if ((u64)grid > chunks) grid = (int)chunks;
+  gt_span_kernel<<<grid, kGtThreads, 0, h->stream>>>(dR, sm, h->mask, h->cfg.key_mask, h->ctr);
+  h->launches++;
+  CK(cudaGetLastError());
+  return HJ_OK;
 }
 
 int run_build_rest(hj_handle* h, const u64* dR, u64 n, u64 stride, u64 slen, bool nocc, u32 ipt) {
@@ -616,9 +647,17 @@ int radix_partition_rel_opt(hj_handle* h, const u64* in, u64 n, RelBufs& rb, con
   return HJ_OK;
 }
 
+// materialisation request (hj_join_materialize): out may be null (count only)
+struct MatReq {
+  ulonglong2* out;
+  u64 capacity;  // pairs
+  u64 needed;    // pairs the join produces (set after the count pass)
+  bool written;
+};
+
 int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS, u64 m, bool pendS, hj_result* res,
                    bool pre1 = false, bool force_exact = false, const u64* offR1 = nullptr,
-                   const u64* offS1 = nullptr) {
+                   const u64* offS1 = nullptr, MatReq* mat = nullptr) {
   RadixPlan pl;
   int rc;
   if ((rc = plan_radix(h, n, &pl))) {
@@ -653,6 +692,73 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
     if (rc) return rc;
   }
   mark(h, E_JOIN0);
+  if (mat) {
+    // count / scan / write over the partitions (rx_joinmat.cuh); shared-memory partitions of 32-bit keys only
+    if (use_l2 || !dS || pl.bits < 1 || (h->cfg.key_mask & 0xffffffffull) != 0xffffffffull) {
+      snprintf(h->err, sizeof(h->err), "materialise: needs shared-memory partitions (fan-out 2^%u too low for |R|) "
+               "and 32-bit keys", pl.bits);
+      return HJ_EINVAL;
+    }
+    if ((rc = ensure(h, h->mat_cnt, (u64)nparts + 1))) return rc;
+    const void* kc = (const void*)rx_join32_mat_kernel<1024, 2, false>;
+    const void* kw = (const void*)rx_join32_mat_kernel<1024, 2, true>;
+    cudaFuncAttributes fa;
+    CK(cudaFuncGetAttributes(&fa, kw));
+    size_t avail = h->smem_optin - fa.sharedSizeBytes - 1024;
+    u64 want = (n >> pl.bits) + 1;
+    if (want < 64) want = 64;
+    u32 nbuckets = (u32)(want * 32 <= avail ? want * 2 : avail / 16);  // 4 slots per expected R tuple, W = 2
+    nbuckets &= ~1u;
+    const size_t smem = (size_t)nbuckets * 16;
+    CK(cudaFuncSetAttribute(kc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CK(cudaFuncSetAttribute(kw, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int grid = grid_for(h, kw, 1024, smem);
+    if ((u32)grid > nparts) grid = (int)nparts;
+    const u64 *aR = h->rb[0].out.p, *aoR = opt ? h->rb[0].cursors.p : h->rb[0].offsets.p, *aS = h->rb[1].out.p,
+              *aoS = opt ? h->rb[1].cursors.p : h->rb[1].offsets.p;
+    u32 a_np = nparts, a_bits = pl.bits;
+    u64* a_ctr = h->ctr;
+    u64 a_capR = capR, a_capS = capS;
+    u64* a_cnt = h->mat_cnt.p;
+    ulonglong2* a_out = mat->out;
+    void* args[] = {&aR, &aoR, &aS, &aoS, &a_np, &a_bits, &nbuckets, &a_ctr, &a_capR, &a_capS, &a_cnt, &a_out};
+    CK(cudaLaunchKernel(kc, dim3(grid), dim3(1024), args, smem, h->stream));
+    rx_mat_scan_kernel<<<1, 1024, 0, h->stream>>>(h->mat_cnt.p, nparts, h->ctr + C_MAT_TOTAL);
+    h->launches += 2;
+    if ((rc = fetch_counters(h))) return rc;
+    if (opt && h->h_ctr[C_OPT_OVF]) {
+      h->no_optimistic = true;
+      return run_radix_join(h, dR, n, false, dS, m, false, res, pre1, true, nullptr, nullptr, mat);
+    }
+    if (h->h_ctr[C_KEY_HI]) {
+      snprintf(h->err, sizeof(h->err), "materialise: keys wider than 32 bits");
+      return HJ_EINVAL;
+    }
+    mat->needed = h->h_ctr[C_MAT_TOTAL];
+    mat->written = false;
+    if (mat->out && mat->needed <= mat->capacity) {
+      CK(cudaLaunchKernel(kw, dim3(grid), dim3(1024), args, smem, h->stream));
+      h->launches++;
+      mat->written = true;
+    }
+    mark(h, E_JOIN);
+    mark(h, E_END);
+    if ((rc = fetch_counters(h))) return rc;
+    if (res) {
+      fill_common(h, res);
+      if (!mat->written) res->matches = mat->needed;
+      res->path_taken = HJ_PATH_RADIX;
+      res->radix_bits = pl.bits;
+      res->passes = pl.passes;
+      // two join passes read both relations, the write pass emits 16 B per pair
+      res->hbm_bytes = 8ull * (2 * pl.passes + 2) * (n + m) + (mat->written ? 16ull * mat->needed : 0ull);
+    }
+    if (mat->out && !mat->written) {
+      snprintf(h->err, sizeof(h->err), "materialise: %llu pairs do not fit the buffer of %llu", mat->needed, mat->capacity);
+      return HJ_EOVERFLOW;
+    }
+    return HJ_OK;
+  }
   if (use_l2) {
     Digit full;
     memset(&full, 0, sizeof(full));
@@ -1002,6 +1108,30 @@ int hj_join(hj_handle* h, const uint64_t* R, uint64_t n, const uint64_t* S, uint
   if ((rc = prepare_table(h, n))) return rc;
   mark(h, E_T0);
   CK(cudaMemsetAsync(h->ctr, 0, C_COUNT * sizeof(u64), h->stream));
+  if (algo == HJ_ALGO_ADAPTIVE && is_device_ptr(R)) {
+    // Locality pre-check on a device-resident R: the span signal needs no table, so an input that is
+    // going to the radix join anyway never pays for clearing one.  (Host inputs keep the order below:
+    // their clear hides under the R copy.)
+    if ((rc = run_span(h, (const u64*)R, n))) return rc;
+    if ((rc = fetch_counters(h))) return rc;
+    const double locality = contention_of(h);
+    const double thr0 = h->cfg.adaptive_threshold > 0 ? h->cfg.adaptive_threshold : default_threshold(h);
+    if (locality > thr0) {
+      const u64 sampled = h->h_ctr[C_SAMPLED];
+      mark(h, E_CLEAR);
+      mark(h, E_SAMPLE);
+      h->built = false;
+      if ((rc = stage(h, (const u64*)S, m, h->stageS, &dS, E_CPS, &pendS))) return rc;
+      rc = run_radix_join(h, (const u64*)R, n, false, dS, m, pendS, res);
+      if (res && rc == HJ_OK) {
+        res->contention = locality;
+        res->sampled = sampled;
+        res->us_sample = span_us(h, E_T0, E_SAMPLE);
+      }
+      return rc;
+    }
+    CK(cudaMemsetAsync(h->ctr, 0, C_COUNT * sizeof(u64), h->stream));
+  }
   if ((rc = zero_async(h, h->table.p, h->slots))) return rc;
   mark(h, E_CLEAR);
   mark(h, E_CP0, h->copy_stream);
@@ -1044,7 +1174,7 @@ int hj_join(hj_handle* h, const uint64_t* R, uint64_t n, const uint64_t* S, uint
   const double contention = contention_of(h);
   const u64 sampled = h->h_ctr[C_SAMPLED], retries = h->h_ctr[C_CAS_RETRIES], sectors = h->h_ctr[C_SECTORS];
   const float us_sample = span_us(h, E_CLEAR, E_SAMPLE), us_clear = span_us(h, E_T0, E_CLEAR);
-  const double thr = h->cfg.adaptive_threshold > 0 ? h->cfg.adaptive_threshold : 0.25;
+  const double thr = h->cfg.adaptive_threshold > 0 ? h->cfg.adaptive_threshold : default_threshold(h);
   if (contention > thr) {
     // radix path; the sampled prefix is abandoned with the table
     h->built = false;
@@ -1065,6 +1195,29 @@ int hj_join(hj_handle* h, const uint64_t* R, uint64_t n, const uint64_t* S, uint
     res->contention = contention;
     res->us_sample = us_sample;
   }
+  return rc;
+}
+
+int hj_join_materialize(hj_handle* h, const uint64_t* R, uint64_t n, const uint64_t* S, uint64_t m, uint64_t* out_pairs,
+                        uint64_t capacity_pairs, uint64_t* n_pairs, hj_result* res) {
+  if (!h || !R || !n || !S || !m) return HJ_EINVAL;
+  if (out_pairs && (!is_device_ptr(out_pairs) || ((uintptr_t)out_pairs & 15))) {
+    snprintf(h->err, sizeof(h->err), "materialise: out_pairs must be a 16-byte aligned device pointer");
+    return HJ_EINVAL;
+  }
+  CK(cudaSetDevice(h->device));
+  if (res) memset(res, 0, sizeof(*res));
+  reset_events(h);
+  int rc;
+  const u64 *dR = nullptr, *dS = nullptr;
+  bool pendR = false, pendS = false;
+  mark(h, E_T0);
+  mark(h, E_CP0, h->copy_stream);
+  if ((rc = stage(h, (const u64*)R, n, h->stageR, &dR, E_CPR, &pendR))) return rc;
+  if ((rc = stage(h, (const u64*)S, m, h->stageS, &dS, E_CPS, &pendS))) return rc;
+  MatReq mat{reinterpret_cast<ulonglong2*>(out_pairs), capacity_pairs, 0, false};
+  rc = run_radix_join(h, dR, n, pendR, dS, m, pendS, res, false, false, nullptr, nullptr, &mat);
+  if (n_pairs) *n_pairs = mat.needed;
   return rc;
 }
 

@@ -133,6 +133,19 @@ int hj_probe(hj_handle *h, const uint64_t *S, uint64_t m, hj_result *res);
  * with the probe of histogram_join (:306-369) restored. */
 int hj_join(hj_handle *h, const uint64_t *R, uint64_t n, const uint64_t *S,
             uint64_t m, hj_result *res);
+
+/* Result materialisation.  The reference only counts ("TODO: we don't
+ * materialize", mc/src/no_partitioning_join.c:301, parallel_radix_join.c:359); this emits the
+ * pairs.  Radix join of R and S (host or device pointers) whose every matching pair is written
+ * to out_pairs as two uint64_t {r tuple, s tuple}: one dense DEVICE array (16-byte aligned) of
+ * *n_pairs entries; pairs of one radix partition are contiguous, order inside a partition is
+ * unspecified.  Count / scan / write: with out_pairs == NULL only the count pass runs and
+ * *n_pairs says how large the buffer must be; with capacity_pairs < *n_pairs nothing is written
+ * and HJ_EOVERFLOW is returned.  Needs keys of at most 32 bits and a fan-out that puts an R
+ * partition into shared memory (the default plan; else HJ_EINVAL).  res->matches / checksum as
+ * hj_join; the handle may have any cfg.algo. */
+int hj_join_materialize(hj_handle *h, const uint64_t *R, uint64_t n, const uint64_t *S, uint64_t m,
+                        uint64_t *out_pairs, uint64_t capacity_pairs, uint64_t *n_pairs, hj_result *res);
 /* HTMHashBuild.hpp:100-156 sampling round: insert K*16384 tuples of each of
  * the 64 slices of R into the (cleared) global table, measure contention.
  * The sampled prefix stays in the table, as in the reference (:170). */

@@ -79,6 +79,25 @@ class Oracle:
         self.lib.orc_true_join(_p(R), R.size, _p(S), S.size, key_mask, C.byref(m), C.byref(c))
         return m.value, c.value
 
+    def true_join_pairs(self, R, S, key_bits=32):
+        """Every matching pair (r tuple, s tuple) of the true equi-join on the low key_bits, as an
+        (n_pairs, 2) uint64 array sorted lexicographically -- the checker of hj_join_materialize (the
+        reference never materialises: no_partitioning_join.c:301).  numpy; count and checksum are
+        cross-checked against orc_true_join by the caller."""
+        mask = np.uint64((1 << key_bits) - 1)
+        R = R[R != 0]
+        S = S[S != 0]
+        Rs = R[np.argsort(R & mask, kind="stable")]
+        rk = Rs & mask
+        lo = np.searchsorted(rk, S & mask, side="left")
+        hi = np.searchsorted(rk, S & mask, side="right")
+        cnt = (hi - lo).astype(np.int64)
+        s_rep = np.repeat(S, cnt)
+        start = np.repeat(lo, cnt)
+        within = np.arange(int(cnt.sum()), dtype=np.int64) - np.repeat(np.cumsum(cnt) - cnt, cnt)
+        pairs = np.stack([Rs[start + within], s_rep], axis=1) if cnt.sum() else np.empty((0, 2), np.uint64)
+        return pairs[np.lexsort((pairs[:, 1], pairs[:, 0]))]
+
     def radix_partition(self, a, shift, bits):
         out = np.empty_like(a)
         off = np.empty((1 << bits) + 1, dtype=np.uint64)

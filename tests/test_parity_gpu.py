@@ -366,3 +366,97 @@ def test_reference_named_entry_points_and_cli(hj, oracle):
     Ru = hj.generate_data("uniform", n)
     assert line["inputSum"] == oracle.sum(Ru) and line["matches"] == n
     assert line["outputSum"] == line["inputSum"]
+
+
+# ---- result materialisation and skewed inputs (8f-3) ---------------------------------
+def _zipf_fk(m, n, z, seed):
+    """S keys drawn from a zipf(z) distribution over a random permutation of R's keys 1..n, payload =
+    position (mc's --skew workload, genzipf.c: alphabet permutation + inverse-cdf lookup; numpy instead
+    of serial rand(), so not bit-identical to the reference's generator)."""
+    rng = np.random.default_rng(seed)
+    alphabet = rng.permutation(n).astype(np.uint64) + np.uint64(1)
+    cdf = np.cumsum(1.0 / np.arange(1, n + 1, dtype=np.float64) ** z)
+    cdf /= cdf[-1]
+    keys = alphabet[np.minimum(np.searchsorted(cdf, rng.random(m)), n - 1)]
+    return keys | (np.arange(m, dtype=np.uint64) << np.uint64(32))
+
+
+def _sorted_pairs(h, d_out, n_pairs):
+    flat = h.to_host(d_out, 2 * n_pairs).reshape(-1, 2)
+    return flat[np.lexsort((flat[:, 1], flat[:, 0]))]
+
+
+@pytest.mark.parametrize("case", ["pk_fk", "duplicates", "zipf", "ragged"])
+def test_materialize_pairs_equal_oracle(hj, oracle, case):
+    """hj_join_materialize: the emitted pairs, sorted, are exactly the oracle's pairs; count and checksum
+    agree with the counting join; pairs are dense (no gaps)."""
+    if case == "pk_fk":
+        R, S = hj.mc_relation_pk(1 << 16), hj.mc_relation_fk(1 << 19, 1 << 16)
+    elif case == "duplicates":  # both sides repeat keys: several pairs per probe tuple
+        R = hj.generate_data("uniform", 1 << 16, 1 << 13, 16) | (np.arange(1 << 16, dtype=np.uint64) << np.uint64(32))
+        S = hj.generate_data("uniform", 1 << 17, 1 << 13, 16) | (np.arange(1 << 17, dtype=np.uint64) << np.uint64(40))
+    elif case == "zipf":
+        R, S = hj.mc_relation_pk(1 << 16), _zipf_fk(1 << 19, 1 << 16, 1.0, 7)
+    else:  # odd sizes, keys without partner
+        R = hj.generate_data("shuffle", (1 << 15) + 77)
+        S = hj.generate_data("shuffle", (1 << 16) + 5)
+    want = oracle.true_join_pairs(R, S)
+    cnt, chk = oracle.true_join(R, S, 0xFFFFFFFF)
+    assert want.shape[0] == cnt
+    with hj.HashJoin("radix", key_mask=0xFFFFFFFF) as h:
+        res, need = h.join_materialize(R, S)  # count only
+        assert need == cnt and res.matches == cnt
+        d_out = h.device_alloc(max(need, 1) * 16)
+        res, n_pairs = h.join_materialize(R, S, d_out, need)
+        assert n_pairs == cnt and (res.matches, res.checksum) == (cnt, chk)
+        got = _sorted_pairs(h, d_out, n_pairs)
+        assert np.array_equal(got, want)
+        plain = h.join(R, S)
+        assert (plain.matches, plain.checksum) == (cnt, chk)
+        h.device_free(d_out)
+
+
+def test_materialize_buffer_too_small_reports_size(hj):
+    R, S = hj.mc_relation_pk(1 << 14), hj.mc_relation_fk(1 << 16, 1 << 14)
+    with hj.HashJoin("radix", key_mask=0xFFFFFFFF) as h:
+        d_out = h.device_alloc(1000 * 16)
+        with pytest.raises(hj.HJError) as e:
+            h.join_materialize(R, S, d_out, 1000)
+        assert e.value.code == hj.HJ_EOVERFLOW and e.value.n_pairs == 1 << 16
+        h.device_free(d_out)
+
+
+def test_materialize_large_properties(hj):
+    """2^24 x 2^26 FK join: every S tuple appears exactly once with its R partner (size-independent
+    properties: pair count, key equality of the halves, sum of the s halves == sum of S)."""
+    n, m = 1 << 24, 1 << 26
+    with hj.HashJoin("radix") as h:
+        dR, dS = h.device_alloc(n * 8), h.device_alloc(m * 8)
+        h.generate(1, 0, n, n, 12345, dR)
+        h.generate(1, 0, m, n, 54321, dS)
+        d_out = h.device_alloc(m * 16)
+        res, n_pairs = h.join_materialize((dR, n), (dS, m), d_out, m)
+        assert n_pairs == m == res.matches
+        plain = h.join((dR, n), (dS, m))
+        assert plain.checksum == res.checksum
+        pairs = h.to_host(d_out, 2 * m).reshape(-1, 2)
+        assert np.array_equal(pairs[:, 0] & np.uint64(0xFFFFFFFF), pairs[:, 1] & np.uint64(0xFFFFFFFF))
+        S = h.to_host(dS, m)
+        assert int(pairs[:, 1].sum(dtype=np.uint64)) == int(S.sum(dtype=np.uint64))
+        assert int((pairs[:, 0].sum(dtype=np.uint64) + pairs[:, 1].sum(dtype=np.uint64)) & np.uint64(2**64 - 1)) == res.checksum
+        for p in (dR, dS, d_out):
+            h.device_free(p)
+
+
+@pytest.mark.parametrize("z", [0.5, 1.0, 1.5])
+@pytest.mark.parametrize("algo", ["atomic", "radix", "adaptive"])
+def test_zipf_skewed_probe_side(hj, oracle, algo, z):
+    """mc --skew: a zipf-distributed foreign key.  Heavy hitters make S partitions very uneven (the
+    histogram-free regions overflow and the exact layout takes over); the join result must not change."""
+    n, m = 1 << 18, 1 << 21
+    R, S = hj.mc_relation_pk(n), _zipf_fk(m, n, z, 11)
+    want = oracle.true_join(R, S, 0xFFFFFFFF)
+    assert want[0] == m
+    with hj.HashJoin(algo, key_mask=0xFFFFFFFF) as h:
+        res = h.join(R, S)
+        assert (res.matches, res.checksum) == want
