@@ -63,6 +63,7 @@ struct hj_handle {
   RelBufs rb[2];
   DevBuf flush;
   DevBuf peer_ptrs;  // device copy of the peers' pass-1 buffer pointers (fused exchange)
+  DevBuf tasks;      // join tasks (partition, S slice) of rx_join32 (skew handling)
   DevBuf mat_cnt;    // per-partition pair counts / offsets of the materialising join
   u32 launches = 0;
   char err[256];
@@ -825,9 +826,18 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
     u32 a_np = nparts, a_bits = pl.bits;
     u64* a_ctr = h->ctr;
     u64 a_capR = capR, a_capS = capS;
-    void* args[] = {&aR, &aoR, &aS, &aoS, &a_np, &a_bits, &nbuckets, &a_ctr, &a_capR, &a_capS};
+    // tasks = (partition, S slice): S partitions beyond 4x the mean are probed by several CTAs
+    u64 slice = 4 * (m >> pl.bits);
+    if (slice < 32768) slice = 32768;
+    if (getenv("HJ_JOIN_SLICE")) slice = strtoull(getenv("HJ_JOIN_SLICE"), nullptr, 10);
+    slice &= ~1ull;
+    const u64 max_tasks = (u64)nparts + m / slice + 1;
+    if ((rc = ensure(h, h->tasks, max_tasks))) return rc;
+    rx_tasks_kernel<<<1, 1024, 0, h->stream>>>(aoS, nparts, capS, slice, h->tasks.p, max_tasks, h->ctr);
+    const u64* a_tasks = h->tasks.p;
+    void* args[] = {&aR, &aoR, &aS, &aoS, &a_np, &a_bits, &nbuckets, &a_ctr, &a_capR, &a_capS, &a_tasks, &slice};
     CK(cudaLaunchKernel(k, dim3(grid), dim3(threads), args, smem, h->stream));
-    h->launches++;
+    h->launches += 2;
   }
   if (!use_l2) {
     size_t smem = (size_t)pl.slots * 8;

@@ -29,6 +29,7 @@ enum Counter {
   C_KEY_HI,          // OR of the key bits above bit 31 over every tuple rx_hist saw (0: rx_join32 applies)
   C_OPT_OVF,         // a region of the histogram-free layout overflowed: redo on the exact path
   C_TILE0, C_TILE1,  // tile tickets of the L2 join kernels (rx_joinl2.cuh)
+  C_NTASKS,          // join tasks = (partition, S slice) pairs built by rx_tasks_kernel (skew handling)
   C_MAT_TOTAL,       // pairs the materialising join will write (rx_joinmat.cuh, after the count pass)
   C_COUNT = 24
 };

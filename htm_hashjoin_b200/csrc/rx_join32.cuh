@@ -176,12 +176,65 @@ __device__ __noinline__ u64 j32_probe_multi(u32 base, u32 nbuckets, u32 k) {
   return ((u64)cnt << 32) | pay;
 }
 
+// Skew handling (the reference's SKEW_HANDLING task splitting, parallel_radix_join.c:958-1055): the
+// unit of work is a TASK = (partition p, slice k of S_p), S_p cut into slices of `slice` tuples, so a
+// heavy-hitter partition (zipf foreign keys) is probed by many CTAs, each with its own copy of R_p's
+// table, instead of serialising the whole join behind one CTA (z = 1.0: join 2.05 ms of a 3.3 ms
+// total before).  With balanced partitions every partition is one task and nothing changes.
+// One CTA builds tasks[t] = p | k << 32, partition-major, and ctr[C_NTASKS].
+__global__ void __launch_bounds__(1024)
+rx_tasks_kernel(const u64* __restrict__ offS, u32 nparts, u64 capS, u64 slice, u64* __restrict__ tasks,
+                u64 max_tasks, u64* __restrict__ ctr) {
+  __shared__ u32 warp_tot[32];
+  __shared__ u32 s_carry;
+  const u32 tid = threadIdx.x, lane = tid & 31u, wid = tid >> 5;
+  if (tid == 0) s_carry = 0;
+  __syncthreads();
+  for (u32 b0 = 0; b0 < nparts; b0 += 1024u) {
+    const u32 p = b0 + tid;
+    u32 nt = 0;
+    if (p < nparts) {
+      const u64 s0 = capS ? p * capS : offS[p];
+      const u64 s1 = capS ? (offS[p] < s0 + capS ? offS[p] : s0 + capS) : offS[p + 1];
+      const u64 ns = s1 - s0;
+      nt = ns <= slice ? 1u : (u32)((ns + slice - 1) / slice);
+    }
+    u32 incl = nt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const u32 y = __shfl_up_sync(0xffffffffu, incl, o);
+      if ((int)lane >= o) incl += y;
+    }
+    if (lane == 31) warp_tot[wid] = incl;
+    __syncthreads();
+    if (wid == 0) {
+      const u32 w = warp_tot[lane];
+      u32 wi = w;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const u32 y = __shfl_up_sync(0xffffffffu, wi, o);
+        if ((int)lane >= o) wi += y;
+      }
+      warp_tot[lane] = wi - w;
+    }
+    __syncthreads();
+    const u32 carry = s_carry;
+    u64 first = (u64)carry + warp_tot[wid] + incl - nt;
+    for (u32 k = 0; k < nt; k++)
+      if (first + k < max_tasks) tasks[first + k] = (u64)p | ((u64)k << 32);
+    __syncthreads();
+    if (tid == 1023) s_carry = carry + warp_tot[wid] + incl;
+    __syncthreads();
+  }
+  if (tid == 0) ctr[C_NTASKS] = (u64)s_carry < max_tasks ? (u64)s_carry : max_tasks;
+}
+
 // Dynamic shared memory: nbuckets * 8 * W bytes.
 template <int THREADS, int BATCH, int MINB, int W>
 __global__ void __launch_bounds__(THREADS, MINB)
 rx_join32_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const u64* __restrict__ Sp,
                  const u64* __restrict__ offS, u32 nparts, u32 radix_bits, u32 nbuckets, u64* __restrict__ ctr,
-                 u64 capR, u64 capS) {
+                 u64 capR, u64 capS, const u64* __restrict__ tasks, u64 slice) {
   static_assert(BATCH % 2 == 0, "BATCH tuples = BATCH/2 16-byte loads");
   static_assert(W == 2 || W == 4, "bucket of 2 or 4 keys");
   if (ctr[C_KEY_HI] != 0ull) return;  // keys wider than 32 bits: rx_join_kernel handles this join
@@ -205,17 +258,23 @@ rx_join32_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const
   u64 matches = 0, key_sum = 0, maxpart = 0, chunked = 0;
   u32 pay_sum = 0;
 
-  for (u32 p = blockIdx.x; p < nparts; p += gridDim.x) {
+  const u32 ntasks = (u32)ctr[C_NTASKS];
+  for (u32 t = blockIdx.x; t < ntasks; t += gridDim.x) {
+    const u64 task = tasks[t];
+    const u32 p = (u32)task;
+    const u64 k = task >> 32;
     // exact layout: partition p = [off[p], off[p+1]); histogram-free layout (cap != 0, see ScOpt
     // in rx_kernels.cuh): [p*cap, min(off[p], (p+1)*cap)) with off = the scatter's final cursors
     const u64 r0 = capR ? p * capR : offR[p];
     const u64 r1 = capR ? (offR[p] < r0 + capR ? offR[p] : r0 + capR) : offR[p + 1];
-    const u64 s0 = capS ? p * capS : offS[p];
-    const u64 s1 = capS ? (offS[p] < s0 + capS ? offS[p] : s0 + capS) : offS[p + 1];
+    u64 s0 = capS ? p * capS : offS[p];
+    u64 s1 = capS ? (offS[p] < s0 + capS ? offS[p] : s0 + capS) : offS[p + 1];
+    s0 += k * slice;  // slice k of S_p (k == 0 and one slice: the whole partition)
+    if (s1 - s0 > slice) s1 = s0 + slice;
     const u64 nr = r1 - r0;
-    maxpart = nr > maxpart ? nr : maxpart;
-    if (nr == 0 || s1 == s0) continue;
-    if (nr > chunk_cap) chunked++;
+    if (k == 0) maxpart = nr > maxpart ? nr : maxpart;
+    if (nr == 0 || s1 <= s0) continue;
+    if (nr > chunk_cap && k == 0) chunked++;
     for (u64 c0 = r0; c0 < r1; c0 += chunk_cap) {
       const u64 c1 = c0 + chunk_cap < r1 ? c0 + chunk_cap : r1;
       __syncthreads();  // the previous probe is over before the table is cleared
