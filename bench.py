@@ -43,6 +43,10 @@ def parse_args():
     ap.add_argument("--r-dist", default="shuffle", help="DataGen distribution of R at N=1 (host generated)")
     ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
                     help="N>1: exchange fused with radix pass 1 over peer memory, or partition + NCCL all-to-all")
+    ap.add_argument("--chunks", type=int, default=1,
+                    help="fused exchange: split S into this many chunks and overlap the exchange of chunk c+1 "
+                         "with pass 2 + join of chunk c (a join is additive over disjoint parts of S)")
+    ap.add_argument("--peer-ctas", type=int, default=48, help="CTAs of an overlapped peer scatter (NVLink-bound)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--extras", action="store_true", help="also time configs[0] (atomic 16M uniform) etc.")
@@ -270,7 +274,15 @@ class Rank:
             handles = self.exchange.exchange_ipc_handles((self.h.ipc_export(self.recvR), self.h.ipc_export(self.recvS)))
             self.peerR = [self.recvR if g == self.rank else self.h.ipc_open(handles[g][0]) for g in range(G)]
             self.peerS = [self.recvS if g == self.rank else self.h.ipc_open(handles[g][1]) for g in range(G)]
-            self.cnt = torch.zeros(2 * G * self.f1, dtype=torch.int64, device=dev)
+            self.chunks = max(1, args.chunks)
+            self.peer_ctas = args.peer_ctas
+            self.cnt = torch.zeros((1 + self.chunks) * G * self.f1, dtype=torch.int64, device=dev)
+            if self.chunks > 1:
+                assert self.m % (2 * self.chunks) == 0
+                # second handle = second stream: the exchange of chunk c+1 runs beside the join of chunk c
+                self.hx = hj.HashJoin(args.algo, device=self.local, num_partitions=1 << bits, passes=2,
+                                      pass1_bits=self.b1)
+                self.cap_c = (cap_s // self.chunks) & ~1  # per-chunk receive buffer (16-byte aligned)
         elif G > 1:
             self.sendR = torch.empty(self.n, dtype=torch.int64, device=dev)
             self.sendS = torch.empty(self.m, dtype=torch.int64, device=dev)
@@ -308,7 +320,7 @@ class Rank:
         ex = self.exchange
         dom_bits = ex.domain_bits_for(self.domain)
         if self.fused:
-            return self.step_fused(dom_bits)
+            return self.step_fused_chunked(dom_bits) if self.chunks > 1 else self.step_fused(dom_bits)
         # 1. split both slices by destination GPU (high key bits of the key domain)
         self.h.exchange_partition(self.dR.data_ptr(), self.n, G, dom_bits, self.sendR.data_ptr(), self.offR.data_ptr())
         self.h.exchange_partition(self.dS.data_ptr(), self.m, G, dom_bits, self.sendS.data_ptr(), self.offS.data_ptr())
@@ -363,6 +375,59 @@ class Rank:
         out = ex.reduce_result(res.matches, res.checksum, "cuda")
         t.append(time.perf_counter())
         self.fused_ms = [round((b - a) * 1e3, 3) for a, b in zip(t, t[1:])]  # hist, counts, scatter, barrier, join, reduce
+        return out
+
+    def step_fused_chunked(self, dom_bits):
+        """step_fused with S cut into chunks by position: join(R, S) = sum over chunks of join(R, S_c), so
+        chunk c can be joined (handle h) while chunk c+1 still travels (handle hx, a few CTAs: NVLink-bound)."""
+        torch, G, ex, gf, C = self.torch, self.world, self.exchange, self.world * self.f1, self.chunks
+        mc = self.m // C
+        t = [time.perf_counter()]
+        self.hx.peer_hist(self.dR.data_ptr(), self.n, G, dom_bits, self.b1, self.cnt.data_ptr())
+        for c in range(C):
+            self.hx.peer_hist(self.dS.data_ptr() + 8 * c * mc, mc, G, dom_bits, self.b1,
+                              self.cnt.data_ptr() + 8 * gf * (1 + c))
+        t.append(time.perf_counter())
+        allc = ex.gather_counts(self.cnt)
+        cur, recv, off, own = [], [], [], 0
+        for c in range(1 + C):
+            a = allc[:, c * gf:(c + 1) * gf].contiguous()
+            cu, rc, of = ex.peer_cursors(a, self.rank, G, self.f1)
+            cur.append(cu); recv.append(rc[self.rank]); off.append(of)
+            own = own + a[self.rank, self.rank * self.f1:(self.rank + 1) * self.f1].sum()
+        sizes = torch.stack(recv + [own]).tolist()  # one sync: cursors ready too
+        nr, ns, own = sizes[0], sizes[1:1 + C], sizes[-1]
+        if nr > self.cap[0] or max(ns) > self.cap_c:
+            raise RuntimeError("exchange receive buffer too small")
+        t.append(time.perf_counter())
+        peer_c = lambda c: [p + 8 * c * self.cap_c for p in self.peerS]
+        self.hx.peer_scatter_async(self.dR.data_ptr(), self.n, G, dom_bits, self.b1, self.peerR, cur[0].data_ptr())
+        self.hx.peer_scatter_async(self.dS.data_ptr(), mc, G, dom_bits, self.b1, peer_c(0), cur[1].data_ptr())
+        self.hx.sync()
+        self.dist.barrier()
+        torch.cuda.synchronize()
+        t.append(time.perf_counter())
+        matches = checksum = 0
+        for c in range(C):
+            if c + 1 < C:  # next chunk leaves on a few CTAs while this one is joined on the rest
+                self.hx.peer_scatter_async(self.dS.data_ptr() + 8 * (c + 1) * mc, mc, G, dom_bits, self.b1,
+                                           peer_c(c + 1), cur[2 + c].data_ptr(), self.peer_ctas)
+            res = self.h.join_pass1(self.recvR, nr, self.recvS + 8 * c * self.cap_c, ns[c], off[0].data_ptr(),
+                                    off[1 + c].data_ptr())
+            matches += res.matches
+            checksum = (checksum + res.checksum) & (2**64 - 1)
+            self.launches += res.kernel_launches
+            if c + 1 < C:
+                self.hx.sync()
+                self.dist.barrier()
+                torch.cuda.synchronize()
+        t.append(time.perf_counter())
+        self.launches += 2 + 2 * C
+        self.nvlink_bytes += 8 * (self.n + self.m - own)
+        self.last = res
+        out = ex.reduce_result(matches, checksum, "cuda")
+        t.append(time.perf_counter())
+        self.fused_ms = [round((b - a) * 1e3, 3) for a, b in zip(t, t[1:])]  # hist, counts, R + chunk 0, pipeline, reduce
         return out
 
     def barrier(self):

@@ -209,6 +209,12 @@ class HashJoin:
         self._check(lib.hj_peer_scatter(self._h, int(d_in), int(n), n_dest, domain_bits, b1, arr, int(d_cursors)),
                     "hj_peer_scatter")
 
+    def peer_scatter_async(self, d_in, n, n_dest, domain_bits, b1, peer_bufs, d_cursors, max_ctas=0):
+        """hj_peer_scatter_async: enqueued only (sync() waits), on at most max_ctas CTAs."""
+        arr = (C.c_uint64 * n_dest)(*[int(p) for p in peer_bufs])
+        self._check(lib.hj_peer_scatter_async(self._h, int(d_in), int(n), n_dest, domain_bits, b1, arr, int(d_cursors),
+                                              int(max_ctas)), "hj_peer_scatter_async")
+
     def join_pass1(self, d_R1, n, d_S1, m, d_offR1=None, d_offS1=None):
         res = hj_result()
         self._check(lib.hj_join_pass1(self._h, int(d_R1), int(n), int(d_offR1) if d_offR1 else None, int(d_S1), int(m),

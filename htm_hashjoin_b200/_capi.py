@@ -22,7 +22,7 @@ ABI_SYMBOLS = [
     "hj_generate", "hj_device_alloc", "hj_device_free", "hj_host_alloc", "hj_host_free",
     "hj_copy", "hj_flush_l2", "hj_sync",
     "hj_radix_plan", "hj_ipc_export", "hj_ipc_open", "hj_ipc_close", "hj_peer_hist", "hj_peer_scatter",
-    "hj_join_pass1", "hj_join_materialize",
+    "hj_join_pass1", "hj_join_materialize", "hj_peer_scatter_async",
 ]
 # host-side mirror of the reference interface (csrc/ref_entry.hpp, csrc/datagen.hpp)
 HOST_SYMBOLS = ["hj_ref_run", "hj_ref_set_radix", "hj_ref_set_device", "hj_ref_last_status",
@@ -95,6 +95,8 @@ def load():
         "hj_peer_hist": (C.c_int, [H, u64p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32, u64p]),
         "hj_peer_scatter": (C.c_int, [H, u64p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32,
                                       C.POINTER(C.c_uint64), u64p]),
+        "hj_peer_scatter_async": (C.c_int, [H, u64p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32,
+                                            C.POINTER(C.c_uint64), u64p, C.c_uint32]),
         "hj_join_pass1": (C.c_int, [H, u64p, C.c_uint64, u64p, u64p, C.c_uint64, u64p, C.POINTER(hj_result)]),
         "hj_join_materialize": (C.c_int, [H, u64p, C.c_uint64, u64p, C.c_uint64, u64p, C.c_uint64,
                                           C.POINTER(C.c_uint64), C.POINTER(hj_result)]),

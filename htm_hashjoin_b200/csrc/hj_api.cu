@@ -1382,8 +1382,23 @@ int hj_peer_hist(hj_handle* h, const uint64_t* in, uint64_t n, uint32_t n_dest, 
 // peer_bufs: HOST array of n_dest device pointers (entry `self` = the local buffer, the others
 // opened with hj_ipc_open); cursors: DEVICE array of n_dest << b1 u64, on entry the first element
 // of this rank's exclusive range for every (dest, low bits), advanced by the claims.
+static int peer_scatter_impl(hj_handle* h, const uint64_t* in, uint64_t n, uint32_t n_dest, uint32_t domain_bits,
+                             uint32_t b1, uint64_t* const* peer_bufs, uint64_t* cursors, uint32_t max_ctas, bool sync);
+
 int hj_peer_scatter(hj_handle* h, const uint64_t* in, uint64_t n, uint32_t n_dest, uint32_t domain_bits, uint32_t b1,
                     uint64_t* const* peer_bufs, uint64_t* cursors) {
+  return peer_scatter_impl(h, in, n, n_dest, domain_bits, b1, peer_bufs, cursors, 0, true);
+}
+// Same, but only enqueued (hj_sync waits for it), on at most max_ctas CTAs (0: all SMs).  The scatter is
+// NVLink-bound, so a third of the SMs keeps the links busy while another handle's pass 2 + join of the
+// previous chunk runs on the rest (bench.py --chunks).
+int hj_peer_scatter_async(hj_handle* h, const uint64_t* in, uint64_t n, uint32_t n_dest, uint32_t domain_bits,
+                          uint32_t b1, uint64_t* const* peer_bufs, uint64_t* cursors, uint32_t max_ctas) {
+  return peer_scatter_impl(h, in, n, n_dest, domain_bits, b1, peer_bufs, cursors, max_ctas, false);
+}
+
+static int peer_scatter_impl(hj_handle* h, const uint64_t* in, uint64_t n, uint32_t n_dest, uint32_t domain_bits,
+                             uint32_t b1, uint64_t* const* peer_bufs, uint64_t* cursors, uint32_t max_ctas, bool sync) {
   if (!h || !in || !peer_bufs || !cursors || !is_device_ptr(in) || !is_device_ptr(cursors)) return HJ_EINVAL;
   Digit dg;
   int rc = peer_digit(h, n_dest, domain_bits, b1, &dg);
@@ -1406,12 +1421,13 @@ int hj_peer_scatter(hj_handle* h, const uint64_t* in, uint64_t n, uint32_t n_des
   CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int grid = grid_for(h, (const void*)k, kScThreads, smem);
   if (getenv("HJ_PEER_CTAS")) grid = h->sm_count * atoi(getenv("HJ_PEER_CTAS"));
+  if (max_ctas && (u32)grid > max_ctas) grid = (int)max_ctas;
   if ((u64)grid > ntiles) grid = (int)(ntiles ? ntiles : 1);
   k<<<grid, kScThreads, smem, h->stream>>>((const u64*)in, nullptr, dg, F, 1, rb.one.p, rb.one.p + 2, (u64*)cursors,
                                            reinterpret_cast<u64* const*>(h->peer_ptrs.p), ScOpt{});
   h->launches++;
   CK(cudaGetLastError());
-  CK(cudaStreamSynchronize(h->stream));
+  if (sync) CK(cudaStreamSynchronize(h->stream));
   return HJ_OK;
 }
 

@@ -191,6 +191,12 @@ int hj_peer_hist(hj_handle *h, const uint64_t *in, uint64_t n, uint32_t n_dest,
 int hj_peer_scatter(hj_handle *h, const uint64_t *in, uint64_t n, uint32_t n_dest,
                     uint32_t domain_bits, uint32_t b1, uint64_t *const *peer_bufs,
                     uint64_t *cursors);
+/* hj_peer_scatter without the final wait (hj_sync waits for it) and on at most max_ctas CTAs
+ * (0 = all SMs): the scatter is NVLink-bound, so it can share the GPU with another handle's
+ * hj_join_pass1 of the previous chunk of S (a join is additive over disjoint parts of S).
+ * Consecutive async scatters on one handle run in order. */
+int hj_peer_scatter_async(hj_handle *h, const uint64_t *in, uint64_t n, uint32_t n_dest, uint32_t domain_bits,
+                          uint32_t b1, uint64_t *const *peer_bufs, uint64_t *cursors, uint32_t max_ctas);
 /* offR1/offS1: DEVICE arrays of the 2^b1 + 1 pass-1 partition offsets inside R1/S1 (or NULL:
  * the library histograms what arrived). */
 int hj_join_pass1(hj_handle *h, const uint64_t *R1, uint64_t n, const uint64_t *offR1,
