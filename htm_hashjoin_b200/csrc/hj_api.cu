@@ -1408,15 +1408,18 @@ static int peer_scatter_impl(hj_handle* h, const uint64_t* in, uint64_t n, uint3
   if ((rc = ensure(h, rb.one, 4))) return rc;
   if ((rc = ensure(h, h->peer_ptrs, kScMaxPeers))) return rc;
   const u32 F = n_dest << b1;
-  constexpr int kPeerIPT = 32;
-  const u32 tile = kScThreads * kPeerIPT;
+  // tile = 512 x IPT tuples: 32 -> one CTA per SM, the longest runs; 16 (HJ_PEER_IPT=16) -> two CTAs per SM
+  static const int peer_ipt = getenv("HJ_PEER_IPT") ? atoi(getenv("HJ_PEER_IPT")) : 32;
+  const u32 tile = kScThreads * (peer_ipt == 16 ? 16 : 32);
   const u64 ntiles = (n + tile - 1) / tile;
   const u64 one[4] = {0, n, 0, ntiles};  // the one-parent view: offsets {0, n}, tiles {0, ntiles}
   CK(cudaMemcpyAsync(rb.one.p, one, sizeof(one), cudaMemcpyHostToDevice, h->stream));
   CK(cudaMemcpyAsync(h->peer_ptrs.p, peer_bufs, n_dest * sizeof(u64*), cudaMemcpyHostToDevice, h->stream));
   // runs leave through bulk async copies (TMA) unless HJ_PEER_NO_BULK is set (then: 8-byte stores)
   const bool bulk = !getenv("HJ_PEER_NO_BULK") && (F % 2 == 0);
-  auto k = bulk ? rx_scatter_kernel<kPeerIPT, 2, true, 0, true> : rx_scatter_kernel<kPeerIPT, 2, true, 0, false>;
+  auto k = peer_ipt == 16 ? rx_scatter_kernel<16, 2, true, 0, true>
+           : bulk         ? rx_scatter_kernel<32, 2, true, 0, true>
+                          : rx_scatter_kernel<32, 2, true, 0, false>;
   size_t smem = (size_t)tile * 8 + (size_t)F * 16 + (bulk ? sc_bulk_extra(F) : 0);
   CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int grid = grid_for(h, (const void*)k, kScThreads, smem);
