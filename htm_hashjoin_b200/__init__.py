@@ -215,6 +215,21 @@ class HashJoin:
         self._check(lib.hj_peer_scatter_async(self._h, int(d_in), int(n), n_dest, domain_bits, b1, arr, int(d_cursors),
                                               int(max_ctas)), "hj_peer_scatter_async")
 
+    def peer_scatter_regions(self, d_in, n, n_dest, domain_bits, b1, peer_bufs, d_cursors, rank, region_cap, trash_off):
+        """hj_peer_scatter_regions (histogram-free exchange); returns True when a region overflowed."""
+        arr = (C.c_uint64 * n_dest)(*[int(p) for p in peer_bufs])
+        ovf = C.c_uint32(0)
+        self._check(lib.hj_peer_scatter_regions(self._h, int(d_in), int(n), n_dest, domain_bits, b1, arr, int(d_cursors),
+                                                int(rank), int(region_cap), int(trash_off), C.byref(ovf)),
+                    "hj_peer_scatter_regions")
+        return bool(ovf.value)
+
+    def join_regions(self, d_R1, n, d_curR, cap_r, d_S1, m, d_curS, cap_s, n_src):
+        res = hj_result()
+        self._check(lib.hj_join_regions(self._h, int(d_R1), int(n), int(d_curR), int(cap_r), int(d_S1), int(m),
+                                        int(d_curS), int(cap_s), int(n_src), C.byref(res)), "hj_join_regions")
+        return res
+
     def join_pass1(self, d_R1, n, d_S1, m, d_offR1=None, d_offS1=None):
         res = hj_result()
         self._check(lib.hj_join_pass1(self._h, int(d_R1), int(n), int(d_offR1) if d_offR1 else None, int(d_S1), int(m),

@@ -23,6 +23,7 @@ ABI_SYMBOLS = [
     "hj_copy", "hj_flush_l2", "hj_sync",
     "hj_radix_plan", "hj_ipc_export", "hj_ipc_open", "hj_ipc_close", "hj_peer_hist", "hj_peer_scatter",
     "hj_join_pass1", "hj_join_materialize", "hj_peer_scatter_async",
+    "hj_peer_scatter_regions", "hj_join_regions",
 ]
 # host-side mirror of the reference interface (csrc/ref_entry.hpp, csrc/datagen.hpp)
 HOST_SYMBOLS = ["hj_ref_run", "hj_ref_set_radix", "hj_ref_set_device", "hj_ref_last_status",
@@ -97,6 +98,11 @@ def load():
                                       C.POINTER(C.c_uint64), u64p]),
         "hj_peer_scatter_async": (C.c_int, [H, u64p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32,
                                             C.POINTER(C.c_uint64), u64p, C.c_uint32]),
+        "hj_peer_scatter_regions": (C.c_int, [H, u64p, C.c_uint64, C.c_uint32, C.c_uint32, C.c_uint32,
+                                              C.POINTER(C.c_uint64), u64p, C.c_uint32, C.c_uint64, C.c_uint64,
+                                              C.POINTER(C.c_uint32)]),
+        "hj_join_regions": (C.c_int, [H, u64p, C.c_uint64, u64p, C.c_uint64, u64p, C.c_uint64, u64p, C.c_uint64,
+                                      C.c_uint32, C.POINTER(hj_result)]),
         "hj_join_pass1": (C.c_int, [H, u64p, C.c_uint64, u64p, u64p, C.c_uint64, u64p, C.POINTER(hj_result)]),
         "hj_join_materialize": (C.c_int, [H, u64p, C.c_uint64, u64p, C.c_uint64, u64p, C.c_uint64,
                                           C.POINTER(C.c_uint64), C.POINTER(hj_result)]),

@@ -453,10 +453,11 @@ u64 opt_region_cap(u64 n, u32 bits) {
   return (avg + r + 64 + 1) & ~1ull;
 }
 
-int ensure_rel(hj_handle* h, RelBufs& rb, u64 n, const RadixPlan& pl, bool pre1 = false, bool opt = false) {
+int ensure_rel(hj_handle* h, RelBufs& rb, u64 n, const RadixPlan& pl, bool pre1 = false, bool opt = false,
+               u32 n_src = 1) {
   int rc;
   u64 nb = 1ull << pl.bits;
-  u64 np = 1ull << pl.b1;
+  u64 np = (1ull << pl.b1) * n_src;  // parents of pass 2 (one per source rank after a region exchange)
   // histogram-free layout: 2^bits regions + one scatter tile of scratch for diverted claims
   const u64 elems = opt ? nb * opt_region_cap(n, pl.bits) + kScThreads * 8 + 2 : n + 2;
   if ((rc = ensure(h, rb.out, elems))) return rc;
@@ -592,8 +593,16 @@ int radix_partition_rel(hj_handle* h, const u64* in, u64 n, RelBufs& rb, const R
 // fixed-capacity regions, rb.cursors ends up holding the fill level of every final region.
 // pre1_off != nullptr: `in` is already the pass-1 output (fused exchange) with exact parent offsets
 // pre1_off[0..F1]: only pass 2 runs, and it gathers the key-width flag.
+// What a histogram-free exchange leaves in a receive buffer: pass-1 partition `low` as n_src regions of
+// `cap` tuples, region low * n_src + src = [start, cur[low * n_src + src]) (hj_join_regions).
+struct Pre1Regions {
+  const u64* cur;
+  u64 cap;
+  u32 n_src;
+};
+
 int radix_partition_rel_opt(hj_handle* h, const u64* in, u64 n, RelBufs& rb, const RadixPlan& pl, int evb,
-                            const u64* pre1_off = nullptr) {
+                            const u64* pre1_off = nullptr, const Pre1Regions* reg = nullptr) {
   const u32 nb = 1u << pl.bits, F1 = 1u << pl.b1, F2 = 1u << pl.b2;
   const u32 tile = kScThreads * pl.tile_ipt;
   const u64 C2 = opt_region_cap(n, pl.bits), C1 = C2 * F2;
@@ -618,7 +627,13 @@ int radix_partition_rel_opt(hj_handle* h, const u64* in, u64 n, RelBufs& rb, con
   memset(&d1, 0, sizeof(d1));
   d1.key_mask = h->cfg.key_mask; d1.mode = 0; d1.shift = 0; d1.bits = pl.b1;
   d2 = d1; d2.shift = pl.b1; d2.bits = pl.b2;
-  if (!pre1_off) {
+  u32 nparent2 = F1, pshift = 0;
+  if (reg) {
+    nparent2 = F1 * reg->n_src;
+    while ((1u << pshift) < reg->n_src) pshift++;
+    if ((1u << pshift) != reg->n_src || nparent2 > (u32)kScParentCache) return HJ_EINVAL;
+  }
+  if (!pre1_off && !reg) {
     size_t smem = stage + (size_t)tile * 8 + (size_t)F1 * 16 + (bulk ? sc_bulk_extra(F1) : 0);
     CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int grid = grid_for(h, (const void*)k, kScThreads, smem);
@@ -629,18 +644,19 @@ int radix_partition_rel_opt(hj_handle* h, const u64* in, u64 n, RelBufs& rb, con
     CK(cudaGetLastError());
   }
   if (evb >= 0) mark(h, evb + 3);
-  if (pre1_off) rx_pre1_parents_kernel<<<1, 1024, 0, h->stream>>>(pre1_off, F1, tile, rb.poff.p, rb.pend.p, rb.ptiles.p);
+  if (reg) rx_opt_parents_kernel<<<1, 1024, 0, h->stream>>>(reg->cur, nparent2, reg->cap, tile, rb.poff.p, rb.pend.p, rb.ptiles.p);
+  else if (pre1_off) rx_pre1_parents_kernel<<<1, 1024, 0, h->stream>>>(pre1_off, F1, tile, rb.poff.p, rb.pend.p, rb.ptiles.p);
   else rx_opt_parents_kernel<<<1, 1024, 0, h->stream>>>(rb.pcur.p, F1, C1, tile, rb.poff.p, rb.pend.p, rb.ptiles.p);
   h->launches++;
   {
-    auto kp2 = pre1_off ? k : k2;  // after the fused exchange nobody has looked at the key width yet
+    auto kp2 = (pre1_off || reg) ? k : k2;  // after the fused exchange nobody has looked at the key width yet
     size_t smem = stage + (size_t)tile * 8 + (size_t)F2 * 16 + (bulk ? sc_bulk_extra(F2) : 0);
     CK(cudaFuncSetAttribute(kp2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int grid = grid_for(h, (const void*)kp2, kScThreads, smem);
-    if ((u64)grid > ntiles + F1) grid = (int)(ntiles + F1);
-    ScOpt o{rb.pend.p, C2, (u64)nb * C2, h->ctr};
-    kp2<<<grid, kScThreads, smem, h->stream>>>(pre1_off ? in : rb.tmp.p, rb.out.p, d2, F2, F1, rb.poff.p, rb.ptiles.p,
-                                               rb.cursors.p, nullptr, o);
+    if ((u64)grid > ntiles + nparent2) grid = (int)(ntiles + nparent2);
+    ScOpt o{rb.pend.p, C2, (u64)nb * C2, h->ctr, pshift, 0, 0, 0};
+    kp2<<<grid, kScThreads, smem, h->stream>>>((pre1_off || reg) ? in : rb.tmp.p, rb.out.p, d2, F2, nparent2, rb.poff.p,
+                                               rb.ptiles.p, rb.cursors.p, nullptr, o);
     h->launches++;
     CK(cudaGetLastError());
   }
@@ -658,7 +674,8 @@ struct MatReq {
 
 int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS, u64 m, bool pendS, hj_result* res,
                    bool pre1 = false, bool force_exact = false, const u64* offR1 = nullptr,
-                   const u64* offS1 = nullptr, MatReq* mat = nullptr) {
+                   const u64* offS1 = nullptr, MatReq* mat = nullptr, const Pre1Regions* regR = nullptr,
+                   const Pre1Regions* regS = nullptr) {
   RadixPlan pl;
   int rc;
   if ((rc = plan_radix(h, n, &pl))) {
@@ -676,19 +693,20 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
   const bool use_l2 = dS && (getenv("HJ_FORCE_L2JOIN") || need > 21000) && !getenv("HJ_NO_L2JOIN");
   // Histogram-free partitioning (ScOpt, rx_kernels.cuh) for the 2-pass shared-memory join; the
   // exact, histogram-based layout everywhere else and after an overflow on this handle.
-  const bool opt = dS && (!pre1 || (offR1 && offS1)) && !use_l2 && pl.passes == 2 && !h->no_optimistic && !force_exact &&
+  const bool opt = dS && (!pre1 || (offR1 && offS1) || (regR && regS)) && !use_l2 && pl.passes == 2 && !h->no_optimistic && !force_exact &&
                    !getenv("HJ_NO_OPTIMISTIC");
   const u64 capR = opt ? opt_region_cap(n, pl.bits) : 0, capS = opt ? opt_region_cap(m, pl.bits) : 0;
-  if ((rc = ensure_rel(h, h->rb[0], n, pl, pre1, opt))) return rc;
-  if (dS && (rc = ensure_rel(h, h->rb[1], m, pl, pre1, opt))) return rc;
+  if ((regR || regS) && !opt) return HJ_EINVAL;  // regions need the histogram-free 2-pass shared-memory plan
+  if ((rc = ensure_rel(h, h->rb[0], n, pl, pre1, opt, regR ? regR->n_src : 1))) return rc;
+  if (dS && (rc = ensure_rel(h, h->rb[1], m, pl, pre1, opt, regS ? regS->n_src : 1))) return rc;
   CK(cudaMemsetAsync(h->ctr, 0, C_COUNT * sizeof(u64), h->stream));
   if ((rc = wait_staged(h, E_CPR, pendR))) return rc;
-  if (opt) rc = radix_partition_rel_opt(h, dR, n, h->rb[0], pl, E_RX, pre1 ? offR1 : nullptr);
+  if (opt) rc = radix_partition_rel_opt(h, dR, n, h->rb[0], pl, E_RX, pre1 ? offR1 : nullptr, regR);
   else rc = radix_partition_rel(h, dR, n, h->rb[0], pl, E_RX, h->ctr + C_MAX_PART, pre1);
   if (rc) return rc;
   if (dS) {
     if ((rc = wait_staged(h, E_CPS, pendS))) return rc;
-    if (opt) rc = radix_partition_rel_opt(h, dS, m, h->rb[1], pl, E_RX + 5, pre1 ? offS1 : nullptr);
+    if (opt) rc = radix_partition_rel_opt(h, dS, m, h->rb[1], pl, E_RX + 5, pre1 ? offS1 : nullptr, regS);
     else rc = radix_partition_rel(h, dS, m, h->rb[1], pl, E_RX + 5, nullptr, pre1);
     if (rc) return rc;
   }
@@ -859,6 +877,10 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
   if ((rc = fetch_counters(h))) return rc;
   if (opt && h->h_ctr[C_OPT_OVF]) {
     // a region overflowed (skewed partition sizes): nothing was lost -- redo on the exact path
+    if (regR) {  // the exact path needs contiguous pass-1 partitions: the caller redoes the exchange
+      snprintf(h->err, sizeof(h->err), "join_regions: a pass-2 region overflowed; redo with hj_peer_hist + hj_join_pass1");
+      return HJ_EOVERFLOW;
+    }
     h->no_optimistic = true;
     return run_radix_join(h, dR, n, false, dS, m, false, res, pre1, true);
   }
@@ -1382,8 +1404,13 @@ int hj_peer_hist(hj_handle* h, const uint64_t* in, uint64_t n, uint32_t n_dest, 
 // peer_bufs: HOST array of n_dest device pointers (entry `self` = the local buffer, the others
 // opened with hj_ipc_open); cursors: DEVICE array of n_dest << b1 u64, on entry the first element
 // of this rank's exclusive range for every (dest, low bits), advanced by the claims.
+struct PeerRegions {  // histogram-free exchange: this rank's regions in every destination buffer
+  u32 rank;
+  u64 region_cap, trash_off;
+};
 static int peer_scatter_impl(hj_handle* h, const uint64_t* in, uint64_t n, uint32_t n_dest, uint32_t domain_bits,
-                             uint32_t b1, uint64_t* const* peer_bufs, uint64_t* cursors, uint32_t max_ctas, bool sync);
+                             uint32_t b1, uint64_t* const* peer_bufs, uint64_t* cursors, uint32_t max_ctas, bool sync,
+                             const PeerRegions* reg = nullptr);
 
 int hj_peer_scatter(hj_handle* h, const uint64_t* in, uint64_t n, uint32_t n_dest, uint32_t domain_bits, uint32_t b1,
                     uint64_t* const* peer_bufs, uint64_t* cursors) {
@@ -1397,8 +1424,31 @@ int hj_peer_scatter_async(hj_handle* h, const uint64_t* in, uint64_t n, uint32_t
   return peer_scatter_impl(h, in, n, n_dest, domain_bits, b1, peer_bufs, cursors, max_ctas, false);
 }
 
+// Histogram-free exchange, sending side: no hj_peer_hist, no counts before the scatter.  Region
+// low * n_dest + rank of every destination buffer (region_cap tuples each, the same on all ranks) belongs
+// to this rank; cursors[(dest << b1) | low] must hold that region's first element on entry and holds
+// its fill level on return -- the receivers need those values (all-gather) for hj_join_regions.
+// *overflowed = 1: a region was too small (skewed keys); its surplus went to the scratch zone at
+// trash_off of the destination buffer (one 16384-tuple tile + 2) and the exchange has to be redone
+// with the exact protocol (hj_peer_hist / hj_peer_scatter / hj_join_pass1).
+int hj_peer_scatter_regions(hj_handle* h, const uint64_t* in, uint64_t n, uint32_t n_dest, uint32_t domain_bits,
+                            uint32_t b1, uint64_t* const* peer_bufs, uint64_t* cursors, uint32_t rank,
+                            uint64_t region_cap, uint64_t trash_off, uint32_t* overflowed) {
+  if (!h || rank >= n_dest || !region_cap || (region_cap & 1) || (trash_off & 1)) return HJ_EINVAL;
+  CK(cudaSetDevice(h->device));
+  CK(cudaMemsetAsync(h->ctr + C_OPT_OVF, 0, sizeof(u64), h->stream));
+  PeerRegions reg{rank, region_cap, trash_off};
+  int rc = peer_scatter_impl(h, in, n, n_dest, domain_bits, b1, peer_bufs, cursors, 0, false, &reg);
+  if (rc) return rc;
+  CK(cudaMemcpyAsync(h->h_ctr + C_OPT_OVF, h->ctr + C_OPT_OVF, sizeof(u64), cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  if (overflowed) *overflowed = h->h_ctr[C_OPT_OVF] ? 1u : 0u;
+  return HJ_OK;
+}
+
 static int peer_scatter_impl(hj_handle* h, const uint64_t* in, uint64_t n, uint32_t n_dest, uint32_t domain_bits,
-                             uint32_t b1, uint64_t* const* peer_bufs, uint64_t* cursors, uint32_t max_ctas, bool sync) {
+                             uint32_t b1, uint64_t* const* peer_bufs, uint64_t* cursors, uint32_t max_ctas, bool sync,
+                             const PeerRegions* reg) {
   if (!h || !in || !peer_bufs || !cursors || !is_device_ptr(in) || !is_device_ptr(cursors)) return HJ_EINVAL;
   Digit dg;
   int rc = peer_digit(h, n_dest, domain_bits, b1, &dg);
@@ -1417,9 +1467,13 @@ static int peer_scatter_impl(hj_handle* h, const uint64_t* in, uint64_t n, uint3
   CK(cudaMemcpyAsync(h->peer_ptrs.p, peer_bufs, n_dest * sizeof(u64*), cudaMemcpyHostToDevice, h->stream));
   // runs leave through bulk async copies (TMA) unless HJ_PEER_NO_BULK is set (then: 8-byte stores)
   const bool bulk = !getenv("HJ_PEER_NO_BULK") && (F % 2 == 0);
-  auto k = peer_ipt == 16 ? rx_scatter_kernel<16, 2, true, 0, true>
-           : bulk         ? rx_scatter_kernel<32, 2, true, 0, true>
-                          : rx_scatter_kernel<32, 2, true, 0, false>;
+  if (reg && !bulk) return HJ_EINVAL;
+  auto k = reg              ? rx_scatter_kernel<32, 2, true, 1, true>
+           : peer_ipt == 16 ? rx_scatter_kernel<16, 2, true, 0, true>
+           : bulk           ? rx_scatter_kernel<32, 2, true, 0, true>
+                            : rx_scatter_kernel<32, 2, true, 0, false>;
+  ScOpt so{};
+  if (reg) so = ScOpt{rb.one.p + 1, reg->region_cap, reg->trash_off, h->ctr, 0, (1u << b1) - 1u, n_dest, reg->rank};
   size_t smem = (size_t)tile * 8 + (size_t)F * 16 + (bulk ? sc_bulk_extra(F) : 0);
   CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int grid = grid_for(h, (const void*)k, kScThreads, smem);
@@ -1427,7 +1481,7 @@ static int peer_scatter_impl(hj_handle* h, const uint64_t* in, uint64_t n, uint3
   if (max_ctas && (u32)grid > max_ctas) grid = (int)max_ctas;
   if ((u64)grid > ntiles) grid = (int)(ntiles ? ntiles : 1);
   k<<<grid, kScThreads, smem, h->stream>>>((const u64*)in, nullptr, dg, F, 1, rb.one.p, rb.one.p + 2, (u64*)cursors,
-                                           reinterpret_cast<u64* const*>(h->peer_ptrs.p), ScOpt{});
+                                           reinterpret_cast<u64* const*>(h->peer_ptrs.p), so);
   h->launches++;
   CK(cudaGetLastError());
   if (sync) CK(cudaStreamSynchronize(h->stream));
@@ -1448,6 +1502,25 @@ int hj_join_pass1(hj_handle* h, const uint64_t* R1, uint64_t n, const uint64_t* 
   if ((offR1 && !is_device_ptr(offR1)) || (offS1 && !is_device_ptr(offS1))) return HJ_EINVAL;
   return run_radix_join(h, (const u64*)R1, n, false, (const u64*)S1, m, false, res, true, false, (const u64*)offR1,
                         (const u64*)offS1);
+}
+
+// hj_join_pass1 for what a histogram-free exchange (hj_peer_scatter_regions) delivered: pass-1 partition
+// `low` sits in n_src regions of cap tuples, region low * n_src + src = [(low * n_src + src) * cap,
+// cur[low * n_src + src]); curR / curS: DEVICE arrays of 2^b1 * n_src fill levels (the senders' final
+// cursors), n / m: tuples that arrived.  n_src must be a power of two, 2^b1 * n_src <= 256.
+int hj_join_regions(hj_handle* h, const uint64_t* R1, uint64_t n, const uint64_t* curR, uint64_t capR,
+                    const uint64_t* S1, uint64_t m, const uint64_t* curS, uint64_t capS, uint32_t n_src,
+                    hj_result* res) {
+  if (!h || !R1 || !S1 || !curR || !curS || !n_src || !is_device_ptr(R1) || !is_device_ptr(S1) ||
+      !is_device_ptr(curR) || !is_device_ptr(curS))
+    return HJ_EINVAL;
+  CK(cudaSetDevice(h->device));
+  if (res) memset(res, 0, sizeof(*res));
+  reset_events(h);
+  mark(h, E_T0);
+  Pre1Regions rr{(const u64*)curR, capR, n_src}, rs{(const u64*)curS, capS, n_src};
+  return run_radix_join(h, (const u64*)R1, n, false, (const u64*)S1, m, false, res, true, false, nullptr, nullptr, nullptr,
+                        &rr, &rs);
 }
 
 int hj_generate(hj_handle* h, int kind, uint64_t first, uint64_t count, uint64_t domain, uint64_t seed,

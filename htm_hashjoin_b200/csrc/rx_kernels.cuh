@@ -223,10 +223,17 @@ constexpr int kScMaxPeers = 16;
 // rx_hist costs (8 of the 48 B/tuple the 2-pass join moves).  Parents are [parent_off[p],
 // parent_end[p]) (gaps between regions), and since rx_hist is gone the key-width flag
 // ctr[C_KEY_HI] is gathered here.
+// parent_shift: parents that share an output partition -- after a histogram-free EXCHANGE the pass-1
+// partition `low` arrives as one region per source rank, parent = low * n_src + src, so the cursor
+// index is (parent >> parent_shift) * F + digit.  PEER && OPT (the sending side of that exchange):
+// digit = (dest << b1) | low goes to region low * ndest + rank of dest's buffer; cursors[digit] is
+// initialised to that region's start by the caller and stays local, the final values are what the
+// receivers are told.
 struct ScOpt {
   const u64* parent_end;
   u64 region_cap, trash_off;
   u64* ctr;
+  u32 parent_shift, low_mask, ndest, rank;
 };
 
 // OPT: 0 = exact layout, 1 = histogram-free + key-width flag (pass 1), 2 = histogram-free (pass 2)
@@ -425,9 +432,11 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
           hist[b] = 0;  // ready for the next tile (nobody reads hist after this scan)
           lbase[b] = run;
           if (c) {
-            const u64 q = (u64)p * F + b;
+            const u64 q = (u64)(OPT ? p >> opt.parent_shift : p) * F + b;
             u64 g = atomicAdd(cursors + q, (u64)c);
-            if (OPT && g + c > (q + 1) * opt.region_cap) {  // region full: divert, flag, host falls back
+            const u64 rend = (PEER && OPT) ? ((u64)(b & opt.low_mask) * opt.ndest + opt.rank + 1) * opt.region_cap
+                                           : (q + 1) * opt.region_cap;
+            if (OPT && g + c > rend) {  // region full: divert, flag, host falls back
               g = opt.trash_off;
               opt.ctr[C_OPT_OVF] = 1ull;
             }

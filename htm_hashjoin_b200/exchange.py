@@ -68,6 +68,35 @@ def peer_cursors(counts_all, rank, n_dest, f1):
     return start[rank].reshape(-1).contiguous(), recv, own_off
 
 
+# ---- histogram-free exchange (hj_peer_scatter_regions / hj_join_regions) -------------------------
+def region_cap(n_local, n_dest, f1):
+    """Capacity of one (source, dest, low bits) region: expected tuples + 8 sigma of a random split + 64,
+    even (16-byte alignment).  The same number on every rank: all ranks hold n_local tuples."""
+    mean = n_local // (n_dest * f1) + 1
+    r = 1
+    while r * r < mean:
+        r += 1
+    return (mean + 8 * r + 64 + 1) & ~1
+
+
+def region_cursor_init(rank, n_dest, f1, cap, device):
+    """cursors[(dest * f1) + low] = first element of region low * n_dest + rank (the same in every
+    destination buffer)."""
+    low = torch.arange(f1, dtype=torch.int64, device=device)
+    return ((low * n_dest + rank) * cap).repeat(n_dest).contiguous()
+
+
+def regions_received(final_all, rank, n_dest, f1, cap):
+    """final_all: int64 [G, G*f1], row s = rank s's cursors after hj_peer_scatter_regions.  Returns
+    (cur [f1*G], n): the fill levels of `rank`'s own regions, index low * G + src (what hj_join_regions
+    takes), and the number of tuples that arrived."""
+    G = n_dest
+    mine = final_all.view(G, G, f1)[:, rank, :]          # [src, low]
+    cur = mine.t().contiguous().view(-1)                 # index low * G + src
+    start = torch.arange(f1 * G, dtype=torch.int64, device=final_all.device) * cap
+    return cur, (cur - start).sum()
+
+
 def gather_counts(local_counts):
     """All-gather of the per-rank hj_peer_hist vectors -> [G, len]."""
     G = dist.get_world_size()

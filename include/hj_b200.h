@@ -202,6 +202,24 @@ int hj_peer_scatter_async(hj_handle *h, const uint64_t *in, uint64_t n, uint32_t
 int hj_join_pass1(hj_handle *h, const uint64_t *R1, uint64_t n, const uint64_t *offR1,
                   const uint64_t *S1, uint64_t m, const uint64_t *offS1, hj_result *res);
 
+/* ---- histogram-free exchange (no hj_peer_hist, no counts before the scatter) -----------------------
+ * Every (source, destination, low bits) triple owns a fixed-capacity region of the destination's pass-1
+ * buffer: region low * n_dest + source, region_cap tuples (even; expected size + slack, the same number
+ * on all ranks, e.g. htm_hashjoin_b200/exchange.py: region_cap).  hj_peer_scatter_regions: cursors
+ * (DEVICE, n_dest << b1) holds on entry the first element of this rank's region for every
+ * (dest << b1) | low, on return its fill level; all-gather the cursors -- that collective is also the
+ * barrier -- and give every receiver the fill levels of its regions: hj_join_regions (curR / curS: DEVICE
+ * arrays of (2^b1 * n_src) entries, index low * n_src + source; n / m: tuples that arrived) runs pass 2 +
+ * the per-partition join.  *overflowed != 0 (skewed keys): the surplus went to the scratch zone at
+ * trash_off (16384 + 2 tuples) of the destination buffer; redo the step with the exact protocol above.
+ * n_src must be a power of two and 2^b1 * n_src <= 256. */
+int hj_peer_scatter_regions(hj_handle *h, const uint64_t *in, uint64_t n, uint32_t n_dest, uint32_t domain_bits,
+                            uint32_t b1, uint64_t *const *peer_bufs, uint64_t *cursors, uint32_t rank,
+                            uint64_t region_cap, uint64_t trash_off, uint32_t *overflowed);
+int hj_join_regions(hj_handle *h, const uint64_t *R1, uint64_t n, const uint64_t *curR, uint64_t capR,
+                    const uint64_t *S1, uint64_t m, const uint64_t *curS, uint64_t capS, uint32_t n_src,
+                    hj_result *res);
+
 /* ---- device-side input synthesis (sizes beyond uint32_t/rand()) --
  * Counter-based generators with a bit-identical CPU restatement in oracle/:
  *   kind 0: out[i] = first + i + 1                       (sorted slice)

@@ -159,3 +159,77 @@ def test_two_rank_fused_exchange_protocol(built):
         p.join(timeout=60)
         assert p.exitcode == 0
     assert total == want and want[0] == m
+
+
+def _regions_worker(rank, world, port, n, m, q):
+    """Histogram-free exchange on CPU: every rank appends to ITS regions (exchange.region_cap /
+    region_cursor_init), the final cursors are all-gathered, exchange.regions_received gives every receiver
+    the fill levels of its regions; what sits inside them joins to the global result."""
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from htm_hashjoin_b200 import exchange
+    from tests.oracle_lib import Oracle
+    orc = Oracle()
+    R = orc.generate_data("shuffle", n)
+    S = orc.mc_fk(m, n)
+    b1, f1 = 3, 8
+    dom_bits = exchange.domain_bits_for(n)
+    bufs = []
+    for rel, tot in ((R, n), (S, m)):
+        sl = rel[rank * tot // world:(rank + 1) * tot // world]
+        cap = exchange.region_cap(sl.size, world, f1)
+        assert cap % 2 == 0
+        dig = _peer_digit(sl, world, dom_bits, b1)
+        cur = exchange.region_cursor_init(rank, world, f1, cap, "cpu")
+        assert cur.numel() == world * f1
+        writes = []
+        for d in range(world * f1):
+            t = sl[dig == d]
+            low = d % f1
+            assert int(cur[d]) == (low * world + rank) * cap
+            assert t.size <= cap                                     # uniform keys never overflow 8 sigma
+            writes.append((d // f1, int(cur[d]), t))
+            cur[d] += t.size
+        final_all = exchange.gather_counts(cur)                      # doubles as the barrier
+        mine, n_recv = exchange.regions_received(final_all, rank, world, f1, cap)
+        gathered = [None] * world
+        dist.all_gather_object(gathered, writes)
+        buf = np.zeros(f1 * world * cap, dtype=np.uint64)
+        for w in gathered:
+            for dest, off, t in w:
+                if dest == rank:
+                    assert (buf[off:off + t.size] == 0).all()        # regions never overlap
+                    buf[off:off + t.size] = t
+        got = []
+        for p in range(f1 * world):
+            seg = buf[p * cap:int(mine[p])]
+            assert (seg != 0).all() and ((seg & np.uint64(f1 - 1)) == np.uint64(p // world)).all()
+            got.append(seg)
+        got = np.concatenate(got)
+        assert got.size == int(n_recv) == np.count_nonzero(buf)
+        lo, hi = rank * n // world, (rank + 1) * n // world
+        assert got.min() >= lo + 1 and got.max() <= hi
+        bufs.append(got)
+    mt, ck = orc.true_join(bufs[0], bufs[1])
+    total = exchange.reduce_result(mt, ck, "cpu")
+    if rank == 0:
+        q.put((total, orc.true_join(R, S)))
+    dist.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+def test_two_rank_region_exchange_protocol(built):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    n, m = 1 << 13, 3 << 13
+    procs = [ctx.Process(target=_regions_worker, args=(r, 2, port, n, m, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    total, want = q.get(timeout=240)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert total == want

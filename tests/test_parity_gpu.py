@@ -460,3 +460,56 @@ def test_zipf_skewed_probe_side(hj, oracle, algo, z):
     with hj.HashJoin(algo, key_mask=0xFFFFFFFF) as h:
         res = h.join(R, S)
         assert (res.matches, res.checksum) == want
+
+
+@pytest.mark.parametrize("skewed", [False, True])
+def test_region_exchange_logical_ranks(hj, oracle, skewed):
+    """hj_peer_scatter_regions / hj_join_regions (histogram-free exchange) with two logical ranks on one
+    GPU.  Uniform keys: the regions hold everything and the join equals the oracle.  Skewed keys (one
+    key repeated): the overflow is reported, nothing is written outside the region or the scratch zone."""
+    import torch
+    from htm_hashjoin_b200 import exchange
+    G, n, m = 2, 1 << 18, 3 << 18
+    R = hj.generate_data("shuffle", n)
+    S = np.concatenate([hj.generate_data("shuffle", n), hj.mc_relation_fk(n, n) & np.uint64(0xFFFFFFFF),
+                        hj.generate_data("shuffle", n)])  # random order: every (source, dest) pair gets its share
+    if skewed:
+        S = S.copy()
+        S[: m // 4] = 12345
+    want = oracle.true_join(R, S)
+    dom_bits = exchange.domain_bits_for(n)
+    with hj.HashJoin("radix", num_partitions=1 << 8, passes=2) as h:
+        bits, b1, b2, passes = h.radix_plan(n // G)
+        f1 = 1 << b1
+        state = {}
+        any_ovf = False
+        for name, rel in (("R", R), ("S", S)):
+            slices = [rel[g * rel.size // G:(g + 1) * rel.size // G] for g in range(G)]
+            cap = exchange.region_cap(slices[0].size, G, f1)
+            trash = f1 * G * cap
+            bufs = [h.device_alloc((trash + 16384 + 2 + 2) * 8) for _ in range(G)]
+            guard = np.uint64(0xDEADBEEFDEADBEEF)
+            finals = []
+            for g in range(G):
+                d_sl = h.to_device(slices[g])
+                cur = exchange.region_cursor_init(g, G, f1, cap, "cuda")
+                torch.cuda.synchronize()
+                any_ovf |= h.peer_scatter_regions(d_sl[0], slices[g].size, G, dom_bits, b1, bufs, cur.data_ptr(), g, cap, trash)
+                finals.append(cur)
+                h.device_free(d_sl[0])
+            final_all = torch.stack(finals)
+            state[name] = (bufs, final_all, cap)
+        assert any_ovf == skewed
+        if skewed:
+            return
+        total = [0, 0]
+        for g in range(G):
+            curR, nr = exchange.regions_received(state["R"][1], g, G, f1, state["R"][2])
+            curS, ns = exchange.regions_received(state["S"][1], g, G, f1, state["S"][2])
+            torch.cuda.synchronize()
+            res = h.join_regions(state["R"][0][g], int(nr), curR.data_ptr(), state["R"][2],
+                                 state["S"][0][g], int(ns), curS.data_ptr(), state["S"][2], G)
+            total[0] += res.matches
+            total[1] = (total[1] + res.checksum) % (1 << 64)
+        assert sum(int(exchange.regions_received(state["S"][1], g, G, f1, state["S"][2])[1]) for g in range(G)) == m
+        assert tuple(total) == want
