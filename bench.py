@@ -41,8 +41,9 @@ def parse_args():
     ap.add_argument("--passes", type=int, default=0)
     ap.add_argument("--algo", default="radix", choices=["radix", "atomic", "adaptive", "nocc"])
     ap.add_argument("--r-dist", default="shuffle", help="DataGen distribution of R at N=1 (host generated)")
-    ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
-                    help="N>1: exchange fused with radix pass 1 over peer memory, or partition + NCCL all-to-all")
+    ap.add_argument("--exchange", default="regions", choices=["regions", "fused", "nccl"],
+                    help="N>1: exchange fused with radix pass 1 over peer memory -- histogram-free into fixed-capacity "
+                         "regions (default), or with exact counts first (fused) -- or partition + NCCL all-to-all")
     ap.add_argument("--chunks", type=int, default=1,
                     help="fused exchange: split S into this many chunks and overlap the exchange of chunk c+1 "
                          "with pass 2 + join of chunk c (a join is additive over disjoint parts of S)")
@@ -252,7 +253,8 @@ class Rank:
         self.s_desc = "counter-based FK (hj_generate kind 1, seed 54321: |S|/|R| permutations of 1..|R|)"
         self.hS = None
         self.gen_s = time.time() - t0
-        self.fused = G > 1 and args.exchange == "fused"
+        self.fused = G > 1 and args.exchange in ("fused", "regions")
+        self.regions = G > 1 and args.exchange == "regions"
         if G > 1:
             cap_r = self.n + self.n // 32 + 65536
             cap_s = self.m + self.m // 32 + 65536
@@ -274,6 +276,14 @@ class Rank:
             handles = self.exchange.exchange_ipc_handles((self.h.ipc_export(self.recvR), self.h.ipc_export(self.recvS)))
             self.peerR = [self.recvR if g == self.rank else self.h.ipc_open(handles[g][0]) for g in range(G)]
             self.peerS = [self.recvS if g == self.rank else self.h.ipc_open(handles[g][1]) for g in range(G)]
+            if self.regions:
+                ex = self.exchange
+                self.reg_cap = (ex.region_cap(self.n, G, self.f1), ex.region_cap(self.m, G, self.f1))
+                self.reg_trash = (self.f1 * G * self.reg_cap[0], self.f1 * G * self.reg_cap[1])
+                assert self.reg_trash[0] + 16386 <= cap_r and self.reg_trash[1] + 16386 <= cap_s
+                self.reg_init = (ex.region_cursor_init(self.rank, G, self.f1, self.reg_cap[0], dev),
+                                 ex.region_cursor_init(self.rank, G, self.f1, self.reg_cap[1], dev))
+                self.reg_vec = torch.zeros(2 * G * self.f1 + 1, dtype=torch.int64, device=dev)
             self.chunks = max(1, args.chunks)
             self.peer_ctas = args.peer_ctas
             self.cnt = torch.zeros((1 + self.chunks) * G * self.f1, dtype=torch.int64, device=dev)
@@ -319,6 +329,11 @@ class Rank:
             self.h.copy(self.dS.data_ptr(), self.hS.ctypes.data, self.m * 8)
         ex = self.exchange
         dom_bits = ex.domain_bits_for(self.domain)
+        if self.regions and self.chunks == 1:
+            out = self.step_regions(dom_bits)
+            if out is not None:
+                return out
+            self.region_fallbacks = getattr(self, "region_fallbacks", 0) + 1  # skewed keys: exact protocol
         if self.fused:
             return self.step_fused_chunked(dom_bits) if self.chunks > 1 else self.step_fused(dom_bits)
         # 1. split both slices by destination GPU (high key bits of the key domain)
@@ -375,6 +390,43 @@ class Rank:
         out = ex.reduce_result(res.matches, res.checksum, "cuda")
         t.append(time.perf_counter())
         self.fused_ms = [round((b - a) * 1e3, 3) for a, b in zip(t, t[1:])]  # hist, counts, scatter, barrier, join, reduce
+        return out
+
+    def step_regions(self, dom_bits):
+        """Histogram-free exchange (hj_peer_scatter_regions / hj_join_regions): no counting pass, the
+        all-gather of the final cursors is the only collective before the join and doubles as the barrier.
+        Returns None when a region overflowed anywhere (the caller redoes the step with exact counts)."""
+        torch, G, ex, gf = self.torch, self.world, self.exchange, self.world * self.f1
+        t = [time.perf_counter()]
+        v = self.reg_vec
+        v[:gf].copy_(self.reg_init[0])
+        v[gf:2 * gf].copy_(self.reg_init[1])
+        torch.cuda.synchronize()
+        ovf = self.h.peer_scatter_regions(self.dR.data_ptr(), self.n, G, dom_bits, self.b1, self.peerR, v.data_ptr(),
+                                          self.rank, self.reg_cap[0], self.reg_trash[0])
+        ovf |= self.h.peer_scatter_regions(self.dS.data_ptr(), self.m, G, dom_bits, self.b1, self.peerS,
+                                           v.data_ptr() + 8 * gf, self.rank, self.reg_cap[1], self.reg_trash[1])
+        v[2 * gf] = int(ovf)
+        t.append(time.perf_counter())
+        allf = ex.gather_counts(v)  # everybody's stores have landed once this returns
+        cur_r, nr = ex.regions_received(allf[:, :gf].contiguous(), self.rank, G, self.f1, self.reg_cap[0])
+        cur_s, ns = ex.regions_received(allf[:, gf:2 * gf].contiguous(), self.rank, G, self.f1, self.reg_cap[1])
+        own = (v[self.rank * self.f1:(self.rank + 1) * self.f1] - self.reg_init[0][:self.f1]).sum() + \
+            (v[gf + self.rank * self.f1:gf + (self.rank + 1) * self.f1] - self.reg_init[1][:self.f1]).sum()
+        nr, ns, own, any_ovf = torch.stack([nr, ns, own, allf[:, 2 * gf].sum()]).tolist()
+        t.append(time.perf_counter())
+        self.launches += 2
+        if any_ovf:
+            return None
+        self.nvlink_bytes += 8 * (self.n + self.m - own)
+        res = self.h.join_regions(self.recvR, nr, cur_r.data_ptr(), self.reg_cap[0], self.recvS, ns, cur_s.data_ptr(),
+                                  self.reg_cap[1], G)
+        t.append(time.perf_counter())
+        self.launches += res.kernel_launches
+        self.last = res
+        out = ex.reduce_result(res.matches, res.checksum, "cuda")
+        t.append(time.perf_counter())
+        self.fused_ms = [round((b - a) * 1e3, 3) for a, b in zip(t, t[1:])]  # scatter, gather, join, reduce
         return out
 
     def step_fused_chunked(self, dom_bits):
@@ -560,7 +612,9 @@ def run_b200(args):
                                f"(BASELINE configs[2] at N=1; x8 = configs[4])",
                    "algo": args.algo, "radix_bits": int(last.radix_bits), "passes": int(last.passes),
                    "tuples_per_step": tuples, "l2": "inputs (9 GiB/GPU) larger than L2, no flush needed",
-                   "exchange": "none" if G == 1 else ("fused with radix pass 1: stores into the owners' pass-1 buffers over NVLink (CUDA IPC)"
+                   "exchange": "none" if G == 1 else ("fused with radix pass 1, histogram-free: TMA stores into fixed-capacity regions of the owners' pass-1 buffers over NVLink (CUDA IPC)"
+                                                      if args.exchange == "regions" else
+                                                      "fused with radix pass 1: stores into the owners' pass-1 buffers over NVLink (CUDA IPC)"
                                                       if args.exchange == "fused" else
                                                       "range partition + torch.distributed all_to_all_single (NCCL)")},
         "phases_us": {k: round(v, 1) for k, v in ph.items()},
@@ -570,9 +624,16 @@ def run_b200(args):
     if G > 1:
         line["nvlink_bytes_per_gpu_per_step"] = int(nvl)
         if getattr(rk, "fused", False):
-            line["fused_exchange_ms_last_step"] = dict(zip(
-                ["peer_hist", "counts+cursors", "peer_scatter", "barrier", "pass2+join", "allreduce"], rk.fused_ms))
-            line["nvlink_gbs_in_peer_scatter"] = round(nvl / (rk.fused_ms[2] * 1e-3) / 1e9, 1)
+            if getattr(rk, "regions", False) and rk.chunks == 1 and not getattr(rk, "region_fallbacks", 0):
+                names, sc = ["peer_scatter", "cursor all-gather (= barrier)", "pass2+join", "allreduce"], 0
+            elif rk.chunks > 1:
+                names, sc = ["peer_hist", "counts+cursors", "scatter R + chunk 0", "pipeline", "allreduce"], 2
+            else:
+                names, sc = ["peer_hist", "counts+cursors", "peer_scatter", "barrier", "pass2+join", "allreduce"], 2
+            line["fused_exchange_ms_last_step"] = dict(zip(names, rk.fused_ms))
+            if rk.chunks == 1:
+                line["nvlink_gbs_in_peer_scatter"] = round(nvl / (rk.fused_ms[sc] * 1e-3) / 1e9, 1)
+            line["region_fallbacks"] = getattr(rk, "region_fallbacks", 0)
     if G == 1 and not args.no_cpu_baseline:
         v, desc, _ = cpu_reference_join(24, 27, 1, 1)
         line["cpu_baseline"] = dict(desc, value=round(v, 2), unit=UNIT)

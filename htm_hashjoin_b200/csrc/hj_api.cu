@@ -503,6 +503,11 @@ bool sc_tmain() {
   static const bool on = getenv("HJ_SC_TMAIN") != nullptr;
   return on;
 }
+// Bulk (TMA) flush per pass: one cp.async.bulk per run pays off while a run is long -- 4096-tuple tiles
+// over F <= 128 digits = 32+ tuples (scatter 2 at C3: 4.68 -> 4.09 ms); at 256 / 512 digits (16 / 8 tuples
+// per run, the pass 2 after a 4- / 8-GPU exchange) it LOSES to 8-byte stores from consecutive lanes:
+// 2.48 vs 2.27 ms and 3.33 vs 2.60 ms per 2^30-tuple launch.
+bool sc_bulk_for(u32 F) { return sc_bulk() && F % 2 == 0 && F <= 128; }
 // BULK shared memory on top of tile + F*16: one spare tile slot per digit (+2) and the run lengths
 size_t sc_bulk_extra(u32 F) { return (size_t)(F + 2) * 8 + (size_t)F * 4; }
 
@@ -510,7 +515,7 @@ template <int IPT, int MODE>
 int launch_scatter_tm(hj_handle* h, const u64* in, u64* out, const Digit& dg, u32 F, u32 nparent, const u64* poff,
                       const u64* ptiles, u64* cursors, u64 max_tiles) {
   // runs leave through bulk async copies (TMA) when the fan-out is even; HJ_SC_NO_BULK: 8-byte stores
-  const bool bulk = sc_bulk() && F % 2 == 0;
+  const bool bulk = sc_bulk_for(F);
   auto k = bulk ? rx_scatter_kernel<IPT, MODE, false, 0, true> : rx_scatter_kernel<IPT, MODE, false, 0, false>;
   size_t smem = (size_t)kScThreads * IPT * 8 + (size_t)F * 16 + (bulk ? sc_bulk_extra(F) : 0);
   CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -613,15 +618,19 @@ int radix_partition_rel_opt(hj_handle* h, const u64* in, u64 n, RelBufs& rb, con
   CK(cudaMemcpyAsync(rb.one.p, one, sizeof(one), cudaMemcpyHostToDevice, h->stream));
   h->launches++;
   if (evb >= 0) mark(h, evb + 2);
-  const bool bulk = sc_bulk() && F1 % 2 == 0 && F2 % 2 == 0;
+  // per pass: runs leave through bulk copies (TMA) while they are long enough (sc_bulk_for)
+  const bool bulk1 = sc_bulk_for(F1), bulk2 = sc_bulk_for(F2);
   // input tiles staged through shared memory by one bulk copy each (TMAIN), with the bulk flush only
-  const bool tmain = bulk && sc_tmain() && F1 <= 128 && F2 <= 128;  // beyond: the staging buffer costs a CTA per SM
-  auto k = tmain  ? rx_scatter_kernel<8, 0, false, 1, true, true>
-           : bulk ? rx_scatter_kernel<8, 0, false, 1, true>
-                  : rx_scatter_kernel<8, 0, false, 1, false>;
-  auto k2 = tmain  ? rx_scatter_kernel<8, 0, false, 2, true, true>
-            : bulk ? rx_scatter_kernel<8, 0, false, 2, true>
-                   : rx_scatter_kernel<8, 0, false, 2, false>;
+  const bool tmain = bulk1 && bulk2 && sc_tmain();
+  auto k = tmain   ? rx_scatter_kernel<8, 0, false, 1, true, true>
+           : bulk1 ? rx_scatter_kernel<8, 0, false, 1, true>
+                   : rx_scatter_kernel<8, 0, false, 1, false>;
+  auto k1b = tmain   ? rx_scatter_kernel<8, 0, false, 1, true, true>   // pass 2 after an exchange (key width unknown)
+             : bulk2 ? rx_scatter_kernel<8, 0, false, 1, true>
+                     : rx_scatter_kernel<8, 0, false, 1, false>;
+  auto k2 = tmain   ? rx_scatter_kernel<8, 0, false, 2, true, true>
+            : bulk2 ? rx_scatter_kernel<8, 0, false, 2, true>
+                    : rx_scatter_kernel<8, 0, false, 2, false>;
   const size_t stage = tmain ? (size_t)tile * 8 : 0;
   Digit d1, d2;
   memset(&d1, 0, sizeof(d1));
@@ -634,7 +643,7 @@ int radix_partition_rel_opt(hj_handle* h, const u64* in, u64 n, RelBufs& rb, con
     if ((1u << pshift) != reg->n_src || nparent2 > (u32)kScParentCache) return HJ_EINVAL;
   }
   if (!pre1_off && !reg) {
-    size_t smem = stage + (size_t)tile * 8 + (size_t)F1 * 16 + (bulk ? sc_bulk_extra(F1) : 0);
+    size_t smem = stage + (size_t)tile * 8 + (size_t)F1 * 16 + (bulk1 ? sc_bulk_extra(F1) : 0);
     CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int grid = grid_for(h, (const void*)k, kScThreads, smem);
     if ((u64)grid > ntiles) grid = (int)(ntiles ? ntiles : 1);
@@ -649,8 +658,8 @@ int radix_partition_rel_opt(hj_handle* h, const u64* in, u64 n, RelBufs& rb, con
   else rx_opt_parents_kernel<<<1, 1024, 0, h->stream>>>(rb.pcur.p, F1, C1, tile, rb.poff.p, rb.pend.p, rb.ptiles.p);
   h->launches++;
   {
-    auto kp2 = (pre1_off || reg) ? k : k2;  // after the fused exchange nobody has looked at the key width yet
-    size_t smem = stage + (size_t)tile * 8 + (size_t)F2 * 16 + (bulk ? sc_bulk_extra(F2) : 0);
+    auto kp2 = (pre1_off || reg) ? k1b : k2;  // after the fused exchange nobody has looked at the key width yet
+    size_t smem = stage + (size_t)tile * 8 + (size_t)F2 * 16 + (bulk2 ? sc_bulk_extra(F2) : 0);
     CK(cudaFuncSetAttribute(kp2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int grid = grid_for(h, (const void*)kp2, kScThreads, smem);
     if ((u64)grid > ntiles + nparent2) grid = (int)(ntiles + nparent2);

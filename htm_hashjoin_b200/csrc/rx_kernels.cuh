@@ -459,7 +459,7 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
     // buffer is free: every thread passed the barrier above with its tuples in registers)
     const u32 cnt_cur = cnt;
     t += gridDim.x;
-    if (t < total_tiles) {
+    if (TMAIN && t < total_tiles) {
       locate(t, p, cnt);
       via_tma = tma_ok(cnt);
       if (via_tma) fetch_tma();
@@ -469,8 +469,13 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
     for (int j = 0; j < IPT; j++)
       if (v[j] != 0ull) tile[lbase[dr[j] >> 16] + (dr[j] & 0xffffu)] = v[j];
 
-    // v is dead: start the next tile's register loads before flushing this one
-    if (t < total_tiles && !via_tma) fetch_regs(cnt);
+    // v is dead: start the next tile's register loads before flushing this one.  (Without TMAIN the
+    // tile is located only now: locating it before the placement keeps three more registers alive
+    // across it, which spilled under the 40-register cap and cost 25 % in the 512-way pass.)
+    if (t < total_tiles) {
+      if (!TMAIN) locate(t, p, cnt);
+      if (!TMAIN || !via_tma) fetch_regs(cnt);
+    }
     __syncthreads();
 
     if (BULK) {

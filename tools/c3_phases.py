@@ -20,6 +20,7 @@ ap.add_argument("--log-r", type=int, default=27)
 ap.add_argument("--log-s", type=int, default=30)
 ap.add_argument("--bits", type=int, default=0)
 ap.add_argument("--passes", type=int, default=0)
+ap.add_argument("--pass1-bits", type=int, default=0)
 ap.add_argument("--reps", type=int, default=5)
 ap.add_argument("--tag", default="")
 a = ap.parse_args()
@@ -29,6 +30,8 @@ if a.bits:
     kw["num_partitions"] = 1 << a.bits
 if a.passes:
     kw["passes"] = a.passes
+if a.pass1_bits:
+    kw["pass1_bits"] = a.pass1_bits
 with hj.HashJoin("radix", **kw) as h:
     dR, dS = h.device_alloc(n * 8), h.device_alloc(m * 8)
     h.generate(1, 0, n, n, 12345, dR)
