@@ -699,7 +699,10 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
   const u64 per = (n >> pl.bits) + 1;
   u64 need = per + 64;
   for (u64 r = 1; r * r < per * 64; r++) need = per + 64 + r;  // + 8*sqrt(per)
-  const bool use_l2 = dS && (getenv("HJ_FORCE_L2JOIN") || need > 21000) && !getenv("HJ_NO_L2JOIN");
+  // up to three shared-memory chunks per R partition (S_p is probed once per chunk) still beat the L2 table:
+  // 2^12 partitions at C3 (2 chunks) 17.6 ms through L2; HJ_L2_MIN_NEED overrides the switch point
+  static const u64 l2_min_need = getenv("HJ_L2_MIN_NEED") ? strtoull(getenv("HJ_L2_MIN_NEED"), nullptr, 10) : 63000;
+  const bool use_l2 = dS && (getenv("HJ_FORCE_L2JOIN") || need > l2_min_need) && !getenv("HJ_NO_L2JOIN");
   // Histogram-free partitioning (ScOpt, rx_kernels.cuh) for the 2-pass shared-memory join; the
   // exact, histogram-based layout everywhere else and after an overflow on this handle.
   const bool opt = dS && (!pre1 || (offR1 && offS1) || (regR && regS)) && !use_l2 && pl.passes == 2 && !h->no_optimistic && !force_exact &&

@@ -58,8 +58,11 @@ rx_join32_mat_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, c
     const u64 out0 = WRITE ? part_cnt[p] : 0ull;
     __syncthreads();  // s_cur of the previous partition has been read
     if (tid == 0) s_cur = 0ull;
-    for (u64 c0 = r0; c0 < r1 && s1 > s0; c0 += chunk_cap) {
-      const u64 c1 = c0 + chunk_cap < r1 ? c0 + chunk_cap : r1;
+    const u64 nr = r1 - r0;
+    const u64 nchunk = (nr + chunk_cap - 1) / chunk_cap;  // equal chunks, as rx_join32_kernel
+    const u64 cstep = nchunk > 1 ? (nr + nchunk - 1) / nchunk : chunk_cap;
+    for (u64 c0 = r0; c0 < r1 && s1 > s0; c0 += cstep) {
+      const u64 c1 = c0 + cstep < r1 ? c0 + cstep : r1;
       __syncthreads();
       for (u32 a = tab.base + 16u * tid; a < tab_end; a += 16u * THREADS)
         sts_v4(a, kJ32Empty, kJ32Empty, kJ32Empty, kJ32Empty);

@@ -134,6 +134,21 @@ def test_radix_oversized_partitions_l2_table(hj, oracle):
         assert res.max_partition == n // 2
 
 
+@pytest.mark.parametrize("dist", ["shuffle", "uniform"])
+def test_radix_partitions_of_two_chunks_stay_in_shared_memory(hj, oracle, dist):
+    """R partitions of up to three table chunks (here 32768 tuples = 2 chunks) take the shared-memory join by
+    default, S_p probed once per chunk; the L2 table starts beyond that."""
+    n = 1 << 18
+    R, S = _inputs(hj, dist, 16, n)
+    with hj.HashJoin("radix", num_partitions=8, passes=2) as h:
+        res = h.join(R, S)
+        assert (res.matches, res.checksum) == oracle.true_join(R, S)
+        if dist == "shuffle":
+            assert res.max_partition == n // 8
+        res2, pairs = h.join_materialize(R, S)  # count pass over chunked partitions
+        assert pairs == res.matches
+
+
 def test_radix_oversized_partitions_chunked(hj, oracle, monkeypatch):
     """Same with the L2 path switched off: R partitions go through shared memory in chunks."""
     monkeypatch.setenv("HJ_NO_L2JOIN", "1")
@@ -284,7 +299,11 @@ def test_fused_exchange_logical_ranks(hj, oracle):
                     bufs = [h.device_alloc((int(recv[d]) + 2) * 8) for d in range(G)]
                 cur = cur.contiguous()
                 torch.cuda.synchronize()
-                h.peer_scatter(d_slices[g][0], slices[g].size, G, dom_bits, b1, bufs, cur.data_ptr())
+                if g == 0:
+                    h.peer_scatter(d_slices[g][0], slices[g].size, G, dom_bits, b1, bufs, cur.data_ptr())
+                else:  # the enqueue-only variant on a limited number of CTAs
+                    h.peer_scatter_async(d_slices[g][0], slices[g].size, G, dom_bits, b1, bufs, cur.data_ptr(), 16)
+                    h.sync()
             recv_bufs[name], recv_n[name] = bufs, [int(x) for x in recv]
             # what arrived at logical rank 0 is pass-1 partitioned and in its key range
             got = h.to_host(bufs[0], recv_n[name][0])

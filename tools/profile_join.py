@@ -3,6 +3,7 @@
 
   python tools/profile_join.py radix   # |R|=2^25 PK, |S|=2^28 FK, 2^11 partitions in 2 passes (C3's partition size)
   python tools/profile_join.py global  # atomic table, |R|=|S|=2^24, uniform then sorted
+  python tools/profile_join.py mat     # hj_join_materialize on the radix workload (count / scan / write kernels)
 """
 import sys
 import os
@@ -21,6 +22,17 @@ if what == "radix":
         for _ in range(2):
             r = h.join((dR, n), (dS, m))
             assert r.matches == m
+            print({k: round(v, 1) for k, v in r.as_dict().items() if k.startswith("us_") and v})
+elif what == "mat":
+    n, m = 1 << 25, 1 << 28
+    with hj.HashJoin("radix", num_partitions=1 << 11, passes=2) as h:
+        dR, dS = h.device_alloc(n * 8), h.device_alloc(m * 8)
+        h.generate(1, 0, n, n, 12345, dR)
+        h.generate(1, 0, m, n, 54321, dS)
+        d_out = h.device_alloc(m * 16)
+        for _ in range(2):
+            r, pairs = h.join_materialize((dR, n), (dS, m), d_out, m)
+            assert r.matches == m == pairs
             print({k: round(v, 1) for k, v in r.as_dict().items() if k.startswith("us_") and v})
 else:
     n = 1 << 24
