@@ -459,7 +459,7 @@ int ensure_rel(hj_handle* h, RelBufs& rb, u64 n, const RadixPlan& pl, bool pre1 
   u64 nb = 1ull << pl.bits;
   u64 np = (1ull << pl.b1) * n_src;  // parents of pass 2 (one per source rank after a region exchange)
   // histogram-free layout: 2^bits regions + one scatter tile of scratch for diverted claims
-  const u64 elems = opt ? nb * opt_region_cap(n, pl.bits) + kScThreads * 8 + 2 : n + 2;
+  const u64 elems = opt ? nb * opt_region_cap(n, pl.bits) + kScThreads * 32 + 2 : n + 2;
   if ((rc = ensure(h, rb.out, elems))) return rc;
   if (pl.passes == 2 && !pre1 && (rc = ensure(h, rb.tmp, elems))) return rc;
   if (opt && (rc = ensure(h, rb.pend, np + 2))) return rc;
@@ -507,7 +507,26 @@ bool sc_tmain() {
 // over F <= 128 digits = 32+ tuples (scatter 2 at C3: 4.68 -> 4.09 ms); at 256 / 512 digits (16 / 8 tuples
 // per run, the pass 2 after a 4- / 8-GPU exchange) it LOSES to 8-byte stores from consecutive lanes:
 // 2.48 vs 2.27 ms and 3.33 vs 2.60 ms per 2^30-tuple launch.
-bool sc_bulk_for(u32 F) { return sc_bulk() && F % 2 == 0 && F <= 128; }
+bool sc_bulk_for(u32 F, u32 tile = kScThreads * 8) { return sc_bulk() && F % 2 == 0 && F <= tile / 32; }
+
+// Tile of the histogram-free passes: 512 threads x IPT tuples.  8192-tuple tiles (IPT 16, two CTAs per SM,
+// 64 registers) beat 4096-tuple ones (IPT 8, three CTAs, 40 registers, a few spills): runs are twice as long
+// and every tuple pays for half as many barriers -- C3: scatter 1 3.77 -> 3.37 ms (87 % of the HBM roofline),
+// scatter 2 4.14 -> 3.57 ms, 116 k -> 128 k Mtuples/s.  HJ_SC_IPT = 8 | 16 | 32 overrides.
+u32 sc_opt_ipt() {
+  static const u32 v = [] {
+    const char* e = getenv("HJ_SC_IPT");
+    const int x = e ? atoi(e) : 16;
+    return (u32)(x == 8 || x == 32 ? x : 16);
+  }();
+  return v;
+}
+using ScKernel = void (*)(const u64*, u64*, Digit, u32, u32, const u64*, const u64*, u64*, u64* const*, ScOpt);
+template <int IPT>
+ScKernel sc_opt_kernel(int opt, bool bulk) {
+  if (opt == 1) return bulk ? rx_scatter_kernel<IPT, 0, false, 1, true> : rx_scatter_kernel<IPT, 0, false, 1, false>;
+  return bulk ? rx_scatter_kernel<IPT, 0, false, 2, true> : rx_scatter_kernel<IPT, 0, false, 2, false>;
+}
 // BULK shared memory on top of tile + F*16: one spare tile slot per digit (+2) and the run lengths
 size_t sc_bulk_extra(u32 F) { return (size_t)(F + 2) * 8 + (size_t)F * 4; }
 
@@ -609,7 +628,8 @@ struct Pre1Regions {
 int radix_partition_rel_opt(hj_handle* h, const u64* in, u64 n, RelBufs& rb, const RadixPlan& pl, int evb,
                             const u64* pre1_off = nullptr, const Pre1Regions* reg = nullptr) {
   const u32 nb = 1u << pl.bits, F1 = 1u << pl.b1, F2 = 1u << pl.b2;
-  const u32 tile = kScThreads * pl.tile_ipt;
+  const u32 ipt = sc_opt_ipt();
+  const u32 tile = kScThreads * ipt;
   const u64 C2 = opt_region_cap(n, pl.bits), C1 = C2 * F2;
   const u64 ntiles = (n + tile - 1) / tile;
   if (evb >= 0) { mark(h, evb); mark(h, evb + 1); }
@@ -619,18 +639,20 @@ int radix_partition_rel_opt(hj_handle* h, const u64* in, u64 n, RelBufs& rb, con
   h->launches++;
   if (evb >= 0) mark(h, evb + 2);
   // per pass: runs leave through bulk copies (TMA) while they are long enough (sc_bulk_for)
-  const bool bulk1 = sc_bulk_for(F1), bulk2 = sc_bulk_for(F2);
-  // input tiles staged through shared memory by one bulk copy each (TMAIN), with the bulk flush only
-  const bool tmain = bulk1 && bulk2 && sc_tmain();
-  auto k = tmain   ? rx_scatter_kernel<8, 0, false, 1, true, true>
-           : bulk1 ? rx_scatter_kernel<8, 0, false, 1, true>
-                   : rx_scatter_kernel<8, 0, false, 1, false>;
-  auto k1b = tmain   ? rx_scatter_kernel<8, 0, false, 1, true, true>   // pass 2 after an exchange (key width unknown)
-             : bulk2 ? rx_scatter_kernel<8, 0, false, 1, true>
-                     : rx_scatter_kernel<8, 0, false, 1, false>;
-  auto k2 = tmain   ? rx_scatter_kernel<8, 0, false, 2, true, true>
-            : bulk2 ? rx_scatter_kernel<8, 0, false, 2, true>
-                    : rx_scatter_kernel<8, 0, false, 2, false>;
+  const bool bulk1 = sc_bulk_for(F1, tile), bulk2 = sc_bulk_for(F2, tile);
+  // input tiles staged through shared memory by one bulk copy each (TMAIN): 4096-tuple tiles + bulk flush only
+  const bool tmain = ipt == 8 && bulk1 && bulk2 && sc_tmain();
+  ScKernel k, k1b, k2;  // pass 1; pass 2 after an exchange (key width still unknown); pass 2
+  if (tmain) {
+    k = k1b = rx_scatter_kernel<8, 0, false, 1, true, true>;
+    k2 = rx_scatter_kernel<8, 0, false, 2, true, true>;
+  } else if (ipt == 32) {
+    k = sc_opt_kernel<32>(1, bulk1); k1b = sc_opt_kernel<32>(1, bulk2); k2 = sc_opt_kernel<32>(2, bulk2);
+  } else if (ipt == 16) {
+    k = sc_opt_kernel<16>(1, bulk1); k1b = sc_opt_kernel<16>(1, bulk2); k2 = sc_opt_kernel<16>(2, bulk2);
+  } else {
+    k = sc_opt_kernel<8>(1, bulk1); k1b = sc_opt_kernel<8>(1, bulk2); k2 = sc_opt_kernel<8>(2, bulk2);
+  }
   const size_t stage = tmain ? (size_t)tile * 8 : 0;
   Digit d1, d2;
   memset(&d1, 0, sizeof(d1));

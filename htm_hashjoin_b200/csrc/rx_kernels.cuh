@@ -276,7 +276,7 @@ __device__ __forceinline__ void mbar_wait(u32 a, u32 parity) {
 // register loads (profiles/r01_scatter_tmain_vs_regs.jsonl) -- the extra shared-memory write + read
 // per tuple costs more than the exposed load latency it removes; kept opt-in (HJ_SC_TMAIN=1).
 template <int IPT, int MODE, bool PEER = false, int OPT = 0, bool BULK = false, bool TMAIN = false>
-__global__ void __launch_bounds__(kScThreads, PEER ? (IPT >= 32 ? 1 : 2) : 3)
+__global__ void __launch_bounds__(kScThreads, IPT >= 32 ? 1 : (PEER || IPT >= 16) ? 2 : 3)
 rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u32 F, u32 nparent,
                   const u64* __restrict__ parent_off, const u64* __restrict__ parent_tiles,
                   u64* __restrict__ cursors, u64* const* __restrict__ peer_out, ScOpt opt) {
