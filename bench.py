@@ -585,13 +585,13 @@ def run_b200(args):
             # HBM roofline line is pass 2 alone
             P = 1
             sc_us, sc_bytes = ph["us_scatter2"], 16.0 * (n_loc + m_loc)
-        roof = {"bound": "hbm", "kernel": f"rx_scatter_kernel<8> ({2 * P} launches/step: R and S x {P} passes)",
+        roof = {"bound": "hbm", "kernel": f"rx_scatter_kernel<16> ({2 * P} launches/step: R and S x {P} passes)",
                 "achieved": round(sc_bytes / (sc_us * 1e-6) / 1e9, 1), "peak": peak, "unit": "GB/s",
                 "frac": round(sc_bytes / (sc_us * 1e-6) / 1e9 / peak, 4),
-                # ncu --set full, profiles/r01_ncu_radix_v3_raw.csv: the S pass-2 launch over 2^28 tuples moved
-                # dram__bytes_read 2.148 GB + dram__bytes_write 2.090 GB = 15.79 B/tuple (algorithmic: 16)
-                "traffic": int(15.79 * sc_bytes / 16.0 / (2 * P)),
-                "traffic_source": "15.79 B/tuple measured by ncu at |S|=2^28 (profiles/r01_ncu_radix_v3_raw.csv), "
+                # ncu --set full, profiles/r01_ncu_radix_v4_raw.csv: the S launches over 2^28 tuples moved
+                # dram__bytes_read 2.148 GB + dram__bytes_write 2.100 GB = 15.83 B/tuple (algorithmic: 16)
+                "traffic": int(15.83 * sc_bytes / 16.0 / (2 * P)),
+                "traffic_source": "15.83 B/tuple measured by ncu at |S|=2^28 (profiles/r01_ncu_radix_v4_raw.csv), "
                                   "scaled to this launch size",
                 "peak_source": peak_src, "avg_launch_us": round(sc_us / (2 * P), 1),
                 "algorithmic_bytes_per_launch": int(sc_bytes / (2 * P)),
