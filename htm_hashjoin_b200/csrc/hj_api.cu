@@ -394,6 +394,9 @@ int clear_probe_counters(hj_handle* h) {
 
 // ---- radix --------------------------------------------------------------------
 
+// tile of the exact-layout passes (rx_hist + rx_scan offsets): 512 x 16 = 8192 tuples, as the histogram-free ones
+constexpr int kExactIPT = 16;
+
 struct RadixPlan {
   u32 bits, passes, b1, b2;
   u32 slots;        // join table slots
@@ -440,7 +443,7 @@ int plan_radix(hj_handle* h, u64 n, RadixPlan* pl) {
   while (cap * 2 * sizeof(u64) <= h->smem_optin - 1024) cap *= 2;  // 16384 slots at 227 KB
   if (slots > cap) slots = cap;
   pl->slots = (u32)slots;
-  pl->tile_ipt = 8;
+  pl->tile_ipt = kExactIPT;
   return HJ_OK;
 }
 
@@ -507,7 +510,7 @@ bool sc_tmain() {
 // over F <= 128 digits = 32+ tuples (scatter 2 at C3: 4.68 -> 4.09 ms); at 256 / 512 digits (16 / 8 tuples
 // per run, the pass 2 after a 4- / 8-GPU exchange) it LOSES to 8-byte stores from consecutive lanes:
 // 2.48 vs 2.27 ms and 3.33 vs 2.60 ms per 2^30-tuple launch.
-bool sc_bulk_for(u32 F, u32 tile = kScThreads * 8) { return sc_bulk() && F % 2 == 0 && F <= tile / 32; }
+bool sc_bulk_for(u32 F, u32 tile) { return sc_bulk() && F % 2 == 0 && F <= tile / 32; }
 
 // Tile of the histogram-free passes: 512 threads x IPT tuples.  8192-tuple tiles (IPT 16, two CTAs per SM,
 // 64 registers) beat 4096-tuple ones (IPT 8, three CTAs, 40 registers, a few spills): runs are twice as long
@@ -534,7 +537,7 @@ template <int IPT, int MODE>
 int launch_scatter_tm(hj_handle* h, const u64* in, u64* out, const Digit& dg, u32 F, u32 nparent, const u64* poff,
                       const u64* ptiles, u64* cursors, u64 max_tiles) {
   // runs leave through bulk async copies (TMA) when the fan-out is even; HJ_SC_NO_BULK: 8-byte stores
-  const bool bulk = sc_bulk_for(F);
+  const bool bulk = sc_bulk_for(F, kScThreads * IPT);
   auto k = bulk ? rx_scatter_kernel<IPT, MODE, false, 0, true> : rx_scatter_kernel<IPT, MODE, false, 0, false>;
   size_t smem = (size_t)kScThreads * IPT * 8 + (size_t)F * 16 + (bulk ? sc_bulk_extra(F) : 0);
   CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -589,7 +592,7 @@ int radix_partition_rel(hj_handle* h, const u64* in, u64 n, RelBufs& rb, const R
   const u64 max_tiles1 = (n + tile - 1) / tile;
   int rc;
   if (pl.passes == 1) {
-    if ((rc = launch_scatter_t<8>(h, in, rb.out.p, full, nb, 1, rb.poff.p, rb.ptiles.p, rb.cursors.p, max_tiles1)))
+    if ((rc = launch_scatter_t<kExactIPT>(h, in, rb.out.p, full, nb, 1, rb.poff.p, rb.ptiles.p, rb.cursors.p, max_tiles1)))
       return rc;
     if (evb >= 0) { mark(h, evb + 3); mark(h, evb + 4); }
   } else {
@@ -598,14 +601,14 @@ int radix_partition_rel(hj_handle* h, const u64* in, u64 n, RelBufs& rb, const R
     memset(&d1, 0, sizeof(d1));
     d1.key_mask = h->cfg.key_mask; d1.mode = 0; d1.shift = 0; d1.bits = pl.b1;
     if (!pre1 &&
-        (rc = launch_scatter_t<8>(h, in, rb.tmp.p, d1, F1, 1, rb.one.p, rb.one.p + 2, rb.pcur.p, max_tiles1)))
+        (rc = launch_scatter_t<kExactIPT>(h, in, rb.tmp.p, d1, F1, 1, rb.one.p, rb.one.p + 2, rb.pcur.p, max_tiles1)))
       return rc;
     if (evb >= 0) mark(h, evb + 3);
     // pass 2: every pass-1 partition by the next b2 bits into out (radix_cluster, :402-440)
     Digit d2;
     memset(&d2, 0, sizeof(d2));
     d2.key_mask = h->cfg.key_mask; d2.mode = 0; d2.shift = pl.b1; d2.bits = pl.b2;
-    if ((rc = launch_scatter_t<8>(h, pre1 ? in : rb.tmp.p, rb.out.p, d2, F2, F1, rb.poff.p, rb.ptiles.p,
+    if ((rc = launch_scatter_t<kExactIPT>(h, pre1 ? in : rb.tmp.p, rb.out.p, d2, F2, F1, rb.poff.p, rb.ptiles.p,
                                   rb.cursors.p, max_tiles1 + F1)))
       return rc;
     if (evb >= 0) mark(h, evb + 4);
@@ -1330,13 +1333,13 @@ int hj_radix_partition(hj_handle* h, const uint64_t* in, uint64_t n, uint32_t sh
   Digit dg;
   memset(&dg, 0, sizeof(dg));
   dg.key_mask = h->cfg.key_mask; dg.mode = 0; dg.shift = shift; dg.bits = bits;
-  const u32 tile = kScThreads * 8;
+  const u32 tile = kScThreads * kExactIPT;
   CK(cudaMemsetAsync(rb.ghist.p, 0, F * sizeof(u64), h->stream));
   if ((rc = launch_hist(h, (const u64*)in, n, dg, F, rb.ghist.p))) return rc;
   rx_scan_kernel<<<1, kScanThreads, 0, h->stream>>>(rb.ghist.p, F, (u64*)offsets, rb.cursors.p, F, rb.poff.p,
                                                     rb.pcur.p, rb.ptiles.p, rb.one.p, tile, nullptr);
   CK(cudaGetLastError());
-  if ((rc = launch_scatter_t<8>(h, (const u64*)in, (u64*)out, dg, F, 1, rb.poff.p, rb.ptiles.p, rb.cursors.p,
+  if ((rc = launch_scatter_t<kExactIPT>(h, (const u64*)in, (u64*)out, dg, F, 1, rb.poff.p, rb.ptiles.p, rb.cursors.p,
                                 (n + tile - 1) / tile)))
     return rc;
   CK(cudaStreamSynchronize(h->stream));
@@ -1360,13 +1363,13 @@ int hj_exchange_partition(hj_handle* h, const uint64_t* in, uint64_t n, uint32_t
   Digit dg;
   memset(&dg, 0, sizeof(dg));
   dg.key_mask = h->cfg.key_mask; dg.mode = 2; dg.ndest = n_dest; dg.domain_bits = domain_bits;
-  const u32 tile = kScThreads * 8;
+  const u32 tile = kScThreads * kExactIPT;
   CK(cudaMemsetAsync(rb.ghist.p, 0, F * sizeof(u64), h->stream));
   if ((rc = launch_hist(h, (const u64*)in, n, dg, F, rb.ghist.p))) return rc;
   rx_scan_kernel<<<1, kScanThreads, 0, h->stream>>>(rb.ghist.p, F, (u64*)offsets, rb.cursors.p, F, rb.poff.p,
                                                     rb.pcur.p, rb.ptiles.p, rb.one.p, tile, nullptr);
   CK(cudaGetLastError());
-  if ((rc = launch_scatter_t<8>(h, (const u64*)in, (u64*)out, dg, F, 1, rb.poff.p, rb.ptiles.p, rb.cursors.p,
+  if ((rc = launch_scatter_t<kExactIPT>(h, (const u64*)in, (u64*)out, dg, F, 1, rb.poff.p, rb.ptiles.p, rb.cursors.p,
                                 (n + tile - 1) / tile)))
     return rc;
   CK(cudaStreamSynchronize(h->stream));
