@@ -857,6 +857,8 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
       case 3: J32V(512, 8, 2, 2);
       case 5: J32V(256, 8, 4, 2);
       case 10: J32V(1024, 4, 1, 2);
+      case 11: J32V(1024, 6, 1, 2);
+      case 12: J32V(1024, 8, 1, 2);
       default: J32V(384, 4, 4, 2);
     }
 #undef J32V

@@ -360,7 +360,7 @@ rx_join32_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const
           }
         };
         auto process = [&](u64 (&v)[BATCH], u64 bi) {
-          constexpr int G = BATCH < 4 ? BATCH : 4;  // bucket loads in flight per thread
+          constexpr int G = BATCH < 4 ? BATCH : (BATCH % 4 == 0 ? 4 : 2);  // bucket loads in flight per thread
           if (bi < nfull) {
 #pragma unroll
             for (int g = 0; g < BATCH; g += G) j32_probe_unique<W, G, false>(tab, v + g, acc);
