@@ -1045,7 +1045,8 @@ void hj_destroy(hj_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
   if (h->stream) cudaStreamSynchronize(h->stream);
-  DevBuf* bufs[] = {&h->table, &h->ovf_table, &h->ovf_list, &h->stageR, &h->stageS, &h->flush, &h->peer_ptrs};
+  DevBuf* bufs[] = {&h->table, &h->ovf_table, &h->ovf_list, &h->stageR, &h->stageS, &h->flush,
+                    &h->peer_ptrs, &h->tasks, &h->mat_cnt};
   for (DevBuf* b : bufs)
     if (b->p) cudaFree(b->p);
   for (RelBufs& rb : h->rb) {
