@@ -21,13 +21,13 @@ import json
 import numpy as np
 
 from . import _capi
-from ._capi import (HJ_ALGO_ADAPTIVE, HJ_ALGO_ATOMIC, HJ_ALGO_NOCC, HJ_ALGO_RADIX, HJ_EINVAL, HJ_EOVERFLOW, HJ_OK,
-                    HJ_PATH_GLOBAL, HJ_PATH_RADIX, hj_config, hj_result)
+from ._capi import (HJ_ALGO_ADAPTIVE, HJ_ALGO_ATOMIC, HJ_ALGO_NOCC, HJ_ALGO_RADIX, HJ_ALGO_SORTMERGE, HJ_EINVAL,
+                    HJ_EOVERFLOW, HJ_OK, HJ_PATH_GLOBAL, HJ_PATH_RADIX, HJ_PATH_SORTMERGE, hj_config, hj_result)
 
 lib = _capi.load()  # raises ImportError if libhj_b200.so is missing
 
 ALGOS = {"atomic": HJ_ALGO_ATOMIC, "nocc": HJ_ALGO_NOCC, "radix": HJ_ALGO_RADIX,
-         "adaptive": HJ_ALGO_ADAPTIVE, "htm": HJ_ALGO_ADAPTIVE}
+         "adaptive": HJ_ALGO_ADAPTIVE, "htm": HJ_ALGO_ADAPTIVE, "sortmerge": HJ_ALGO_SORTMERGE}
 
 
 class HJError(RuntimeError):
@@ -322,6 +322,11 @@ def NoCCHashBuild(relR, rSize=None, relS=None, sSize=None, scaleOutput=2, numPar
 def HTMHashBuild(relR, rSize=None, relS=None, sSize=None, transactionSize=16, scaleOutput=2, numPartitions=64,
                  probeLength=4):
     return _ref_run("htm", relR, rSize, relS, sSize, transactionSize, scaleOutput, numPartitions, probeLength)
+
+
+def SortMerge(build, buildSize=None, probe=None, probeSize=None, numPartitions=64):
+    """SortMerge.hpp:5-6 -- the sort-merge comparator (partitioned sort-merge join on the GPU)."""
+    return _ref_run("sortmerge", build, buildSize, probe, probeSize, 0, 2, numPartitions, 4)
 
 
 def PRO(relR, relS=None, nthreads=1, radix_bits=14, passes=2):

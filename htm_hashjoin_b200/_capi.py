@@ -11,8 +11,8 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "csrc", "libhj_b200.so")
 
 HJ_OK, HJ_EINVAL, HJ_ENOMEM, HJ_ECUDA, HJ_EOVERFLOW, HJ_ESTATE = 0, -1, -2, -3, -4, -5
-HJ_ALGO_ATOMIC, HJ_ALGO_NOCC, HJ_ALGO_RADIX, HJ_ALGO_ADAPTIVE = 0, 1, 2, 3
-HJ_PATH_NONE, HJ_PATH_GLOBAL, HJ_PATH_RADIX = 0, 1, 2
+HJ_ALGO_ATOMIC, HJ_ALGO_NOCC, HJ_ALGO_RADIX, HJ_ALGO_ADAPTIVE, HJ_ALGO_SORTMERGE = 0, 1, 2, 3, 4
+HJ_PATH_NONE, HJ_PATH_GLOBAL, HJ_PATH_RADIX, HJ_PATH_SORTMERGE = 0, 1, 2, 3
 
 # every symbol include/hj_b200.h declares (tests check the library exports them all)
 ABI_SYMBOLS = [

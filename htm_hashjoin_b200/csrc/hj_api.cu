@@ -21,6 +21,7 @@
 #include "rx_join32.cuh"
 #include "rx_joinl2.cuh"
 #include "rx_joinmat.cuh"
+#include "rx_sortmerge.cuh"
 
 using namespace hj;
 
@@ -406,7 +407,7 @@ struct RadixPlan {
 constexpr u32 kMaxBitsPerPass = 12;
 constexpr u32 kMaxTotalBits = 15;  // 2^15 bins * 4 B = 128 KiB privatised histogram
 
-int plan_radix(hj_handle* h, u64 n, RadixPlan* pl) {
+int plan_radix(hj_handle* h, u64 n, RadixPlan* pl, u64 target_per = 16384) {
   u32 bits = 0;
   if (h->cfg.num_partitions) {
     u32 f = h->cfg.num_partitions;
@@ -417,7 +418,7 @@ int plan_radix(hj_handle* h, u64 n, RadixPlan* pl) {
     // 1024-thread CTA per SM); measured at C3: 13 bits (6+7) 11.9 ms, 14 bits 12.2, 15 bits 12.7
     // (cheaper scatter passes outweigh the slower 1-CTA join).  Mid-size inputs get at least 2048
     // partitions so every SM has several.
-    while (bits < kMaxTotalBits && (n >> bits) > 16384) bits++;
+    while (bits < kMaxTotalBits && (n >> bits) > target_per) bits++;
     while (bits < 11 && (n >> bits) > 2048) bits++;
     if (bits < 4) bits = 4;
   }
@@ -709,10 +710,11 @@ struct MatReq {
 int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS, u64 m, bool pendS, hj_result* res,
                    bool pre1 = false, bool force_exact = false, const u64* offR1 = nullptr,
                    const u64* offS1 = nullptr, MatReq* mat = nullptr, const Pre1Regions* regR = nullptr,
-                   const Pre1Regions* regS = nullptr) {
+                   const Pre1Regions* regS = nullptr, bool sortmerge = false) {
   RadixPlan pl;
   int rc;
-  if ((rc = plan_radix(h, n, &pl))) {
+  // sort-merge: R partitions of <= 4096 tuples sort in one 8192-element shared-memory network with slack
+  if ((rc = plan_radix(h, n, &pl, sortmerge ? 4096 : 16384))) {
     snprintf(h->err, sizeof(h->err), "radix plan: numPartitions must be a power of two <= 2^%u (<= 2^%u for 1 pass)",
              kMaxTotalBits, kMaxBitsPerPass);
     return rc;
@@ -727,7 +729,11 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
   // up to three shared-memory chunks per R partition (S_p is probed once per chunk) still beat the L2 table:
   // 2^12 partitions at C3 (2 chunks) 17.6 ms through L2; HJ_L2_MIN_NEED overrides the switch point
   static const u64 l2_min_need = getenv("HJ_L2_MIN_NEED") ? strtoull(getenv("HJ_L2_MIN_NEED"), nullptr, 10) : 63000;
-  const bool use_l2 = dS && (getenv("HJ_FORCE_L2JOIN") || need > l2_min_need) && !getenv("HJ_NO_L2JOIN");
+  const bool use_l2 = !sortmerge && dS && (getenv("HJ_FORCE_L2JOIN") || need > l2_min_need) && !getenv("HJ_NO_L2JOIN");
+  if (sortmerge) {
+    if (!dS || mat || pre1) return HJ_EINVAL;
+    force_exact = true;  // contiguous partitions [off[p], off[p+1])
+  }
   // Histogram-free partitioning (ScOpt, rx_kernels.cuh) for the 2-pass shared-memory join; the
   // exact, histogram-based layout everywhere else and after an overflow on this handle.
   const bool opt = dS && (!pre1 || (offR1 && offS1) || (regR && regS)) && !use_l2 && pl.passes == 2 && !h->no_optimistic && !force_exact &&
@@ -812,6 +818,33 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
     if (mat->out && !mat->written) {
       snprintf(h->err, sizeof(h->err), "materialise: %llu pairs do not fit the buffer of %llu", mat->needed, mat->capacity);
       return HJ_EOVERFLOW;
+    }
+    return HJ_OK;
+  }
+  if (sortmerge) {
+    // per-partition sort + merge (rx_sortmerge.cuh) on the exact layout
+    const u32 tileB = 4096;
+    u32 capA = 1024;
+    while (capA < 8192 && capA < need) capA <<= 1;  // larger R partitions are merged chunk by chunk
+    const size_t smem = (size_t)(capA + tileB) * 8;
+    const void* k = (const void*)rx_sortmerge_kernel;
+    CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int grid = grid_for(h, k, kSmThreads, smem);
+    if ((u32)grid > nparts) grid = (int)nparts;
+    rx_sortmerge_kernel<<<grid, kSmThreads, smem, h->stream>>>(h->rb[0].out.p, h->rb[0].offsets.p, h->rb[1].out.p,
+                                                               h->rb[1].offsets.p, nparts, capA, tileB,
+                                                               h->cfg.key_mask, h->ctr);
+    h->launches++;
+    CK(cudaGetLastError());
+    mark(h, E_JOIN);
+    mark(h, E_END);
+    if ((rc = fetch_counters(h))) return rc;
+    if (res) {
+      fill_common(h, res);
+      res->path_taken = HJ_PATH_SORTMERGE;
+      res->radix_bits = pl.bits;
+      res->passes = pl.passes;
+      res->hbm_bytes = 8ull * (2 * pl.passes + 1) * (n + m);  // as the radix join: the sort is on chip
     }
     return HJ_OK;
   }
@@ -1012,7 +1045,7 @@ void hj_config_default(hj_config* cfg) {
 
 int hj_create(const hj_config* cfg, hj_handle** out) {
   if (!cfg || !out || cfg->struct_size != sizeof(hj_config)) return HJ_EINVAL;
-  if (cfg->algo < HJ_ALGO_ATOMIC || cfg->algo > HJ_ALGO_ADAPTIVE) return HJ_EINVAL;
+  if (cfg->algo < HJ_ALGO_ATOMIC || cfg->algo > HJ_ALGO_SORTMERGE) return HJ_EINVAL;
   if (cfg->probe_length == 0 || cfg->probe_length > 1024) return HJ_EINVAL;
   int ndev = hj_device_count();
   if (ndev <= 0 || cfg->device < 0 || cfg->device >= ndev) return HJ_ECUDA;
@@ -1067,12 +1100,13 @@ int hj_reserve(hj_handle* h, uint64_t max_r, uint64_t max_s) {
   if (!h) return HJ_EINVAL;
   CK(cudaSetDevice(h->device));
   int rc;
-  if (h->cfg.algo != HJ_ALGO_RADIX) {
+  const bool sortmerge = h->cfg.algo == HJ_ALGO_SORTMERGE;
+  if (h->cfg.algo != HJ_ALGO_RADIX && !sortmerge) {
     if ((rc = prepare_table(h, max_r))) return rc;
   }
-  if (h->cfg.algo == HJ_ALGO_RADIX || h->cfg.algo == HJ_ALGO_ADAPTIVE) {
+  if (h->cfg.algo == HJ_ALGO_RADIX || h->cfg.algo == HJ_ALGO_ADAPTIVE || sortmerge) {
     RadixPlan pl;
-    if ((rc = plan_radix(h, max_r, &pl))) return rc;
+    if ((rc = plan_radix(h, max_r, &pl, sortmerge ? 4096 : 16384))) return rc;
     if ((rc = ensure_rel(h, h->rb[0], max_r, pl))) return rc;
     if (max_s && (rc = ensure_rel(h, h->rb[1], max_s, pl))) return rc;
   }
@@ -1081,7 +1115,7 @@ int hj_reserve(hj_handle* h, uint64_t max_r, uint64_t max_s) {
 
 int hj_build(hj_handle* h, const uint64_t* R, uint64_t n, hj_result* res) {
   if (!h || !R || !n) return HJ_EINVAL;
-  if (h->cfg.algo == HJ_ALGO_RADIX) return HJ_ESTATE;  // the radix path has no standalone table
+  if (h->cfg.algo == HJ_ALGO_RADIX || h->cfg.algo == HJ_ALGO_SORTMERGE) return HJ_ESTATE;  // no standalone table
   CK(cudaSetDevice(h->device));
   if (res) memset(res, 0, sizeof(*res));
   reset_events(h);
@@ -1128,7 +1162,7 @@ int hj_probe(hj_handle* h, const uint64_t* S, uint64_t m, hj_result* res) {
 
 int hj_sample(hj_handle* h, const uint64_t* R, uint64_t n, hj_result* res) {
   if (!h || !R || !n) return HJ_EINVAL;
-  if (h->cfg.algo == HJ_ALGO_RADIX) return HJ_ESTATE;
+  if (h->cfg.algo == HJ_ALGO_RADIX || h->cfg.algo == HJ_ALGO_SORTMERGE) return HJ_ESTATE;
   CK(cudaSetDevice(h->device));
   if (res) memset(res, 0, sizeof(*res));
   reset_events(h);
@@ -1169,12 +1203,14 @@ int hj_join(hj_handle* h, const uint64_t* R, uint64_t n, const uint64_t* S, uint
   const int algo = h->cfg.algo;
   const u64 *dR = nullptr, *dS = nullptr;
   bool pendR = false, pendS = false;
-  if (algo == HJ_ALGO_RADIX) {
+  if (algo == HJ_ALGO_RADIX || algo == HJ_ALGO_SORTMERGE) {
+    if (algo == HJ_ALGO_SORTMERGE && !S) return HJ_EINVAL;  // a merge needs both sides
     mark(h, E_T0);
     mark(h, E_CP0, h->copy_stream);
     if ((rc = stage(h, (const u64*)R, n, h->stageR, &dR, E_CPR, &pendR))) return rc;
     if ((rc = stage(h, (const u64*)S, m, h->stageS, &dS, E_CPS, &pendS))) return rc;
-    return run_radix_join(h, dR, n, pendR, dS, m, pendS, res);
+    return run_radix_join(h, dR, n, pendR, dS, m, pendS, res, false, algo == HJ_ALGO_SORTMERGE, nullptr, nullptr,
+                          nullptr, nullptr, nullptr, algo == HJ_ALGO_SORTMERGE);
   }
   // the table clear needs no input: enqueue it first so it runs under the R copy
   if ((rc = prepare_table(h, n))) return rc;

@@ -8,7 +8,7 @@
 // suffixes ("--rSize 16M" is atoi()==16 and a SIGFPE in the reference);
 // --probeLength is actually stored (:53-54 stores it in dataDistr); the probe is
 // a runtime flag --probe 0|1 (default 1) instead of the ENABLE_PROBE macro;
-// --algo radix|adaptive, --sSize, --passes, --device, --sDistr fk.
+// --algo radix|adaptive|sortmerge, --sSize, --passes, --device, --sDistr fk.
 #include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -90,7 +90,8 @@ int main(int argc, char* argv[]) {
   p.device = 0;
   parse_args(argc, argv, &p);
 
-  if (p.algo != "atomic" && p.algo != "nocc" && p.algo != "htm" && p.algo != "adaptive" && p.algo != "radix") {
+  if (p.algo != "atomic" && p.algo != "nocc" && p.algo != "htm" && p.algo != "adaptive" && p.algo != "radix" &&
+      p.algo != "sortmerge") {
     printf("Unknown Algo: %s\n", p.algo.c_str());  // main.cpp:107-108 (exit code 0)
     return 0;
   }
@@ -128,6 +129,13 @@ int main(int argc, char* argv[]) {
   } else if (p.algo == "htm" || p.algo == "adaptive") {
     if (relS) HTMHashBuild(relR, n, relS, m, p.transactionSize, p.scaleOutput, p.numPartitions, p.probeLength);
     else HTMHashBuild(relR, n, p.transactionSize, p.scaleOutput, p.numPartitions, p.probeLength);
+  } else if (p.algo == "sortmerge") {  // the reference builds this comparator as its own binary (SortMerge.cpp)
+    if (!relS) {
+      printf("sortmerge needs a probe side (--probe 1)\n");
+      delete[] relR;
+      return 1;
+    }
+    SortMerge(relR, n, relS, m, p.numPartitions);
   } else {  // radix
     char buf[4096];
     int rc = hj_ref_run("radix", relR, p.rSize, relS, sSize, p.transactionSize, p.scaleOutput, p.numPartitions,

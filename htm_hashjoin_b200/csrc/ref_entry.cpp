@@ -29,6 +29,7 @@ int algo_code(const char* a) {
   if (!strcmp(a, "nocc")) return HJ_ALGO_NOCC;
   if (!strcmp(a, "radix") || !strcmp(a, "PRO") || !strcmp(a, "prj")) return HJ_ALGO_RADIX;
   if (!strcmp(a, "htm") || !strcmp(a, "adaptive")) return HJ_ALGO_ADAPTIVE;
+  if (!strcmp(a, "sortmerge")) return HJ_ALGO_SORTMERGE;
   return -100;
 }
 
@@ -73,7 +74,7 @@ extern "C" int hj_ref_run(const char* algo, const uint64_t* relR, uint64_t rSize
   // radix fan-out: explicit numPartitions (power of two) for radix/adaptive; 64 (the CPU
   // default work split, main.cpp:85) and non-powers are treated as "automatic"
   cfg.num_partitions = 0;
-  if (code == HJ_ALGO_RADIX || code == HJ_ALGO_ADAPTIVE) {
+  if (code == HJ_ALGO_RADIX || code == HJ_ALGO_ADAPTIVE || code == HJ_ALGO_SORTMERGE) {
     if (g_radix_bits) cfg.num_partitions = 1u << g_radix_bits;
     else if (numPartitions && numPartitions != 64 && !(numPartitions & (numPartitions - 1)))
       cfg.num_partitions = numPartitions;
@@ -107,6 +108,24 @@ extern "C" int hj_ref_run(const char* algo, const uint64_t* relR, uint64_t rSize
   }
   hj_destroy(h);
 
+  if (code == HJ_ALGO_SORTMERGE) {
+    // SortMerge.cpp:49-68 keys in the reference's order (its "algo" value is a copy-pasted "nocc").  The sort is
+    // split: sortTime = the radix distribution passes, mergeTime = the kernel that sorts each partition pair in
+    // shared memory and merges it.
+    const double tuples = (double)rSize + (double)sSize, dev_us = res.us_total > 0 ? res.us_total : 1.0;
+    snprintf(json_out, cap,
+             "{\"algo\": \"sortmerge\",\"rSize\": %llu, \"hashBuildTimeInMicroseconds\": %lld, "
+             "\"sortTimeInMicroseconds\": %lld, \"mergeTimeInMicroseconds\": %lld, \"totalMatches\": %llu, "
+             "\"inputSum\": %llu, \"sSize\": %llu, \"matches\": %llu, \"checksum\": %llu, \"path\": \"sortmerge\", "
+             "\"radixBits\": %u, \"passes\": %u, \"deviceTimeInMicroseconds\": %.1f, \"tuplesPerSec\": %.6g, "
+             "\"hbmBytes\": %llu, \"kernelLaunches\": %u, \"maxPartition\": %llu}",
+             (unsigned long long)rSize, t1 - t0, (long long)(res.us_total - res.us_join),
+             (long long)res.us_join, (unsigned long long)res.matches, (unsigned long long)sums.input_sum,
+             (unsigned long long)sSize, (unsigned long long)res.matches, (unsigned long long)res.checksum,
+             res.radix_bits, res.passes, res.us_total, tuples / (dev_us * 1e-6), (unsigned long long)res.hbm_bytes,
+             res.kernel_launches, (unsigned long long)res.max_partition);
+    return HJ_OK;
+  }
   const bool global_path = res.path_taken == HJ_PATH_GLOBAL;
   const unsigned long long out_sum =
       global_path ? (unsigned long long)(sums.table_sum + sums.overflow_sum) : (unsigned long long)sums.input_sum;
@@ -165,6 +184,10 @@ void HTMHashBuild(uint64_t* relR, uint32_t rSize, uint32_t transactionSize, uint
 void HTMHashBuild(uint64_t* relR, uint32_t rSize, uint64_t* relS, uint32_t sSize, uint32_t transactionSize,
                   uint32_t scaleOutput, uint32_t numPartitions, uint32_t probeLength) {
   print_line("htm", relR, rSize, relS, sSize, transactionSize, scaleOutput, numPartitions, probeLength);
+}
+
+void SortMerge(uint64_t* build, uint32_t buildSize, uint64_t* probe, uint32_t probeSize, uint32_t numPartitions) {
+  print_line("sortmerge", build, buildSize, probe, probeSize, 0, 2, numPartitions, 4);
 }
 
 int64_t PRO(relation_t* relR, relation_t* relS, int nthreads) {

@@ -26,6 +26,10 @@ void HTMHashBuild(uint64_t* relR, uint32_t rSize, uint32_t transactionSize, uint
                   uint32_t numPartitions, uint32_t probeLength);
 void HTMHashBuild(uint64_t* relR, uint32_t rSize, uint64_t* relS, uint32_t sSize, uint32_t transactionSize,
                   uint32_t scaleOutput, uint32_t numPartitions, uint32_t probeLength);
+// SortMerge.hpp:5-6, the sort-merge comparator: both sides are radix-partitioned, each partition pair is sorted
+// in shared memory and merged (rx_sortmerge.cuh).  Unlike SortMerge.cpp:23-33 the probe side need not arrive
+// sorted.  numPartitions as for radix (64 = automatic).
+void SortMerge(uint64_t* build, uint32_t buildSize, uint64_t* probe, uint32_t probeSize, uint32_t numPartitions);
 
 // mc/src/types.h:31-46
 struct tuple_t { int32_t key; int32_t payload; };
@@ -43,7 +47,7 @@ void hj_ref_set_radix(uint32_t radix_bits, uint32_t passes);
 void hj_ref_set_device(int device);
 int hj_ref_last_status(void);
 // The generic form behind all of the above: 64-bit sizes, any algo
-// ("atomic","nocc","htm"/"adaptive","radix"), JSON line into json_out.
+// ("atomic","nocc","htm"/"adaptive","radix","sortmerge"), JSON line into json_out.
 // Returns the hj_* status.
 int hj_ref_run(const char* algo, const uint64_t* relR, uint64_t rSize, const uint64_t* relS, uint64_t sSize,
                uint32_t transactionSize, uint32_t scaleOutput, uint32_t numPartitions, uint32_t probeLength,

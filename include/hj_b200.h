@@ -43,11 +43,14 @@ enum {
   HJ_ALGO_ATOMIC = 0,  /* global table, CAS inserts   (AtomicHashBuild.hpp:37-67)   */
   HJ_ALGO_NOCC = 1,    /* global table, plain stores  (NoCCHashBuild.hpp:37-62)     */
   HJ_ALGO_RADIX = 2,   /* radix join                  (mc/src/parallel_radix_join.c)*/
-  HJ_ALGO_ADAPTIVE = 3 /* sample, then global or radix (HTMHashBuild.hpp:100-156)   */
+  HJ_ALGO_ADAPTIVE = 3,/* sample, then global or radix (HTMHashBuild.hpp:100-156)   */
+  HJ_ALGO_SORTMERGE = 4/* partitioned sort-merge join, the comparator of SortMerge.cpp:8-39:
+                          radix-partition both sides, sort each partition pair on chip,
+                          two-pointer merge; hj_join only, needs S           */
 };
 
 /* path_taken values in hj_result */
-enum { HJ_PATH_NONE = 0, HJ_PATH_GLOBAL = 1, HJ_PATH_RADIX = 2 };
+enum { HJ_PATH_NONE = 0, HJ_PATH_GLOBAL = 1, HJ_PATH_RADIX = 2, HJ_PATH_SORTMERGE = 3 };
 
 /* Everything that is a command-line flag (main.cpp:47-62) or a compile-time
  * macro (config.h:4-16, mc/src/prj_params.h:15-22) in the reference. */
