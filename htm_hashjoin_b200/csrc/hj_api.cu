@@ -823,17 +823,32 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
   }
   if (sortmerge) {
     // per-partition sort + merge (rx_sortmerge.cuh) on the exact layout
+    // register sort (default) or the shared-memory-only network (HJ_SM_VARIANT=0, the A/B record)
+    static const int variant = getenv("HJ_SM_VARIANT") ? atoi(getenv("HJ_SM_VARIANT")) : 1;
     const u32 tileB = 4096;
-    u32 capA = 1024;
+    u32 capA = variant ? 4096 : 1024;
     while (capA < 8192 && capA < need) capA <<= 1;  // larger R partitions are merged chunk by chunk
     const size_t smem = (size_t)(capA + tileB) * 8;
-    const void* k = (const void*)rx_sortmerge_kernel;
+    // encoding of the register sort by key mask (rx_sortmerge.cuh); HJ_SM_MODE=0 forces the generic order
+    int mode = h->cfg.key_mask == 0xffffffffull ? 1 : h->cfg.key_mask == ~0ull ? 2 : 0;
+    if (getenv("HJ_SM_MODE")) mode = atoi(getenv("HJ_SM_MODE")) ? mode : 0;
+    const void* k = !variant ? (const void*)rx_sortmerge_kernel
+                    : mode == 1 ? (const void*)rx_sortmerge_regs_kernel<1>
+                    : mode == 2 ? (const void*)rx_sortmerge_regs_kernel<2> : (const void*)rx_sortmerge_regs_kernel<0>;
     CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int grid = grid_for(h, k, kSmThreads, smem);
     if ((u32)grid > nparts) grid = (int)nparts;
-    rx_sortmerge_kernel<<<grid, kSmThreads, smem, h->stream>>>(h->rb[0].out.p, h->rb[0].offsets.p, h->rb[1].out.p,
-                                                               h->rb[1].offsets.p, nparts, capA, tileB,
-                                                               h->cfg.key_mask, h->ctr);
+    if (variant) {
+      const u64 *aR = h->rb[0].out.p, *aoR = h->rb[0].offsets.p, *aS = h->rb[1].out.p, *aoS = h->rb[1].offsets.p;
+      u32 a_np = nparts;
+      u64 a_km = h->cfg.key_mask;
+      u64* a_ctr = h->ctr;
+      void* args[] = {&aR, &aoR, &aS, &aoS, &a_np, &capA, &a_km, &a_ctr};
+      CK(cudaLaunchKernel(k, dim3(grid), dim3(kSmThreads), args, smem, h->stream));
+    } else
+      rx_sortmerge_kernel<<<grid, kSmThreads, smem, h->stream>>>(h->rb[0].out.p, h->rb[0].offsets.p, h->rb[1].out.p,
+                                                                 h->rb[1].offsets.p, nparts, capA, tileB,
+                                                                 h->cfg.key_mask, h->ctr);
     h->launches++;
     CK(cudaGetLastError());
     mark(h, E_JOIN);

@@ -12,6 +12,12 @@
 //       merge: thread t owns V consecutive elements of B, finds its start in A with ONE binary
 //       search (the merge-path split) and then walks A and its B elements with two pointers;
 //       equal runs in A are rescanned for equal keys in B (mark / restore of a merge join).
+// Tiles of up to 4096 tuples are sorted in REGISTERS (sm_sort_regs): 512 threads x 8 elements, element
+// i = tid * 8 + e.  Of the 78 compare-exchange steps of a 4096-element bitonic network, those with partner
+// distance j < 8 stay inside a thread, 8 <= j < 256 are warp shuffles, and only the 10 steps with j >= 256 cross
+// warps through a 32 KB shared-memory exchange buffer (conflict-free e * 512 + tid layout).  The merge then
+// runs straight from the registers: a thread's 8 elements ARE its 8 consecutive elements of B.  R chunks of more
+// than 4096 tuples use the shared-memory network (sm_bitonic).
 // Integer only; results are order-independent sums, so they are bit-exact against the oracle.
 #pragma once
 #include "hj_common.cuh"
@@ -51,7 +57,85 @@ __device__ __forceinline__ u32 sm_pow2(u32 v) {
   return p;
 }
 
-// capA / tileB: powers of two, shared memory = (capA + tileB) * 8 bytes
+
+constexpr int kSmIPT = 8;                          // elements per thread of the register sort
+constexpr u32 kSmTile = kSmThreads * kSmIPT;       // 4096
+
+// The register sort works on ENCODED tuples so that, for the two usual key masks, the order (key, tuple) is the
+// plain order of 64-bit words and a compare-exchange costs a 64-bit compare and two selects instead of the ~20
+// instructions of sm_less (ncu of the first version: 1750 thread instructions per tuple, math-pipe bound):
+//   MODE 1  key_mask = 0xffffffff (mc tuples: key low, payload high): halves swapped -- a register rename
+//   MODE 2  key_mask = all 64 bits: the word itself
+//   MODE 0  any other mask: the word itself, ordered with sm_less
+// The padding value ~0 encodes to itself and stays the maximum.
+template <int MODE>
+__device__ __forceinline__ u64 sm_enc(u64 x) { return MODE == 1 ? (x << 32) | (x >> 32) : x; }
+template <int MODE>
+__device__ __forceinline__ u64 sm_dec(u64 w) { return MODE == 1 ? (w << 32) | (w >> 32) : w; }
+template <int MODE>
+__device__ __forceinline__ u64 sm_key(u64 w, u64 kmask) { return MODE == 1 ? w >> 32 : MODE == 2 ? w : w & kmask; }
+template <int MODE>
+__device__ __forceinline__ bool sm_lt(u64 a, u64 b, u64 kmask) { return MODE == 0 ? sm_less(a, b, kmask) : a < b; }
+
+// compare-exchange of a (lower index) and b; up: ascending
+template <int MODE>
+__device__ __forceinline__ void sm_cmpx(u64& a, u64& b, bool up, u64 kmask) {
+  const bool sw = up ? sm_lt<MODE>(b, a, kmask) : sm_lt<MODE>(a, b, kmask);
+  const u64 t = a;
+  a = sw ? b : a;
+  b = sw ? t : b;
+}
+// this thread keeps the smaller (keep_min) or larger of its v and the partner's o
+template <int MODE>
+__device__ __forceinline__ u64 sm_keep(u64 v, u64 o, bool keep_min, u64 kmask) {
+  const bool lt = sm_lt<MODE>(o, v, kmask);
+  return keep_min ? (lt ? o : v) : (lt ? v : o);
+}
+
+// Bitonic sort of the 4096-slot sequence whose element tid * 8 + e sits in v[e] of thread tid, ascending, in
+// blocks of L (a power of two <= 4096: only stages k <= L run; slots >= L must hold the padding value).
+// X: kSmTile u64 of shared memory for the cross-warp steps.  All threads of the CTA call it.
+template <int MODE>
+__device__ __forceinline__ void sm_sort_regs(u64 (&v)[kSmIPT], u64* X, u32 L, u64 kmask) {
+  const u32 tid = threadIdx.x, base = tid * kSmIPT;
+  for (u32 k = 2; k <= L; k <<= 1) {
+    const bool up = (base & k) == 0;  // k >= 8: the same for the thread's 8 elements
+    for (u32 j = k >> 1; j > 0; j >>= 1) {
+      if (j >= 8 * 32) {
+        const u32 tm = j >> 3, pt = tid ^ tm;
+        const bool keep_min = ((tid & tm) == 0) == up;
+        __syncthreads();  // earlier readers of X are done
+#pragma unroll
+        for (int e = 0; e < kSmIPT; e++) X[e * kSmThreads + tid] = v[e];
+        __syncthreads();
+#pragma unroll
+        for (int e = 0; e < kSmIPT; e++) v[e] = sm_keep<MODE>(v[e], X[e * kSmThreads + pt], keep_min, kmask);
+      } else if (j >= 8) {
+        const u32 lm = j >> 3;
+        const bool keep_min = ((tid & lm) == 0) == up;
+#pragma unroll
+        for (int e = 0; e < kSmIPT; e++) v[e] = sm_keep<MODE>(v[e], __shfl_xor_sync(0xffffffffu, v[e], lm), keep_min, kmask);
+      } else if (j == 4) {
+#pragma unroll
+        for (int e = 0; e < 4; e++) sm_cmpx<MODE>(v[e], v[e + 4], up, kmask);  // k >= 8 here
+      } else if (j == 2) {
+        sm_cmpx<MODE>(v[0], v[2], up, kmask);  // k == 4: elements 0..3 ascend, 4..7 descend unless k >= 8
+        sm_cmpx<MODE>(v[1], v[3], up, kmask);
+        const bool up_hi = k >= 8 ? up : false;
+        sm_cmpx<MODE>(v[4], v[6], up_hi, kmask);
+        sm_cmpx<MODE>(v[5], v[7], up_hi, kmask);
+      } else {  // j == 1: direction of element e is (e & k) == 0 for k < 8
+        const bool u0 = k >= 8 ? up : true, u2 = k >= 8 ? up : k == 4, u4 = k >= 8 ? up : k == 2, u6 = k >= 8 ? up : false;
+        sm_cmpx<MODE>(v[0], v[1], u0, kmask);
+        sm_cmpx<MODE>(v[2], v[3], u2, kmask);
+        sm_cmpx<MODE>(v[4], v[5], u4, kmask);
+        sm_cmpx<MODE>(v[6], v[7], u6, kmask);
+      }
+    }
+  }
+}
+
+// The shared-memory-only version (HJ_SM_VARIANT=0; kept for the A/B record).  capA / tileB: powers of two, shared memory = (capA + tileB) * 8 bytes
 __global__ void __launch_bounds__(kSmThreads)
 rx_sortmerge_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const u64* __restrict__ Sp,
                     const u64* __restrict__ offS, u32 nparts, u32 capA, u32 tileB, u64 key_mask,
@@ -112,6 +196,105 @@ rx_sortmerge_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, co
   u64 v[2] = {matches, checksum};
   u64* const d[2] = {ctr + C_MATCHES, ctr + C_CHECKSUM};
   block_sum_atomic<2, kSmThreads>(v, d);
+  maxpart = max(maxpart, __shfl_xor_sync(0xffffffffu, maxpart, 16));
+  maxpart = max(maxpart, __shfl_xor_sync(0xffffffffu, maxpart, 8));
+  maxpart = max(maxpart, __shfl_xor_sync(0xffffffffu, maxpart, 4));
+  maxpart = max(maxpart, __shfl_xor_sync(0xffffffffu, maxpart, 2));
+  maxpart = max(maxpart, __shfl_xor_sync(0xffffffffu, maxpart, 1));
+  if (tid == 0) {
+    atomicMax(ctr + C_MAX_PART, maxpart);
+    if (chunked) atomicAdd(ctr + C_TOO_BIG, chunked);
+  }
+}
+
+// merge of this thread's 8 sorted elements (slots tid * 8 + e < nb of the tile) with A[0, na)
+template <int MODE>
+__device__ __forceinline__ void sm_merge_regs(const u64 (&v)[kSmIPT], u32 nb, const u64* A, u32 na, u64 kmask,
+                                              u64& matches, u64& checksum) {
+  const u32 b0 = threadIdx.x * kSmIPT;
+  if (b0 >= nb) return;
+  const u64 kfirst = sm_key<MODE>(v[0], kmask);
+  u32 lo = 0, hi = na;
+  while (lo < hi) {
+    const u32 mid = (lo + hi) >> 1;
+    if (sm_key<MODE>(A[mid], kmask) < kfirst) lo = mid + 1; else hi = mid;
+  }
+  u32 ai = lo;
+#pragma unroll
+  for (int e = 0; e < kSmIPT; e++) {
+    if (b0 + e < nb) {
+      const u64 ks = sm_key<MODE>(v[e], kmask);
+      while (ai < na && sm_key<MODE>(A[ai], kmask) < ks) ai++;
+      for (u32 j = ai; j < na; j++) {
+        const u64 r = A[j];
+        if (sm_key<MODE>(r, kmask) != ks) break;
+        matches++;
+        checksum += sm_dec<MODE>(r) + sm_dec<MODE>(v[e]);
+      }
+    }
+  }
+}
+
+// The register-sort version (default).  capA: 4096 or 8192; shared memory = (capA + 4096) * 8 bytes.  A holds
+// encoded tuples.
+template <int MODE>
+__global__ void __launch_bounds__(kSmThreads)
+rx_sortmerge_regs_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const u64* __restrict__ Sp,
+                         const u64* __restrict__ offS, u32 nparts, u32 capA, u64 key_mask, u64* __restrict__ ctr) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  u64* A = reinterpret_cast<u64*>(smem_raw);
+  u64* X = A + capA;  // exchange buffer of the register sort
+  const u32 tid = threadIdx.x;
+  const u64 kmask = key_mask ? key_mask : ~0ull;
+  u64 matches = 0, checksum = 0, maxpart = 0, chunked = 0;
+  u64 v[kSmIPT];
+
+  for (u32 p = blockIdx.x; p < nparts; p += gridDim.x) {
+    const u64 r0 = offR[p], r1 = offR[p + 1], s0 = offS[p], s1 = offS[p + 1];
+    const u64 nr = r1 - r0;
+    maxpart = nr > maxpart ? nr : maxpart;
+    if (nr == 0 || s1 == s0) continue;
+    if (nr > capA) chunked++;
+    for (u64 c0 = r0; c0 < r1; c0 += capA) {
+      const u32 na = (u32)(c0 + capA < r1 ? capA : r1 - c0);
+      const u32 LA = sm_pow2(na);
+      __syncthreads();  // the previous merge is done with A
+      if (LA <= kSmTile) {
+        // the input order is irrelevant to a sort: coalesced loads (slot tid * 8 + e <- tuple e * 512 + tid)
+        // when the chunk fills all slots, else slot i <- tuple i so that the padding sits behind slot na
+#pragma unroll
+        for (int e = 0; e < kSmIPT; e++) {
+          const u32 i = na == kSmTile ? e * kSmThreads + tid : tid * kSmIPT + e;
+          v[e] = i < na ? sm_enc<MODE>(ld_stream(Rp + c0 + i)) : ~0ull;
+        }
+        sm_sort_regs<MODE>(v, X, LA, kmask);
+#pragma unroll
+        for (int e = 0; e < kSmIPT; e++)
+          if (tid * kSmIPT + e < LA) A[tid * kSmIPT + e] = v[e];
+        __syncthreads();
+      } else {
+        // more than 4096 tuples: the shared-memory network on plain tuples, encoded afterwards (order kept)
+        for (u32 i = tid; i < LA; i += kSmThreads) A[i] = i < na ? ld_stream(Rp + c0 + i) : ~0ull;
+        __syncthreads();
+        sm_bitonic(A, LA, kmask);
+        for (u32 i = tid; i < LA; i += kSmThreads) A[i] = sm_enc<MODE>(A[i]);
+        __syncthreads();
+      }
+      for (u64 t0 = s0; t0 < s1; t0 += kSmTile) {
+        const u32 nb = (u32)(t0 + kSmTile < s1 ? kSmTile : s1 - t0);
+#pragma unroll
+        for (int e = 0; e < kSmIPT; e++) {
+          const u32 i = nb == kSmTile ? e * kSmThreads + tid : tid * kSmIPT + e;
+          v[e] = i < nb ? sm_enc<MODE>(ld_stream(Sp + t0 + i)) : ~0ull;
+        }
+        sm_sort_regs<MODE>(v, X, sm_pow2(nb), kmask);
+        sm_merge_regs<MODE>(v, nb, A, na, kmask, matches, checksum);
+      }
+    }
+  }
+  u64 vs[2] = {matches, checksum};
+  u64* const d[2] = {ctr + C_MATCHES, ctr + C_CHECKSUM};
+  block_sum_atomic<2, kSmThreads>(vs, d);
   maxpart = max(maxpart, __shfl_xor_sync(0xffffffffu, maxpart, 16));
   maxpart = max(maxpart, __shfl_xor_sync(0xffffffffu, maxpart, 8));
   maxpart = max(maxpart, __shfl_xor_sync(0xffffffffu, maxpart, 4));

@@ -109,6 +109,22 @@ def test_sortmerge_equals_radix_join_at_size(hj):
     assert res.checksum == ref.checksum
 
 
+@pytest.mark.parametrize("key_mask", [0, 0xFFFFFFFF])
+def test_sortmerge_generic_order_equals_encoded(hj, oracle, monkeypatch, key_mask):
+    """The register sort orders encoded words for the two usual key masks; HJ_SM_MODE=0 forces the generic
+    (key, tuple) comparison that any other mask takes.  Same result either way."""
+    rng = np.random.default_rng(21)
+    n, m = 70001, 300017
+    R = rng.integers(1, 50000, n, dtype=np.uint64) | (np.arange(n, dtype=np.uint64) << np.uint64(32))
+    S = rng.integers(1, 50000, m, dtype=np.uint64) | (np.arange(m, dtype=np.uint64) << np.uint64(32))
+    want = oracle.true_join(R, S, key_mask) if key_mask else oracle.true_join(R, S)
+    for mode in ("1", "0"):
+        monkeypatch.setenv("HJ_SM_MODE", mode)
+        with hj.HashJoin("sortmerge", key_mask=key_mask) as h:
+            res = h.join(R, S)
+            assert (res.matches, res.checksum) == want, mode
+
+
 def test_sortmerge_needs_a_probe_side(hj):
     R = hj.generate_data("sorted", 1 << 12)
     with hj.HashJoin("sortmerge") as h:
