@@ -77,62 +77,84 @@ __device__ __forceinline__ u64 sm_key(u64 w, u64 kmask) { return MODE == 1 ? w >
 template <int MODE>
 __device__ __forceinline__ bool sm_lt(u64 a, u64 b, u64 kmask) { return MODE == 0 ? sm_less(a, b, kmask) : a < b; }
 
-// compare-exchange of a (lower index) and b; up: ascending
+// compare-exchange of a (lower index) and b; up: ascending.  (b < a) == up also swaps equal words when
+// descending, which changes nothing.
 template <int MODE>
 __device__ __forceinline__ void sm_cmpx(u64& a, u64& b, bool up, u64 kmask) {
-  const bool sw = up ? sm_lt<MODE>(b, a, kmask) : sm_lt<MODE>(a, b, kmask);
+  const bool sw = sm_lt<MODE>(b, a, kmask) == up;
   const u64 t = a;
   a = sw ? b : a;
   b = sw ? t : b;
 }
-// this thread keeps the smaller (keep_min) or larger of its v and the partner's o
+// this thread keeps the smaller (keep_min) or larger of its v and the partner's o: one compare, one select
 template <int MODE>
 __device__ __forceinline__ u64 sm_keep(u64 v, u64 o, bool keep_min, u64 kmask) {
-  const bool lt = sm_lt<MODE>(o, v, kmask);
-  return keep_min ? (lt ? o : v) : (lt ? v : o);
+  return (sm_lt<MODE>(o, v, kmask) == keep_min) ? o : v;
 }
 
-// Bitonic sort of the 4096-slot sequence whose element tid * 8 + e sits in v[e] of thread tid, ascending, in
-// blocks of L (a power of two <= 4096: only stages k <= L run; slots >= L must hold the padding value).
-// X: kSmTile u64 of shared memory for the cross-warp steps.  All threads of the CTA call it.
-template <int MODE>
-__device__ __forceinline__ void sm_sort_regs(u64 (&v)[kSmIPT], u64* X, u32 L, u64 kmask) {
-  const u32 tid = threadIdx.x, base = tid * kSmIPT;
-  for (u32 k = 2; k <= L; k <<= 1) {
-    const bool up = (base & k) == 0;  // k >= 8: the same for the thread's 8 elements
-    for (u32 j = k >> 1; j > 0; j >>= 1) {
-      if (j >= 8 * 32) {
-        const u32 tm = j >> 3, pt = tid ^ tm;
-        const bool keep_min = ((tid & tm) == 0) == up;
-        __syncthreads();  // earlier readers of X are done
+// Stage k = 2^LK of the bitonic network over the 4096-slot sequence whose element tid * 8 + e sits in v[e] of
+// thread tid.  Fully unrolled: every partner distance j is a compile-time constant, so each step is straight-line
+// code on fixed registers (the first version looped over k and j at run time: 24 % of its instructions were
+// register moves).  j < 8: inside the thread; 8 <= j < 256: warp shuffle; j >= 256: through X.
+template <int MODE, int LK>
+__device__ __forceinline__ void sm_stage(u64 (&v)[kSmIPT], u64* X, u64 kmask) {
+  constexpr u32 k = 1u << LK;
+  const u32 tid = threadIdx.x;
+  const bool up = ((tid * kSmIPT) & k) == 0;  // k >= 8: the same for the thread's 8 elements
 #pragma unroll
-        for (int e = 0; e < kSmIPT; e++) X[e * kSmThreads + tid] = v[e];
-        __syncthreads();
+  for (int lj = LK - 1; lj >= 0; lj--) {
+    const u32 j = 1u << lj;
+    if (j >= 8 * 32) {
+      const u32 tm = j >> 3, pt = tid ^ tm;
+      const bool keep_min = ((tid & tm) == 0) == up;
+      __syncthreads();  // earlier readers of X are done
 #pragma unroll
-        for (int e = 0; e < kSmIPT; e++) v[e] = sm_keep<MODE>(v[e], X[e * kSmThreads + pt], keep_min, kmask);
-      } else if (j >= 8) {
-        const u32 lm = j >> 3;
-        const bool keep_min = ((tid & lm) == 0) == up;
+      for (int e = 0; e < kSmIPT; e++) X[e * kSmThreads + tid] = v[e];
+      __syncthreads();
 #pragma unroll
-        for (int e = 0; e < kSmIPT; e++) v[e] = sm_keep<MODE>(v[e], __shfl_xor_sync(0xffffffffu, v[e], lm), keep_min, kmask);
-      } else if (j == 4) {
+      for (int e = 0; e < kSmIPT; e++) v[e] = sm_keep<MODE>(v[e], X[e * kSmThreads + pt], keep_min, kmask);
+    } else if (j >= 8) {
+      const u32 lm = j >> 3;
+      const bool keep_min = ((tid & lm) == 0) == up;
 #pragma unroll
-        for (int e = 0; e < 4; e++) sm_cmpx<MODE>(v[e], v[e + 4], up, kmask);  // k >= 8 here
-      } else if (j == 2) {
-        sm_cmpx<MODE>(v[0], v[2], up, kmask);  // k == 4: elements 0..3 ascend, 4..7 descend unless k >= 8
-        sm_cmpx<MODE>(v[1], v[3], up, kmask);
-        const bool up_hi = k >= 8 ? up : false;
-        sm_cmpx<MODE>(v[4], v[6], up_hi, kmask);
-        sm_cmpx<MODE>(v[5], v[7], up_hi, kmask);
-      } else {  // j == 1: direction of element e is (e & k) == 0 for k < 8
-        const bool u0 = k >= 8 ? up : true, u2 = k >= 8 ? up : k == 4, u4 = k >= 8 ? up : k == 2, u6 = k >= 8 ? up : false;
-        sm_cmpx<MODE>(v[0], v[1], u0, kmask);
-        sm_cmpx<MODE>(v[2], v[3], u2, kmask);
-        sm_cmpx<MODE>(v[4], v[5], u4, kmask);
-        sm_cmpx<MODE>(v[6], v[7], u6, kmask);
-      }
+      for (int e = 0; e < kSmIPT; e++)
+        v[e] = sm_keep<MODE>(v[e], __shfl_xor_sync(0xffffffffu, v[e], lm), keep_min, kmask);
+    } else {
+      // direction of element e: (e & k) == 0 for k < 8
+#pragma unroll
+      for (int e = 0; e < kSmIPT; e++)
+        if ((e & j) == 0) sm_cmpx<MODE>(v[e], v[e | j], k >= 8 ? up : (e & k) == 0, kmask);
     }
   }
+}
+
+// Bitonic sort, ascending, in blocks of L (a power of two <= 4096: only stages k <= L run; slots >= L must hold
+// the padding value).  X: kSmTile u64 of shared memory for the cross-warp steps.  All threads of the CTA call it.
+template <int MODE>
+__device__ __forceinline__ void sm_sort_regs(u64 (&v)[kSmIPT], u64* X, u32 L, u64 kmask) {
+  sm_stage<MODE, 1>(v, X, kmask);
+  if (L < 4) return;
+  sm_stage<MODE, 2>(v, X, kmask);
+  if (L < 8) return;
+  sm_stage<MODE, 3>(v, X, kmask);
+  if (L < 16) return;
+  sm_stage<MODE, 4>(v, X, kmask);
+  if (L < 32) return;
+  sm_stage<MODE, 5>(v, X, kmask);
+  if (L < 64) return;
+  sm_stage<MODE, 6>(v, X, kmask);
+  if (L < 128) return;
+  sm_stage<MODE, 7>(v, X, kmask);
+  if (L < 256) return;
+  sm_stage<MODE, 8>(v, X, kmask);
+  if (L < 512) return;
+  sm_stage<MODE, 9>(v, X, kmask);
+  if (L < 1024) return;
+  sm_stage<MODE, 10>(v, X, kmask);
+  if (L < 2048) return;
+  sm_stage<MODE, 11>(v, X, kmask);
+  if (L < 4096) return;
+  sm_stage<MODE, 12>(v, X, kmask);
 }
 
 // The shared-memory-only version (HJ_SM_VARIANT=0; kept for the A/B record).  capA / tileB: powers of two, shared memory = (capA + tileB) * 8 bytes
