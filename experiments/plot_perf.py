@@ -16,7 +16,7 @@ import os
 HERE = os.path.dirname(os.path.abspath(__file__))
 COLORS = ["#d62728", "#1f77b4", "#2ca02c", "#9467bd", "#8c564b", "#e377c2", "#7f7f7f", "#bcbd22"]
 GPU_NAMES = {"nocc": "NoCC global table (B200)", "atomic": "Atomic global table (B200)",
-             "radix": "Radix join (B200)", "adaptive": "Adaptive (B200)"}
+             "radix": "Radix join (B200)", "adaptive": "Adaptive (B200)", "sortmerge": "Sort-merge (B200)"}
 
 
 def load_gpu(path):

@@ -25,7 +25,7 @@ import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import htm_hashjoin_b200 as hj  # noqa: E402
 
-PATHS = {0: "none", 1: "global", 2: "radix"}
+PATHS = {0: "none", 1: "global", 2: "radix", 3: "sortmerge"}
 
 
 def timed(h, dR, dS, reps, warm=2):

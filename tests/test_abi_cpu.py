@@ -90,3 +90,34 @@ def test_cli_flag_behaviour():
     r = subprocess.run([exe, "--algo", "atomic", "--rSize", "1K", "--dataDistr", "zipf"], capture_output=True,
                        text=True)
     assert r.returncode == 1 and "Unknown distribution" in r.stdout
+
+
+def test_header_enums_match_the_python_binding(hj):
+    """HJ_ALGO_* / HJ_PATH_* / HJ_E* in include/hj_b200.h are what _capi.py binds (incl. the sort-merge comparator)."""
+    hdr = open(os.path.join(ROOT, "include", "hj_b200.h")).read()
+    vals = {k: int(v) for k, v in re.findall(r"\b(HJ_(?:ALGO|PATH|E)[A-Z_]*|HJ_OK)\s*=\s*(-?\d+)", hdr)}
+    assert vals["HJ_ALGO_SORTMERGE"] == 4 and vals["HJ_PATH_SORTMERGE"] == 3
+    for name, v in vals.items():
+        if hasattr(hj._capi, name):
+            assert getattr(hj._capi, name) == v, name
+    assert hj.ALGOS["sortmerge"] == vals["HJ_ALGO_SORTMERGE"]
+    cfg = hj.hj_config()
+    hj.lib.hj_config_default(C.byref(cfg))
+    cfg.algo = vals["HJ_ALGO_SORTMERGE"] + 1  # one past the last algorithm
+    h = C.c_void_p()
+    assert hj.lib.hj_create(C.byref(cfg), C.byref(h)) == hj._capi.HJ_EINVAL
+
+
+def test_cli_sortmerge_is_a_known_algo():
+    """SortMerge.cpp is its own binary in the reference; here it is --algo sortmerge.  It needs a probe side, and
+    without a GPU it reports the error in the JSON line (exit 2) instead of computing on the CPU."""
+    exe = os.path.join(ROOT, "htm_hashjoin_b200", "csrc", "main")
+    if not os.path.exists(exe):
+        pytest.skip("CLI not built")
+    r = subprocess.run([exe, "--algo", "sortmerge", "--rSize", "1K", "--probe", "0"], capture_output=True, text=True)
+    assert r.returncode == 1 and "needs a probe side" in r.stdout
+    r = subprocess.run([exe, "--algo", "sortmerge", "--rSize", "1K"], capture_output=True, text=True)
+    assert "Unknown Algo" not in r.stdout
+    lib = C.CDLL(os.path.join(ROOT, "htm_hashjoin_b200", "csrc", "libhj_b200.so"))
+    if lib.hj_device_count() <= 0:
+        assert r.returncode == 2 and '"error"' in r.stdout and "no CPU fallback" in r.stdout
