@@ -27,6 +27,9 @@
 #include <AtomicHashBuild.hpp>
 #include <NoCCHashBuild.hpp>
 #include <include/DataGen.hpp>
+#ifdef REF_ENABLE_PROBE
+#include <SortMerge.hpp>  // the comparator: SortMerge.cpp itself is compiled beside this file (oracle/Makefile)
+#endif
 
 // AtomicHashBuild.hpp:113 / NoCCHashBuild.hpp:107 read conflicts[] at
 // outputPartitionSize*i (= 2x the index it was written at, :63), i.e. up to
@@ -96,5 +99,16 @@ int ref_hash_build(const char* algo, uint64_t* R, uint32_t n, uint64_t* S, uint3
   else return -1;
   return emit(cap_out.os.str(), json_out, cap);
 }
+
+#ifdef REF_ENABLE_PROBE
+// SortMerge.hpp:5-6.  The reference sorts `build` IN PLACE (SortMerge.cpp:13-18) -- callers pass a copy -- and
+// merges build[range] with probe[range] slice by slice (:21-35).  The JSON line it prints is returned.
+int ref_sort_merge(uint64_t* build, uint32_t n, uint64_t* probe, uint32_t m, uint32_t numPartitions, char* json_out,
+                   uint32_t cap) {
+  CoutCapture cap_out;
+  SortMerge(build, n, probe, m, numPartitions);
+  return emit(cap_out.os.str(), json_out, cap);
+}
+#endif
 
 }  // extern "C"

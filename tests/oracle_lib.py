@@ -144,6 +144,19 @@ class Reference:
         self.lib.ref_hash_build.argtypes = [C.c_char_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_uint32,
                                             C.c_uint32, C.c_uint32, C.c_char_p, C.c_uint32]
 
+    def sort_merge(self, build, probe, num_partitions=64):
+        """The reference's SortMerge (SortMerge.cpp:8-39) on copies of the inputs; None if this build lacks it."""
+        if not hasattr(self.lib, "ref_sort_merge"):
+            return None
+        self.lib.ref_sort_merge.restype = C.c_int
+        self.lib.ref_sort_merge.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32, C.c_uint32, C.c_char_p,
+                                            C.c_uint32]
+        b, p = build.copy(), probe.copy()
+        buf = C.create_string_buffer(4096)
+        rc = self.lib.ref_sort_merge(_p(b), b.size, _p(p), p.size, num_partitions, buf, 4096)
+        assert rc >= 0
+        return json.loads(buf.value.decode())
+
     def generate_data(self, dist, n, distinct=None, rng=16):
         out = np.empty(n, dtype=np.uint64)
         rc = self.lib.ref_generate_data(dist.encode(), n, distinct if distinct is not None else n, rng, _p(out))

@@ -174,3 +174,47 @@ def test_htm_serial_no_conflicts_on_dense_keys(oracle):
     R = oracle.generate_data("shuffle", 1 << 14)
     conflicts, ts, cs = oracle.htm_serial(R)
     assert conflicts == 0 and cs == 0 and ts == oracle.sum(R)
+
+
+def _ref_sortmerge_restated(build, probe, slices=64):
+    """SortMerge.cpp:13-35 restated: sort the build side, then a two-pointer merge of build[a:b) with probe[a:b)
+    for each of the 64 equal index slices (blocked_range grain = n/64, simple partitioner), both pointers advancing
+    on equality -- the true join only when both sides hold the same unique keys."""
+    b = np.sort(build)
+    n, total = b.size, 0
+    for k in range(slices):
+        lo, hi = k * n // slices, (k + 1) * n // slices
+        li = ri = lo
+        bl, pl = b[lo:hi].tolist(), probe[lo:hi].tolist()
+        li = ri = 0
+        m = hi - lo
+        while li < m and ri < m:
+            left, right = bl[li], pl[ri]
+            total += left == right
+            li += left <= right
+            ri += left >= right
+    return total
+
+
+def test_reference_sortmerge_pins_the_comparator(oracle):
+    """The reference's own SortMerge.cpp compiled into oracle/_ref.  Unique dense keys against S = sorted 1..n
+    (main.cpp:93, the only probe side the reference runs it on): totalMatches = n = the true join, which is what
+    the GPU comparator returns (tests/test_sortmerge_gpu.py).  With duplicate keys ("uniform") its slice-wise
+    lock-step merge is not a join: the restatement above reproduces its count, the true join is larger."""
+    ref = oracle_lib.Reference(probe=True)
+    if not ref.available or ref.sort_merge(np.arange(1, 65, dtype=np.uint64), np.arange(1, 65, dtype=np.uint64)) is None:
+        pytest.skip("oracle/_ref without SortMerge")
+    n = 1 << 16
+    S = oracle.generate_data("sorted", n)
+    for dist in ("sorted", "shuffle", "local_shuffle"):
+        R = oracle.generate_data(dist, n)
+        j = ref.sort_merge(R, S)
+        assert list(j.keys()) == ["algo", "rSize", "hashBuildTimeInMicroseconds", "sortTimeInMicroseconds",
+                                  "mergeTimeInMicroseconds", "totalMatches", "inputSum"]
+        assert j["totalMatches"] == oracle.true_join(R, S)[0] == n, dist
+        assert j["inputSum"] == oracle.sum(R) == n * (n + 1) // 2, dist
+        assert j["totalMatches"] == _ref_sortmerge_restated(R, S), dist
+    R = oracle.generate_data("uniform", n)
+    j = ref.sort_merge(R, S)
+    assert j["totalMatches"] == _ref_sortmerge_restated(R, S)
+    assert j["totalMatches"] < oracle.true_join(R, S)[0] == n

@@ -146,3 +146,20 @@ def test_sortmerge_entry_point_and_cli(hj):
     assert out.returncode == 0, out.stdout + out.stderr
     line = json.loads(out.stdout.strip().splitlines()[-1])
     assert line["totalMatches"] == n and line["path"] == "sortmerge"
+
+
+def test_sortmerge_equals_the_reference_binary(hj):
+    """The reference's SortMerge.cpp itself (oracle/_ref, compiled unmodified) on the same arrays: same totalMatches
+    and inputSum as the GPU entry point, for the unique-key inputs on which the reference's merge is a join."""
+    from tests import oracle_lib
+    ref = oracle_lib.Reference(probe=True)
+    n = 1 << 18
+    S = hj.generate_data("sorted", n)
+    if not ref.available or ref.sort_merge(S[:64], S[:64]) is None:
+        pytest.skip("oracle/_ref without SortMerge")
+    for dist, rng in (("shuffle", 16), ("local_shuffle", 256), ("sorted", 16)):
+        R = hj.generate_data(dist, n, n, rng)
+        want = ref.sort_merge(R, S)
+        got = hj.SortMerge(R, n, S, n, 64)
+        assert (got["totalMatches"], got["inputSum"], got["rSize"]) == (want["totalMatches"], want["inputSum"],
+                                                                        want["rSize"]), dist
