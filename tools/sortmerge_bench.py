@@ -17,7 +17,34 @@ import htm_hashjoin_b200 as hj  # noqa: E402
 ap = argparse.ArgumentParser()
 ap.add_argument("--sizes", default="24:27,27:30", help="log2|R|:log2|S| pairs")
 ap.add_argument("--reps", type=int, default=3)
+ap.add_argument("--cpu-log-n", type=int, default=0,
+                help="also time the reference's own SortMerge.cpp (oracle/_ref) on the host cores against the GPU "
+                     "entry point on the same DataGen arrays of 2^n tuples (checker code: only this tool runs it)")
 a = ap.parse_args()
+if a.cpu_log_n:
+    import time
+    from tests import oracle_lib
+    ref = oracle_lib.Reference(probe=True)
+    n = 1 << a.cpu_log_n
+    S = hj.generate_data("sorted", n)
+    for dist in ("sorted", "shuffle"):
+        R = hj.generate_data(dist, n)
+        row = {"comparator": "SortMerge", "rSize": n, "dataDistr": dist, "host_cores": os.cpu_count()}
+        if ref.available and ref.sort_merge(S[:64], S[:64]) is not None:
+            j = ref.sort_merge(R, S)
+            row["reference_cpu"] = {k: j[k] for k in ("hashBuildTimeInMicroseconds", "sortTimeInMicroseconds",
+                                                      "mergeTimeInMicroseconds", "totalMatches")}
+        hj.SortMerge(R, n, S, n, 64)  # warm-up: context, buffers
+        t0 = time.perf_counter()
+        g = hj.SortMerge(R, n, S, n, 64)
+        wall = (time.perf_counter() - t0) * 1e6
+        row["gpu"] = {"hashBuildTimeInMicroseconds": g["hashBuildTimeInMicroseconds"],
+                      "deviceTimeInMicroseconds": g["deviceTimeInMicroseconds"],
+                      "sortTimeInMicroseconds": g["sortTimeInMicroseconds"],
+                      "mergeTimeInMicroseconds": g["mergeTimeInMicroseconds"], "h2dMicroseconds": g["h2dMicroseconds"],
+                      "totalMatches": g["totalMatches"],
+                      "call_wall_us_incl_create_reserve": round(wall, 1)}
+        print(json.dumps(row), flush=True)
 for pair in a.sizes.split(","):
     lr, ls = (int(x) for x in pair.split(":"))
     n, m = 1 << lr, 1 << ls
