@@ -7,9 +7,9 @@
 // Both relations arrive radix-partitioned on the same key bits (rx_kernels.cuh, exact layout), so
 // the join is per partition pair and no global order is needed (the m-way / MPSM arrangement):
 //   one CTA per partition p
-//     A = R_p sorted by key in shared memory (bitonic network; chunks of capA if R_p is larger)
-//     for every tile of S_p: B = tile sorted by key in shared memory
-//       merge: thread t owns V consecutive elements of B, finds its start in A with ONE binary
+//     A = R_p sorted by key, kept in shared memory (chunks of capA if R_p is larger)
+//     for every 4096-tuple tile of S_p: B = the tile sorted by key
+//       merge: thread t owns 8 consecutive elements of B, finds its start in A with ONE binary
 //       search (the merge-path split) and then walks A and its B elements with two pointers;
 //       equal runs in A are rescanned for equal keys in B (mark / restore of a merge join).
 // Tiles of up to 4096 tuples are sorted in REGISTERS (sm_sort_regs): 512 threads x 8 elements, element
