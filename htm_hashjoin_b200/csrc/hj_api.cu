@@ -828,13 +828,25 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
     const u32 tileB = 4096;
     u32 capA = variant ? 4096 : 1024;
     while (capA < 8192 && capA < need) capA <<= 1;  // larger R partitions are merged chunk by chunk
-    const size_t smem = (size_t)(capA + tileB) * 8;
     // encoding of the register sort by key mask (rx_sortmerge.cuh); HJ_SM_MODE=0 forces the generic order
     int mode = h->cfg.key_mask == 0xffffffffull ? 1 : h->cfg.key_mask == ~0ull ? 2 : 0;
     if (getenv("HJ_SM_MODE")) mode = atoi(getenv("HJ_SM_MODE")) ? mode : 0;
-    const void* k = !variant ? (const void*)rx_sortmerge_kernel
-                    : mode == 1 ? (const void*)rx_sortmerge_regs_kernel<1>
-                    : mode == 2 ? (const void*)rx_sortmerge_regs_kernel<2> : (const void*)rx_sortmerge_regs_kernel<0>;
+    // HJ_SM_CTAS=3 (opt-in, the A/B record): the scan of R's histogram has left the largest R partition in the
+    // counters; when none exceeds 4096 tuples (dense keys split evenly by their low bits) A needs 32 KB only and
+    // three 40-register CTAs fit an SM.  Measured at C3: 27.61 ms vs 27.73 ms with two -- the kernel is bound by
+    // the ALU pipe, not by latency -- so the default stays at two and saves the counter read-back.
+    static const int want_ctas = getenv("HJ_SM_CTAS") ? atoi(getenv("HJ_SM_CTAS")) : 2;
+    int ctas = 2;
+    if (variant && want_ctas == 3) {
+      if ((rc = fetch_counters(h))) return rc;
+      if (h->h_ctr[C_MAX_PART] <= 4096) { capA = 4096; ctas = 3; }
+    }
+    const size_t smem = (size_t)(capA + tileB) * 8;
+    const void* k2 = mode == 1 ? (const void*)rx_sortmerge_regs_kernel<1, 2>
+                     : mode == 2 ? (const void*)rx_sortmerge_regs_kernel<2, 2> : (const void*)rx_sortmerge_regs_kernel<0, 2>;
+    const void* k3 = mode == 1 ? (const void*)rx_sortmerge_regs_kernel<1, 3>
+                     : mode == 2 ? (const void*)rx_sortmerge_regs_kernel<2, 3> : (const void*)rx_sortmerge_regs_kernel<0, 3>;
+    const void* k = !variant ? (const void*)rx_sortmerge_kernel : ctas == 3 ? k3 : k2;
     CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int grid = grid_for(h, k, kSmThreads, smem);
     if ((u32)grid > nparts) grid = (int)nparts;

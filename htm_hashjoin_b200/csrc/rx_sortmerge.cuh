@@ -258,9 +258,10 @@ __device__ __forceinline__ void sm_merge_regs(const u64 (&v)[kSmIPT], u32 nb, co
 }
 
 // The register-sort version (default).  capA: 4096 or 8192; shared memory = (capA + 4096) * 8 bytes.  A holds
-// encoded tuples.
-template <int MODE>
-__global__ void __launch_bounds__(kSmThreads)
+// encoded tuples.  CTAS = CTAs per SM the register budget is set for: 3 needs capA = 4096 (64 KB per CTA), which
+// the host picks when no R partition is larger.
+template <int MODE, int CTAS>
+__global__ void __launch_bounds__(kSmThreads, CTAS)
 rx_sortmerge_regs_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const u64* __restrict__ Sp,
                          const u64* __restrict__ offS, u32 nparts, u32 capA, u64 key_mask, u64* __restrict__ ctr) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
