@@ -8,6 +8,7 @@ this path with the same names and argument meaning:
   AtomicHashBuild        AtomicHashBuild.hpp:14-20
   NoCCHashBuild          NoCCHashBuild.hpp:13-19
   HTMHashBuild           HTMHashBuild.hpp:54-60  (adaptive path on the GPU)
+  SortMerge              SortMerge.hpp:5-6  (the sort-merge comparator)
   PRO                    mc/src/parallel_radix_join.h:33-34
 
 Each *HashBuild returns the dict of the JSON line the reference prints
