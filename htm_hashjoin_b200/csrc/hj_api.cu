@@ -732,7 +732,6 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
   const bool use_l2 = !sortmerge && dS && (getenv("HJ_FORCE_L2JOIN") || need > l2_min_need) && !getenv("HJ_NO_L2JOIN");
   if (sortmerge) {
     if (!dS || mat || pre1) return HJ_EINVAL;
-    force_exact = true;  // contiguous partitions [off[p], off[p+1])
   }
   // Histogram-free partitioning (ScOpt, rx_kernels.cuh) for the 2-pass shared-memory join; the
   // exact, histogram-based layout everywhere else and after an overflow on this handle.
@@ -822,7 +821,7 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
     return HJ_OK;
   }
   if (sortmerge) {
-    // per-partition sort + merge (rx_sortmerge.cuh) on the exact layout
+    // per-partition sort + merge (rx_sortmerge.cuh) on either layout
     // register sort (default) or the shared-memory-only network (HJ_SM_VARIANT=0, the A/B record)
     static const int variant = getenv("HJ_SM_VARIANT") ? atoi(getenv("HJ_SM_VARIANT")) : 1;
     const u32 tileB = 4096;
@@ -837,7 +836,7 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
     // the ALU pipe, not by latency -- so the default stays at two and saves the counter read-back.
     static const int want_ctas = getenv("HJ_SM_CTAS") ? atoi(getenv("HJ_SM_CTAS")) : 2;
     int ctas = 2;
-    if (variant && want_ctas == 3) {
+    if (variant && want_ctas == 3 && !opt) {
       if ((rc = fetch_counters(h))) return rc;
       if (h->h_ctr[C_MAX_PART] <= 4096) { capA = 4096; ctas = 3; }
     }
@@ -851,21 +850,29 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
     int grid = grid_for(h, k, kSmThreads, smem);
     if ((u32)grid > nparts) grid = (int)nparts;
     if (variant) {
-      const u64 *aR = h->rb[0].out.p, *aoR = h->rb[0].offsets.p, *aS = h->rb[1].out.p, *aoS = h->rb[1].offsets.p;
+      // histogram-free layout: the partitions' ends are the scatter's final cursors
+      const u64 *aR = h->rb[0].out.p, *aoR = opt ? h->rb[0].cursors.p : h->rb[0].offsets.p, *aS = h->rb[1].out.p,
+                *aoS = opt ? h->rb[1].cursors.p : h->rb[1].offsets.p;
       u32 a_np = nparts;
-      u64 a_km = h->cfg.key_mask;
+      u64 a_km = h->cfg.key_mask, a_capR = capR, a_capS = capS;
       u64* a_ctr = h->ctr;
-      void* args[] = {&aR, &aoR, &aS, &aoS, &a_np, &capA, &a_km, &a_ctr};
+      void* args[] = {&aR, &aoR, &aS, &aoS, &a_np, &capA, &a_km, &a_ctr, &a_capR, &a_capS};
       CK(cudaLaunchKernel(k, dim3(grid), dim3(kSmThreads), args, smem, h->stream));
     } else
-      rx_sortmerge_kernel<<<grid, kSmThreads, smem, h->stream>>>(h->rb[0].out.p, h->rb[0].offsets.p, h->rb[1].out.p,
-                                                                 h->rb[1].offsets.p, nparts, capA, tileB,
-                                                                 h->cfg.key_mask, h->ctr);
+      rx_sortmerge_kernel<<<grid, kSmThreads, smem, h->stream>>>(
+          h->rb[0].out.p, opt ? h->rb[0].cursors.p : h->rb[0].offsets.p, h->rb[1].out.p,
+          opt ? h->rb[1].cursors.p : h->rb[1].offsets.p, nparts, capA, tileB, h->cfg.key_mask, h->ctr, capR, capS);
     h->launches++;
     CK(cudaGetLastError());
     mark(h, E_JOIN);
     mark(h, E_END);
     if ((rc = fetch_counters(h))) return rc;
+    if (opt && h->h_ctr[C_OPT_OVF]) {
+      // a region overflowed (skewed partition sizes): nothing was lost -- redo on the exact layout
+      h->no_optimistic = true;
+      return run_radix_join(h, dR, n, false, dS, m, false, res, false, true, nullptr, nullptr, nullptr, nullptr, nullptr,
+                            true);
+    }
     if (res) {
       fill_common(h, res);
       res->path_taken = HJ_PATH_SORTMERGE;
@@ -1236,8 +1243,8 @@ int hj_join(hj_handle* h, const uint64_t* R, uint64_t n, const uint64_t* S, uint
     mark(h, E_CP0, h->copy_stream);
     if ((rc = stage(h, (const u64*)R, n, h->stageR, &dR, E_CPR, &pendR))) return rc;
     if ((rc = stage(h, (const u64*)S, m, h->stageS, &dS, E_CPS, &pendS))) return rc;
-    return run_radix_join(h, dR, n, pendR, dS, m, pendS, res, false, algo == HJ_ALGO_SORTMERGE, nullptr, nullptr,
-                          nullptr, nullptr, nullptr, algo == HJ_ALGO_SORTMERGE);
+    return run_radix_join(h, dR, n, pendR, dS, m, pendS, res, false, false, nullptr, nullptr, nullptr, nullptr, nullptr,
+                          algo == HJ_ALGO_SORTMERGE);
   }
   // the table clear needs no input: enqueue it first so it runs under the R copy
   if ((rc = prepare_table(h, n))) return rc;

@@ -4,7 +4,7 @@
 // probe side being generate_data("sorted") (main.cpp:93); here both sides are sorted, so any S works
 // and duplicates on either side count as in the true join (sum_k cntR(k) * cntS(k)).
 //
-// Both relations arrive radix-partitioned on the same key bits (rx_kernels.cuh, exact layout), so
+// Both relations arrive radix-partitioned on the same key bits (rx_kernels.cuh, either layout), so
 // the join is per partition pair and no global order is needed (the m-way / MPSM arrangement):
 //   one CTA per partition p
 //     A = R_p sorted by key, kept in shared memory (chunks of capA if R_p is larger)
@@ -161,7 +161,7 @@ __device__ __forceinline__ void sm_sort_regs(u64 (&v)[kSmIPT], u64* X, u32 L, u6
 __global__ void __launch_bounds__(kSmThreads)
 rx_sortmerge_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const u64* __restrict__ Sp,
                     const u64* __restrict__ offS, u32 nparts, u32 capA, u32 tileB, u64 key_mask,
-                    u64* __restrict__ ctr) {
+                    u64* __restrict__ ctr, u64 capR, u64 capS) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   u64* A = reinterpret_cast<u64*>(smem_raw);
   u64* B = A + capA;
@@ -170,7 +170,12 @@ rx_sortmerge_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, co
   u64 matches = 0, checksum = 0, maxpart = 0, chunked = 0;
 
   for (u32 p = blockIdx.x; p < nparts; p += gridDim.x) {
-    const u64 r0 = offR[p], r1 = offR[p + 1], s0 = offS[p], s1 = offS[p + 1];
+    // exact layout: partition p = [off[p], off[p+1]); histogram-free layout (cap != 0): [p*cap, min(off[p],
+    // (p+1)*cap)) with off = the scatter's final cursors (as rx_join_kernel)
+    const u64 r0 = capR ? p * capR : offR[p];
+    const u64 r1 = capR ? (offR[p] < r0 + capR ? offR[p] : r0 + capR) : offR[p + 1];
+    const u64 s0 = capS ? p * capS : offS[p];
+    const u64 s1 = capS ? (offS[p] < s0 + capS ? offS[p] : s0 + capS) : offS[p + 1];
     const u64 nr = r1 - r0;
     maxpart = nr > maxpart ? nr : maxpart;
     if (nr == 0 || s1 == s0) continue;
@@ -263,7 +268,8 @@ __device__ __forceinline__ void sm_merge_regs(const u64 (&v)[kSmIPT], u32 nb, co
 template <int MODE, int CTAS>
 __global__ void __launch_bounds__(kSmThreads, CTAS)
 rx_sortmerge_regs_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const u64* __restrict__ Sp,
-                         const u64* __restrict__ offS, u32 nparts, u32 capA, u64 key_mask, u64* __restrict__ ctr) {
+                         const u64* __restrict__ offS, u32 nparts, u32 capA, u64 key_mask, u64* __restrict__ ctr,
+                         u64 capR, u64 capS) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   u64* A = reinterpret_cast<u64*>(smem_raw);
   u64* X = A + capA;  // exchange buffer of the register sort
@@ -273,7 +279,12 @@ rx_sortmerge_regs_kernel(const u64* __restrict__ Rp, const u64* __restrict__ off
   u64 v[kSmIPT];
 
   for (u32 p = blockIdx.x; p < nparts; p += gridDim.x) {
-    const u64 r0 = offR[p], r1 = offR[p + 1], s0 = offS[p], s1 = offS[p + 1];
+    // exact layout: partition p = [off[p], off[p+1]); histogram-free layout (cap != 0): [p*cap, min(off[p],
+    // (p+1)*cap)) with off = the scatter's final cursors (as rx_join_kernel)
+    const u64 r0 = capR ? p * capR : offR[p];
+    const u64 r1 = capR ? (offR[p] < r0 + capR ? offR[p] : r0 + capR) : offR[p + 1];
+    const u64 s0 = capS ? p * capS : offS[p];
+    const u64 s1 = capS ? (offS[p] < s0 + capS ? offS[p] : s0 + capS) : offS[p + 1];
     const u64 nr = r1 - r0;
     maxpart = nr > maxpart ? nr : maxpart;
     if (nr == 0 || s1 == s0) continue;
