@@ -126,6 +126,12 @@ class HashJoin:
     def reserve(self, max_r, max_s=0):
         self._check(lib.hj_reserve(self._h, int(max_r), int(max_s)), "hj_reserve")
 
+    def reserve_staging(self, max_r, max_s=0):
+        self._check(lib.hj_reserve_staging(self._h, int(max_r), int(max_s)), "hj_reserve_staging")
+
+    def alloc_count(self):
+        return int(lib.hj_alloc_count(self._h))
+
     def build(self, R):
         p, n = _ptr(R)
         res = hj_result()

@@ -23,7 +23,7 @@ ABI_SYMBOLS = [
     "hj_copy", "hj_flush_l2", "hj_sync",
     "hj_radix_plan", "hj_ipc_export", "hj_ipc_open", "hj_ipc_close", "hj_peer_hist", "hj_peer_scatter",
     "hj_join_pass1", "hj_join_materialize", "hj_peer_scatter_async",
-    "hj_peer_scatter_regions", "hj_join_regions",
+    "hj_peer_scatter_regions", "hj_join_regions", "hj_reserve_staging", "hj_alloc_count",
 ]
 # host-side mirror of the reference interface (csrc/ref_entry.hpp, csrc/datagen.hpp)
 HOST_SYMBOLS = ["hj_ref_run", "hj_ref_set_radix", "hj_ref_set_device", "hj_ref_last_status",
@@ -81,6 +81,8 @@ def load():
         "hj_strerror": (C.c_char_p, [C.c_int]),
         "hj_last_error": (C.c_char_p, [H]),
         "hj_reserve": (C.c_int, [H, C.c_uint64, C.c_uint64]),
+        "hj_reserve_staging": (C.c_int, [H, C.c_uint64, C.c_uint64]),
+        "hj_alloc_count": (C.c_uint64, [H]),
         "hj_build": (C.c_int, [H, u64p, C.c_uint64, C.POINTER(hj_result)]),
         "hj_probe": (C.c_int, [H, u64p, C.c_uint64, C.POINTER(hj_result)]),
         "hj_join": (C.c_int, [H, u64p, C.c_uint64, u64p, C.c_uint64, C.POINTER(hj_result)]),

@@ -40,6 +40,38 @@ struct RelBufs {  // radix-side buffers for one relation
   DevBuf tmp, out, ghist, offsets, cursors, poff, pcur, ptiles, one, pend;
 };
 
+// A/B switches of the experiments under profiles/ (all default off), read when a handle is created:
+// nothing on a timed path calls getenv.
+struct Env {
+  bool sc_no_bulk, sc_tmain, no_optimistic, force_l2, no_l2, no_join32, peer_no_bulk;
+  int sc_ipt, sm_variant, sm_mode, sm_ctas, j32_variant, join_variant, peer_ipt, peer_ctas;
+  u64 l2_min_need, join_slice;
+};
+Env read_env() {
+    auto num = [](const char* k, long long dflt) { const char* v = getenv(k); return v ? atoll(v) : dflt; };
+    Env x;
+    x.sc_no_bulk = getenv("HJ_SC_NO_BULK") != nullptr;
+    x.sc_tmain = getenv("HJ_SC_TMAIN") != nullptr;
+    x.no_optimistic = getenv("HJ_NO_OPTIMISTIC") != nullptr;
+    x.force_l2 = getenv("HJ_FORCE_L2JOIN") != nullptr;
+    x.no_l2 = getenv("HJ_NO_L2JOIN") != nullptr;
+    x.no_join32 = getenv("HJ_NO_JOIN32") != nullptr;
+    x.peer_no_bulk = getenv("HJ_PEER_NO_BULK") != nullptr;
+    x.sc_ipt = (int)num("HJ_SC_IPT", 16);
+    x.sm_variant = (int)num("HJ_SM_VARIANT", 1);
+    x.sm_mode = (int)num("HJ_SM_MODE", -1);
+    x.sm_ctas = (int)num("HJ_SM_CTAS", 2);
+    x.j32_variant = (int)num("HJ_J32_VARIANT", -1);
+    x.join_variant = (int)num("HJ_JOIN_VARIANT", 0);
+    x.peer_ipt = (int)num("HJ_PEER_IPT", 32);
+    x.peer_ctas = (int)num("HJ_PEER_CTAS", 0);
+    x.l2_min_need = (u64)num("HJ_L2_MIN_NEED", 63000);
+    x.join_slice = (u64)num("HJ_JOIN_SLICE", 0);
+    return x;
+}
+Env g_env = read_env();  // refreshed by every hj_create
+const Env& env() { return g_env; }
+
 }  // namespace
 
 struct hj_handle {
@@ -55,6 +87,8 @@ struct hj_handle {
   u64* h_ctr = nullptr;  // pinned mirror
   // global table
   DevBuf table, ovf_table, ovf_list;
+  DevBuf claim;   // one bit per slot: the build's claims (gt_kernels.cuh)
+  DevBuf ovfmap;  // one bit per home slot: some tuple of that home overflowed
   u64 slots = 0, mask = 0;
   bool built = false;
   bool no_optimistic = false;  // a histogram-free attempt overflowed on this handle: stay on the exact path
@@ -67,6 +101,7 @@ struct hj_handle {
   DevBuf tasks;      // join tasks (partition, S slice) of rx_join32 (skew handling)
   DevBuf mat_cnt;    // per-partition pair counts / offsets of the materialising join
   u32 launches = 0;
+  u64 allocs = 0;  // cudaMalloc calls made by ensure() over the handle's life (hj_alloc_count)
   char err[256];
 };
 
@@ -83,10 +118,12 @@ namespace {
 
 int ensure(hj_handle* h, DevBuf& b, u64 elems) {
   if (b.cap >= elems) return HJ_OK;
+  if (&b == &h->table) h->built = false;  // the old table goes away with its contents
   if (b.p) CK(cudaFree(b.p));
   b.p = nullptr;
   b.cap = 0;
   CK(cudaMalloc(&b.p, elems * sizeof(u64)));
+  h->allocs++;
   b.cap = elems;
   return HJ_OK;
 }
@@ -130,9 +167,22 @@ u32 ipt_for(u32 tsize) {
 
 // ---- global table -------------------------------------------------------------
 
-template <int IPT, bool NOCC, bool STATS>
+template <int IPT, bool STATS>
 int launch_build_t(hj_handle* h, const u64* R, const SegMap& sm, u64 key_mask) {
-  auto k = gt_build_kernel<IPT, NOCC, STATS>;
+  auto k = gt_build_kernel<IPT, STATS>;
+  int grid = grid_for(h, (const void*)k, kGtThreads, 0);
+  u64 chunks = ((sm.seg_len + kGtThreads * IPT - 1) / (kGtThreads * IPT)) * sm.nslices;
+  if (chunks == 0) return HJ_OK;
+  if ((u64)grid > chunks) grid = (int)chunks;
+  k<<<grid, kGtThreads, 0, h->stream>>>(R, sm, h->table.p, reinterpret_cast<u32*>(h->claim.p), h->mask, key_mask,
+                                        h->cfg.probe_length, h->ovf_list.p, h->ctr);
+  h->launches++;
+  CK(cudaGetLastError());
+  return HJ_OK;
+}
+template <int IPT>
+int launch_nocc_t(hj_handle* h, const u64* R, const SegMap& sm, u64 key_mask) {
+  auto k = gt_nocc_build_kernel<IPT>;
   int grid = grid_for(h, (const void*)k, kGtThreads, 0);
   u64 chunks = ((sm.seg_len + kGtThreads * IPT - 1) / (kGtThreads * IPT)) * sm.nslices;
   if (chunks == 0) return HJ_OK;
@@ -144,27 +194,23 @@ int launch_build_t(hj_handle* h, const u64* R, const SegMap& sm, u64 key_mask) {
   return HJ_OK;
 }
 
+// (8-byte loads: no alignment requirement beyond the tuple's own)
 int launch_build(hj_handle* h, const u64* R, const SegMap& sm, bool nocc, bool stats, u32 ipt) {
   const u64 km = h->cfg.key_mask;
-  // 16-byte loads need even tuple offsets from a 16-byte aligned base
-  if ((((uintptr_t)R) & 15) || (sm.slice_stride & 1) || (sm.slice_off & 1)) ipt = 1;
-  if (stats) {
-    if (ipt == 1) return launch_build_t<1, false, true>(h, R, sm, km);
-    return launch_build_t<2, false, true>(h, R, sm, km);
-  }
+  if (stats) return launch_build_t<2, true>(h, R, sm, km);
   if (nocc) {
     switch (ipt) {
-      case 1: return launch_build_t<1, true, false>(h, R, sm, km);
-      case 2: return launch_build_t<2, true, false>(h, R, sm, km);
-      case 4: return launch_build_t<4, true, false>(h, R, sm, km);
-      default: return launch_build_t<8, true, false>(h, R, sm, km);
+      case 1: return launch_nocc_t<1>(h, R, sm, km);
+      case 2: return launch_nocc_t<2>(h, R, sm, km);
+      case 4: return launch_nocc_t<4>(h, R, sm, km);
+      default: return launch_nocc_t<8>(h, R, sm, km);
     }
   }
   switch (ipt) {
-    case 1: return launch_build_t<1, false, false>(h, R, sm, km);
-    case 2: return launch_build_t<2, false, false>(h, R, sm, km);
-    case 4: return launch_build_t<4, false, false>(h, R, sm, km);
-    default: return launch_build_t<8, false, false>(h, R, sm, km);
+    case 1: return launch_build_t<1, false>(h, R, sm, km);
+    case 2: return launch_build_t<2, false>(h, R, sm, km);
+    case 4: return launch_build_t<4, false>(h, R, sm, km);
+    default: return launch_build_t<8, false>(h, R, sm, km);
   }
 }
 
@@ -176,18 +222,17 @@ int launch_probe_t(hj_handle* h, const u64* S, u64 m) {
   if (chunks == 0) return HJ_OK;
   if ((u64)grid > chunks) grid = (int)chunks;
   k<<<grid, kGtThreads, 0, h->stream>>>(S, m, h->table.p, h->mask, h->cfg.key_mask, h->cfg.probe_length,
-                                        h->ovf_table.p, h->ovf_table.cap, h->ctr);
+                                        h->ovf_table.p, h->ovf_table.cap, reinterpret_cast<const u32*>(h->ovfmap.p),
+                                        h->ctr);
   h->launches++;
   CK(cudaGetLastError());
   return HJ_OK;
 }
 int launch_probe(hj_handle* h, const u64* S, u64 m, u32 ipt) {
-  if (((uintptr_t)S) & 15) ipt = 1;
   switch (ipt) {
     case 1: return launch_probe_t<1>(h, S, m);
     case 2: return launch_probe_t<2>(h, S, m);
-    case 4: return launch_probe_t<4>(h, S, m);
-    default: return launch_probe_t<8>(h, S, m);
+    default: return launch_probe_t<4>(h, S, m);
   }
 }
 
@@ -206,29 +251,50 @@ int zero_async(hj_handle* h, u64* p, u64 elems) {
 
 int prepare_table(hj_handle* h, u64 n) {
   u32 scale = h->cfg.scale_output ? h->cfg.scale_output : 2;
-  u64 slots = pow2_ceil_u64(n * scale < 64 ? 64 : n * scale);
+  u64 slots = pow2_ceil_u64(n * scale < 128 ? 128 : n * scale);  // >= 4 words of the slot bitmaps
   int rc;
   if ((rc = ensure(h, h->table, slots))) return rc;
   if ((rc = ensure(h, h->ovf_table, slots))) return rc;  // worst case: everything overflows, load 0.5
   if ((rc = ensure(h, h->ovf_list, n ? n : 1))) return rc;
+  if ((rc = ensure(h, h->claim, slots / 64))) return rc;   // one bit per slot (slots >= 64)
+  if ((rc = ensure(h, h->ovfmap, slots / 64))) return rc;
+  if (slots != h->slots) h->built = false;  // a table of another geometry: what was built is gone
   h->slots = slots;
   h->mask = slots - 1;
   return HJ_OK;
 }
 
+// table + claim bitmap to zero (the reference's `new ...{}`, AtomicHashBuild.hpp:25: untimed there)
+int clear_table(hj_handle* h) {
+  int rc;
+  if ((rc = zero_async(h, h->table.p, h->slots))) return rc;
+  CK(cudaMemsetAsync(h->claim.p, 0, h->slots / 8, h->stream));
+  h->built = false;
+  return HJ_OK;
+}
+
 // Stage a host relation on the copy stream (or pass a device pointer through).
 // *pending is set when the compute stream still has to wait for ev_done.
-int stage(hj_handle* h, const u64* p, u64 n, DevBuf& buf, const u64** dev, int ev_done, bool* pending) {
+int stage(hj_handle* h, const u64* p, u64 n, DevBuf& buf, const u64** dev, int ev_done, bool* pending,
+          bool need16 = true) {
   *pending = false;
   if (n == 0 || p == nullptr) {
     *dev = nullptr;
     return HJ_OK;
   }
+  int rc;
   if (is_device_ptr(p)) {
-    *dev = p;
+    if (!need16 || ((uintptr_t)p & 15) == 0) {  // (the global-table kernels read 8 bytes at a time)
+      *dev = p;
+      return HJ_OK;
+    }
+    // a device relation that is only 8-byte aligned (a slice t[1:], an odd tuple offset): the radix
+    // kernels read tuples in 16-byte pairs, so it is moved to an aligned staging buffer first
+    if ((rc = ensure(h, buf, n + (n & 1)))) return rc;
+    CK(cudaMemcpyAsync(buf.p, p, n * sizeof(u64), cudaMemcpyDeviceToDevice, h->stream));
+    *dev = buf.p;
     return HJ_OK;
   }
-  int rc;
   if ((rc = ensure(h, buf, n + (n & 1)))) return rc;
   CK(cudaMemcpyAsync(buf.p, p, n * sizeof(u64), cudaMemcpyHostToDevice, h->copy_stream));
   mark(h, ev_done, h->copy_stream);
@@ -379,10 +445,11 @@ int run_build_rest(hj_handle* h, const u64* dR, u64 n, u64 stride, u64 slen, boo
 }
 
 int run_overflow(hj_handle* h) {
-  int grid = h->sm_count * 4;
-  gt_ovf_clear_kernel<<<grid, 256, 0, h->stream>>>(h->ovf_table.p, h->ctr, h->ovf_table.cap);
-  gt_ovf_insert_kernel<<<grid, 256, 0, h->stream>>>(h->ovf_list.p, h->ovf_table.p, h->ctr, h->cfg.key_mask,
-                                                    h->ovf_table.cap);
+  int grid = h->sm_count * 8;
+  u32* ovfmap = reinterpret_cast<u32*>(h->ovfmap.p);
+  gt_ovf_clear_kernel<<<grid, 256, 0, h->stream>>>(h->ovf_table.p, ovfmap, h->slots / 32, h->ctr, h->ovf_table.cap);
+  gt_ovf_insert_kernel<<<grid, 256, 0, h->stream>>>(h->ovf_list.p, h->ovf_table.p, ovfmap, h->ctr, h->mask,
+                                                    h->cfg.key_mask, h->ovf_table.cap);
   h->launches += 2;
   CK(cudaGetLastError());
   return HJ_OK;
@@ -394,6 +461,14 @@ int clear_probe_counters(hj_handle* h) {
 }
 
 // ---- radix --------------------------------------------------------------------
+
+// The building-block entry points take device pointers in place: they must be 16-byte aligned
+// (the kernels read tuples in pairs).  hj_join & co. re-stage a misaligned device input instead.
+int need_aligned16(hj_handle* h, const void* p, const char* what) {
+  if (((uintptr_t)p & 15) == 0) return HJ_OK;
+  snprintf(h->err, sizeof(h->err), "%s: device pointer %p is not 16-byte aligned", what, p);
+  return HJ_EINVAL;
+}
 
 // tile of the exact-layout passes (rx_hist + rx_scan offsets): 512 x 16 = 8192 tuples, as the histogram-free ones
 constexpr int kExactIPT = 16;
@@ -426,14 +501,15 @@ int plan_radix(hj_handle* h, u64 n, RadixPlan* pl, u64 target_per = 16384) {
   u32 passes = h->cfg.passes;
   if (passes == 0) passes = bits > 8 ? 2 : 1;
   if (passes > 2) return HJ_EINVAL;
-  if (passes == 1 && bits > kMaxBitsPerPass) return HJ_EINVAL;
+  // 1 pass beyond 2^12 (BASELINE configs[2] sweeps 1-pass up to 2^14, prj_params.h:15-22 builds it): no
+  // shared-memory tile holds a run per digit any more -- the direct scatter takes those (rx_scatter_direct_kernel)
   if (passes == 2 && bits < 2) passes = 1;
   pl->bits = bits;
   pl->passes = passes;
   pl->b1 = passes == 2 ? bits / 2 : bits;  // prj_params.h:76-78: pass 1 gets floor(b/2)
   if (passes == 2 && h->cfg.pass1_bits) {
     const u32 want = (u32)h->cfg.pass1_bits;
-    if (want < 1 || want >= bits || bits - want > kMaxBitsPerPass) return HJ_EINVAL;
+    if (want < 1 || want >= bits || want > kMaxBitsPerPass || bits - want > kMaxBitsPerPass) return HJ_EINVAL;
     pl->b1 = want;
   }
   pl->b2 = bits - pl->b1;
@@ -496,17 +572,11 @@ int launch_hist(hj_handle* h, const u64* in, u64 n, const Digit& dg, u32 nbins, 
   return HJ_OK;
 }
 
-bool sc_bulk() {
-  static const bool on = !getenv("HJ_SC_NO_BULK");
-  return on;
-}
+bool sc_bulk() { return !env().sc_no_bulk; }
 // Input tiles staged by TMA: measured SLOWER than register loads at C3 (scatter 1: 4.49 vs 3.80 ms,
 // scatter 2: 4.86 vs 4.16 ms, 3 CTAs/SM in both): the staging pass adds a shared-memory write and a
 // read per tuple to a kernel whose shared-memory pipe is already the busiest unit.  Opt-in only.
-bool sc_tmain() {
-  static const bool on = getenv("HJ_SC_TMAIN") != nullptr;
-  return on;
-}
+bool sc_tmain() { return env().sc_tmain; }
 // Bulk (TMA) flush per pass: one cp.async.bulk per run pays off while a run is long -- 4096-tuple tiles
 // over F <= 128 digits = 32+ tuples (scatter 2 at C3: 4.68 -> 4.09 ms); at 256 / 512 digits (16 / 8 tuples
 // per run, the pass 2 after a 4- / 8-GPU exchange) it LOSES to 8-byte stores from consecutive lanes:
@@ -518,12 +588,8 @@ bool sc_bulk_for(u32 F, u32 tile) { return sc_bulk() && F % 2 == 0 && F <= tile 
 // and every tuple pays for half as many barriers -- C3: scatter 1 3.77 -> 3.37 ms (87 % of the HBM roofline),
 // scatter 2 4.14 -> 3.57 ms, 116 k -> 128 k Mtuples/s.  HJ_SC_IPT = 8 | 16 | 32 overrides.
 u32 sc_opt_ipt() {
-  static const u32 v = [] {
-    const char* e = getenv("HJ_SC_IPT");
-    const int x = e ? atoi(e) : 16;
-    return (u32)(x == 8 || x == 32 ? x : 16);
-  }();
-  return v;
+  const int x = env().sc_ipt;
+  return (u32)(x == 8 || x == 32 ? x : 16);
 }
 using ScKernel = void (*)(const u64*, u64*, Digit, u32, u32, const u64*, const u64*, u64*, u64* const*, ScOpt);
 template <int IPT>
@@ -592,7 +658,14 @@ int radix_partition_rel(hj_handle* h, const u64* in, u64 n, RelBufs& rb, const R
 
   const u64 max_tiles1 = (n + tile - 1) / tile;
   int rc;
-  if (pl.passes == 1) {
+  if (pl.passes == 1 && pl.bits > kMaxBitsPerPass) {
+    // 2^13 .. 2^15 partitions in ONE pass: a tile of 8192 tuples holds less than one tuple per digit, so
+    // there is nothing to write-combine; every tuple claims its slot from the partition's cursor
+    rx_scatter_direct_kernel<<<h->sm_count * 8, 256, 0, h->stream>>>(in, n, rb.out.p, full, rb.cursors.p);
+    h->launches++;
+    CK(cudaGetLastError());
+    if (evb >= 0) { mark(h, evb + 3); mark(h, evb + 4); }
+  } else if (pl.passes == 1) {
     if ((rc = launch_scatter_t<kExactIPT>(h, in, rb.out.p, full, nb, 1, rb.poff.p, rb.ptiles.p, rb.cursors.p, max_tiles1)))
       return rc;
     if (evb >= 0) { mark(h, evb + 3); mark(h, evb + 4); }
@@ -699,6 +772,36 @@ int radix_partition_rel_opt(hj_handle* h, const u64* in, u64 n, RelBufs& rb, con
   return HJ_OK;
 }
 
+// Which layout and which join a radix call takes -- one function, so that hj_reserve sizes exactly
+// what hj_join will use.
+struct RadixChoice {
+  RadixPlan pl;
+  u64 need;     // R tuples per partition incl. 8 sigma of a random split
+  bool use_l2;  // partitions too large for shared memory: the L2-resident partition-local table
+  bool opt;     // histogram-free layout (fixed-capacity regions)
+};
+int choose_radix(hj_handle* h, u64 n, bool has_s, bool pre1, bool pre1_known, bool force_exact, bool sortmerge,
+                 RadixChoice* ch) {
+  int rc;
+  // sort-merge: R partitions of <= 4096 tuples sort in one 8192-element shared-memory network with slack
+  if ((rc = plan_radix(h, n, &ch->pl, sortmerge ? 4096 : 16384))) return rc;
+  const RadixPlan& pl = ch->pl;
+  // Which join: shared memory while an R partition (plus 8 sigma of a random split) fits the
+  // largest table one CTA can hold, else the L2-resident partition-local table (rx_joinl2.cuh).
+  const u64 per = (n >> pl.bits) + 1;
+  u64 need = per + 64;
+  for (u64 r = 1; r * r < per * 64; r++) need = per + 64 + r;  // + 8*sqrt(per)
+  ch->need = need;
+  // up to three shared-memory chunks per R partition (S_p is probed once per chunk) still beat the L2 table:
+  // 2^12 partitions at C3 (2 chunks) 17.6 ms through L2; HJ_L2_MIN_NEED overrides the switch point
+  ch->use_l2 = !sortmerge && has_s && (env().force_l2 || need > env().l2_min_need) && !env().no_l2;
+  // Histogram-free partitioning (ScOpt, rx_kernels.cuh) for the 2-pass shared-memory join; the
+  // exact, histogram-based layout everywhere else and after an overflow on this handle.
+  ch->opt = has_s && (!pre1 || pre1_known) && !ch->use_l2 && pl.passes == 2 && (1u << pl.b1) <= (u32)kScParentCache &&
+            !h->no_optimistic && !force_exact && !env().no_optimistic;
+  return HJ_OK;
+}
+
 // materialisation request (hj_join_materialize): out may be null (count only)
 struct MatReq {
   ulonglong2* out;
@@ -711,32 +814,22 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
                    bool pre1 = false, bool force_exact = false, const u64* offR1 = nullptr,
                    const u64* offS1 = nullptr, MatReq* mat = nullptr, const Pre1Regions* regR = nullptr,
                    const Pre1Regions* regS = nullptr, bool sortmerge = false) {
-  RadixPlan pl;
+  RadixChoice ch;
   int rc;
-  // sort-merge: R partitions of <= 4096 tuples sort in one 8192-element shared-memory network with slack
-  if ((rc = plan_radix(h, n, &pl, sortmerge ? 4096 : 16384))) {
-    snprintf(h->err, sizeof(h->err), "radix plan: numPartitions must be a power of two <= 2^%u (<= 2^%u for 1 pass)",
+  h->built = false;  // the counter block is about to be zeroed and (L2 join) the table reused: no probe after this
+  if ((rc = choose_radix(h, n, dS != nullptr, pre1, (offR1 && offS1) || (regR && regS), force_exact, sortmerge, &ch))) {
+    snprintf(h->err, sizeof(h->err), "radix plan: numPartitions must be a power of two <= 2^%u, passes 1|2, each of two passes <= 2^%u",
              kMaxTotalBits, kMaxBitsPerPass);
     return rc;
   }
+  const RadixPlan& pl = ch.pl;
   if (pre1 && pl.passes != 2) return HJ_EINVAL;
-  // Which join: shared memory while an R partition (plus 8 sigma of a random split) fits the
-  // largest table one CTA can hold, else the L2-resident partition-local table (rx_joinl2.cuh).
   const u32 nparts = 1u << pl.bits;
-  const u64 per = (n >> pl.bits) + 1;
-  u64 need = per + 64;
-  for (u64 r = 1; r * r < per * 64; r++) need = per + 64 + r;  // + 8*sqrt(per)
-  // up to three shared-memory chunks per R partition (S_p is probed once per chunk) still beat the L2 table:
-  // 2^12 partitions at C3 (2 chunks) 17.6 ms through L2; HJ_L2_MIN_NEED overrides the switch point
-  static const u64 l2_min_need = getenv("HJ_L2_MIN_NEED") ? strtoull(getenv("HJ_L2_MIN_NEED"), nullptr, 10) : 63000;
-  const bool use_l2 = !sortmerge && dS && (getenv("HJ_FORCE_L2JOIN") || need > l2_min_need) && !getenv("HJ_NO_L2JOIN");
+  const u64 need = ch.need;
+  const bool use_l2 = ch.use_l2, opt = ch.opt;
   if (sortmerge) {
     if (!dS || mat || pre1) return HJ_EINVAL;
   }
-  // Histogram-free partitioning (ScOpt, rx_kernels.cuh) for the 2-pass shared-memory join; the
-  // exact, histogram-based layout everywhere else and after an overflow on this handle.
-  const bool opt = dS && (!pre1 || (offR1 && offS1) || (regR && regS)) && !use_l2 && pl.passes == 2 && !h->no_optimistic && !force_exact &&
-                   !getenv("HJ_NO_OPTIMISTIC");
   const u64 capR = opt ? opt_region_cap(n, pl.bits) : 0, capS = opt ? opt_region_cap(m, pl.bits) : 0;
   if ((regR || regS) && !opt) return HJ_EINVAL;  // regions need the histogram-free 2-pass shared-memory plan
   if ((rc = ensure_rel(h, h->rb[0], n, pl, pre1, opt, regR ? regR->n_src : 1))) return rc;
@@ -823,18 +916,18 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
   if (sortmerge) {
     // per-partition sort + merge (rx_sortmerge.cuh) on either layout
     // register sort (default) or the shared-memory-only network (HJ_SM_VARIANT=0, the A/B record)
-    static const int variant = getenv("HJ_SM_VARIANT") ? atoi(getenv("HJ_SM_VARIANT")) : 1;
+    const int variant = env().sm_variant;
     const u32 tileB = 4096;
     u32 capA = variant ? 4096 : 1024;
     while (capA < 8192 && capA < need) capA <<= 1;  // larger R partitions are merged chunk by chunk
     // encoding of the register sort by key mask (rx_sortmerge.cuh); HJ_SM_MODE=0 forces the generic order
     int mode = h->cfg.key_mask == 0xffffffffull ? 1 : h->cfg.key_mask == ~0ull ? 2 : 0;
-    if (getenv("HJ_SM_MODE")) mode = atoi(getenv("HJ_SM_MODE")) ? mode : 0;
+    if (env().sm_mode == 0) mode = 0;
     // HJ_SM_CTAS=3 (opt-in, the A/B record): the scan of R's histogram has left the largest R partition in the
     // counters; when none exceeds 4096 tuples (dense keys split evenly by their low bits) A needs 32 KB only and
     // three 40-register CTAs fit an SM.  Measured at C3: 27.61 ms vs 27.73 ms with two -- the kernel is bound by
     // the ALU pipe, not by latency -- so the default stays at two and saves the counter read-back.
-    static const int want_ctas = getenv("HJ_SM_CTAS") ? atoi(getenv("HJ_SM_CTAS")) : 2;
+    const int want_ctas = env().sm_ctas;
     int ctas = 2;
     if (variant && want_ctas == 3 && !opt) {
       if ((rc = fetch_counters(h))) return rc;
@@ -909,9 +1002,9 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
   // 32-bit-key fast path first (returns at once if rx_hist saw wider keys), then the generic
   // kernel (returns at once if the fast path took the join).  Build-only PRO is generic.
   const bool try32 = !use_l2 && dS && pl.bits >= 1 && (h->cfg.key_mask & 0xffffffffull) == 0xffffffffull &&
-                     !getenv("HJ_NO_JOIN32");
+                     !env().no_join32;
   if (try32) {
-    static const int forced = getenv("HJ_J32_VARIANT") ? atoi(getenv("HJ_J32_VARIANT")) : -1;
+    const int forced = env().j32_variant;
     // CTAs/SM by table size (chunk capacity = 0.75 * slots): 4 -> 5.3k, 2 -> 10.8k, 1 -> 21.7k tuples
     const int variant = forced >= 0 ? forced : need <= 5300 ? 7 : need <= 10800 ? 3 : 10;
     const void* k;
@@ -953,7 +1046,7 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
     // tasks = (partition, S slice): S partitions beyond 4x the mean are probed by several CTAs
     u64 slice = 4 * (m >> pl.bits);
     if (slice < 32768) slice = 32768;
-    if (getenv("HJ_JOIN_SLICE")) slice = strtoull(getenv("HJ_JOIN_SLICE"), nullptr, 10);
+    if (env().join_slice) slice = env().join_slice;
     slice &= ~1ull;
     const u64 max_tasks = (u64)nparts + m / slice + 1;
     if ((rc = ensure(h, h->tasks, max_tasks))) return rc;
@@ -966,7 +1059,7 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
   if (!use_l2) {
     size_t smem = (size_t)pl.slots * 8;
     // <loads in flight per thread, CTAs/SM the register budget is set for>
-    static const int variant = getenv("HJ_JOIN_VARIANT") ? atoi(getenv("HJ_JOIN_VARIANT")) : 0;
+    const int variant = env().join_variant;
     auto k = variant == 1 ? rx_join_kernel<4, 3> : variant == 2 ? rx_join_kernel<6, 3> : rx_join_kernel<8, 2>;
     CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int grid = grid_for(h, (const void*)k, kJoinThreads, smem);
@@ -1085,6 +1178,7 @@ int hj_create(const hj_config* cfg, hj_handle** out) {
   if (ndev <= 0 || cfg->device < 0 || cfg->device >= ndev) return HJ_ECUDA;
   hj_handle* h = new (std::nothrow) hj_handle();
   if (!h) return HJ_ENOMEM;
+  g_env = read_env();
   h->cfg = *cfg;
   if (h->cfg.key_mask == 0) h->cfg.key_mask = ~0ull;
   h->device = cfg->device;
@@ -1112,7 +1206,7 @@ void hj_destroy(hj_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
   if (h->stream) cudaStreamSynchronize(h->stream);
-  DevBuf* bufs[] = {&h->table, &h->ovf_table, &h->ovf_list, &h->stageR, &h->stageS, &h->flush,
+  DevBuf* bufs[] = {&h->table, &h->ovf_table, &h->ovf_list, &h->claim, &h->ovfmap, &h->stageR, &h->stageS, &h->flush,
                     &h->peer_ptrs, &h->tasks, &h->mat_cnt};
   for (DevBuf* b : bufs)
     if (b->p) cudaFree(b->p);
@@ -1139,11 +1233,32 @@ int hj_reserve(hj_handle* h, uint64_t max_r, uint64_t max_s) {
     if ((rc = prepare_table(h, max_r))) return rc;
   }
   if (h->cfg.algo == HJ_ALGO_RADIX || h->cfg.algo == HJ_ALGO_ADAPTIVE || sortmerge) {
-    RadixPlan pl;
-    if ((rc = plan_radix(h, max_r, &pl, sortmerge ? 4096 : 16384))) return rc;
-    if ((rc = ensure_rel(h, h->rb[0], max_r, pl))) return rc;
-    if (max_s && (rc = ensure_rel(h, h->rb[1], max_s, pl))) return rc;
+    // exactly what run_radix_join will pick for these sizes: layout (histogram-free regions or exact),
+    // join tasks, the L2 table when the partitions are too large for shared memory
+    const bool has_s = max_s && h->cfg.enable_probe;
+    RadixChoice ch;
+    if ((rc = choose_radix(h, max_r, has_s, false, false, false, sortmerge, &ch))) return rc;
+    if ((rc = ensure_rel(h, h->rb[0], max_r, ch.pl, false, ch.opt))) return rc;
+    if (has_s && (rc = ensure_rel(h, h->rb[1], max_s, ch.pl, false, ch.opt))) return rc;
+    if (has_s) {
+      u64 slice = 4 * (max_s >> ch.pl.bits);
+      if (slice < 32768) slice = 32768;
+      if ((rc = ensure(h, h->tasks, (1ull << ch.pl.bits) + max_s / slice + 1))) return rc;
+      if ((rc = ensure(h, h->mat_cnt, (1ull << ch.pl.bits) + 1))) return rc;
+    }
+    if (ch.use_l2 && (rc = ensure(h, h->table, l2_table_slots(max_r, 1ull << ch.pl.bits)))) return rc;
   }
+  return HJ_OK;
+}
+
+uint64_t hj_alloc_count(const hj_handle* h) { return h ? h->allocs : 0; }
+
+int hj_reserve_staging(hj_handle* h, uint64_t max_r, uint64_t max_s) {
+  if (!h) return HJ_EINVAL;
+  CK(cudaSetDevice(h->device));
+  int rc;
+  if (max_r && (rc = ensure(h, h->stageR, max_r + (max_r & 1)))) return rc;
+  if (max_s && (rc = ensure(h, h->stageS, max_s + (max_s & 1)))) return rc;
   return HJ_OK;
 }
 
@@ -1157,12 +1272,12 @@ int hj_build(hj_handle* h, const uint64_t* R, uint64_t n, hj_result* res) {
   if ((rc = prepare_table(h, n))) return rc;
   mark(h, E_T0);
   CK(cudaMemsetAsync(h->ctr, 0, C_COUNT * sizeof(u64), h->stream));
-  if ((rc = zero_async(h, h->table.p, h->slots))) return rc;
+  if ((rc = clear_table(h))) return rc;
   mark(h, E_CLEAR);
   const u64* dR = nullptr;
   bool pendR = false;
   mark(h, E_CP0, h->copy_stream);
-  if ((rc = stage(h, (const u64*)R, n, h->stageR, &dR, E_CPR, &pendR))) return rc;
+  if ((rc = stage(h, (const u64*)R, n, h->stageR, &dR, E_CPR, &pendR, false))) return rc;
   if ((rc = wait_staged(h, E_CPR, pendR))) return rc;
   return run_global_join(h, dR, n, nullptr, 0, false, h->cfg.algo == HJ_ALGO_NOCC, false, 0, 0, res);
 }
@@ -1177,7 +1292,7 @@ int hj_probe(hj_handle* h, const uint64_t* S, uint64_t m, hj_result* res) {
   const u64* dS = nullptr;
   bool pendS = false;
   mark(h, E_CP0, h->copy_stream);
-  if ((rc = stage(h, (const u64*)S, m, h->stageS, &dS, E_CPS, &pendS))) return rc;
+  if ((rc = stage(h, (const u64*)S, m, h->stageS, &dS, E_CPS, &pendS, false))) return rc;
   if ((rc = wait_staged(h, E_CPS, pendS))) return rc;
   mark(h, E_T0);
   if ((rc = clear_probe_counters(h))) return rc;
@@ -1204,12 +1319,12 @@ int hj_sample(hj_handle* h, const uint64_t* R, uint64_t n, hj_result* res) {
   if ((rc = prepare_table(h, n))) return rc;
   mark(h, E_T0);
   CK(cudaMemsetAsync(h->ctr, 0, C_COUNT * sizeof(u64), h->stream));
-  if ((rc = zero_async(h, h->table.p, h->slots))) return rc;
+  if ((rc = clear_table(h))) return rc;
   mark(h, E_CLEAR);
   const u64* dR = nullptr;
   bool pendR = false;
   mark(h, E_CP0, h->copy_stream);
-  if ((rc = stage(h, (const u64*)R, n, h->stageR, &dR, E_CPR, &pendR))) return rc;
+  if ((rc = stage(h, (const u64*)R, n, h->stageR, &dR, E_CPR, &pendR, false))) return rc;
   if ((rc = wait_staged(h, E_CPR, pendR))) return rc;
   u64 stride, slen;
   if ((rc = run_sample(h, dR, n, &stride, &slen))) return rc;
@@ -1254,6 +1369,8 @@ int hj_join(hj_handle* h, const uint64_t* R, uint64_t n, const uint64_t* S, uint
     // Locality pre-check on a device-resident R: the span signal needs no table, so an input that is
     // going to the radix join anyway never pays for clearing one.  (Host inputs keep the order below:
     // their clear hides under the R copy.)
+    if ((rc = stage(h, (const u64*)R, n, h->stageR, &dR, E_CPR, &pendR))) return rc;  // re-staged if misaligned
+    R = reinterpret_cast<const uint64_t*>(dR);
     if ((rc = run_span(h, (const u64*)R, n))) return rc;
     if ((rc = fetch_counters(h))) return rc;
     const double locality = contention_of(h);
@@ -1274,17 +1391,18 @@ int hj_join(hj_handle* h, const uint64_t* R, uint64_t n, const uint64_t* S, uint
     }
     CK(cudaMemsetAsync(h->ctr, 0, C_COUNT * sizeof(u64), h->stream));
   }
-  if ((rc = zero_async(h, h->table.p, h->slots))) return rc;
+  if ((rc = clear_table(h))) return rc;
   mark(h, E_CLEAR);
   mark(h, E_CP0, h->copy_stream);
-  if ((rc = stage(h, (const u64*)R, n, h->stageR, &dR, E_CPR, &pendR))) return rc;
+  const bool global_only = algo == HJ_ALGO_ATOMIC || algo == HJ_ALGO_NOCC;
+  if ((rc = stage(h, (const u64*)R, n, h->stageR, &dR, E_CPR, &pendR, !global_only))) return rc;
   if ((rc = wait_staged(h, E_CPR, pendR))) return rc;
-  if (algo == HJ_ALGO_ATOMIC || algo == HJ_ALGO_NOCC) {
+  if (global_only) {
     // launch the build before staging S so the S copy runs under it
     // (run_global_join waits for S right before the probe)
     const bool host_s = S && !is_device_ptr(S);
     if (!host_s) {
-      if ((rc = stage(h, (const u64*)S, m, h->stageS, &dS, E_CPS, &pendS))) return rc;
+      if ((rc = stage(h, (const u64*)S, m, h->stageS, &dS, E_CPS, &pendS, false))) return rc;
       return run_global_join(h, dR, n, dS, m, pendS, algo == HJ_ALGO_NOCC, false, 0, 0, res);
     }
     const u32 ipt = ipt_for(h->cfg.transaction_size);
@@ -1370,7 +1488,7 @@ int hj_checksums(hj_handle* h, const uint64_t* R, uint64_t n, hj_result* res) {
   const u64* dR = nullptr;
   if (R && n) {
     bool pend = false;
-    if ((rc = stage(h, (const u64*)R, n, h->stageR, &dR, E_CPR, &pend))) return rc;
+    if ((rc = stage(h, (const u64*)R, n, h->stageR, &dR, E_CPR, &pend, false))) return rc;
     if ((rc = wait_staged(h, E_CPR, pend))) return rc;
   }
   CK(cudaMemsetAsync(h->ctr + C_SUM0, 0, 3 * sizeof(u64), h->stream));
@@ -1393,6 +1511,7 @@ int hj_radix_partition(hj_handle* h, const uint64_t* in, uint64_t n, uint32_t sh
                        uint64_t* offsets) {
   if (!h || !in || !out || !offsets || bits < 1 || bits > kMaxBitsPerPass) return HJ_EINVAL;
   if (!is_device_ptr(in) || !is_device_ptr(out) || !is_device_ptr(offsets)) return HJ_EINVAL;
+  if (need_aligned16(h, in, "hj_radix_partition(in)") || need_aligned16(h, out, "hj_radix_partition(out)")) return HJ_EINVAL;
   CK(cudaSetDevice(h->device));
   RelBufs& rb = h->rb[0];
   const u32 F = 1u << bits;
@@ -1423,6 +1542,7 @@ int hj_exchange_partition(hj_handle* h, const uint64_t* in, uint64_t n, uint32_t
                           uint64_t* out, uint64_t* offsets) {
   if (!h || !in || !out || !offsets || n_dest < 1 || n_dest > 4096 || domain_bits > 62) return HJ_EINVAL;
   if (!is_device_ptr(in) || !is_device_ptr(out) || !is_device_ptr(offsets)) return HJ_EINVAL;
+  if (need_aligned16(h, in, "hj_exchange_partition(in)") || need_aligned16(h, out, "hj_exchange_partition(out)")) return HJ_EINVAL;
   CK(cudaSetDevice(h->device));
   RelBufs& rb = h->rb[0];
   const u32 F = n_dest;
@@ -1500,6 +1620,7 @@ static int peer_digit(hj_handle* h, uint32_t n_dest, uint32_t domain_bits, uint3
 int hj_peer_hist(hj_handle* h, const uint64_t* in, uint64_t n, uint32_t n_dest, uint32_t domain_bits, uint32_t b1,
                  uint64_t* counts) {
   if (!h || !in || !counts || !is_device_ptr(in) || !is_device_ptr(counts)) return HJ_EINVAL;
+  if (need_aligned16(h, in, "hj_peer_hist(in)")) return HJ_EINVAL;
   Digit dg;
   int rc = peer_digit(h, n_dest, domain_bits, b1, &dg);
   if (rc) return rc;
@@ -1560,6 +1681,7 @@ static int peer_scatter_impl(hj_handle* h, const uint64_t* in, uint64_t n, uint3
                              uint32_t b1, uint64_t* const* peer_bufs, uint64_t* cursors, uint32_t max_ctas, bool sync,
                              const PeerRegions* reg) {
   if (!h || !in || !peer_bufs || !cursors || !is_device_ptr(in) || !is_device_ptr(cursors)) return HJ_EINVAL;
+  if (need_aligned16(h, in, "hj_peer_scatter(in)")) return HJ_EINVAL;
   Digit dg;
   int rc = peer_digit(h, n_dest, domain_bits, b1, &dg);
   if (rc) return rc;
@@ -1569,14 +1691,14 @@ static int peer_scatter_impl(hj_handle* h, const uint64_t* in, uint64_t n, uint3
   if ((rc = ensure(h, h->peer_ptrs, kScMaxPeers))) return rc;
   const u32 F = n_dest << b1;
   // tile = 512 x IPT tuples: 32 -> one CTA per SM, the longest runs; 16 (HJ_PEER_IPT=16) -> two CTAs per SM
-  static const int peer_ipt = getenv("HJ_PEER_IPT") ? atoi(getenv("HJ_PEER_IPT")) : 32;
+  const int peer_ipt = env().peer_ipt;
   const u32 tile = kScThreads * (peer_ipt == 16 ? 16 : 32);
   const u64 ntiles = (n + tile - 1) / tile;
   const u64 one[4] = {0, n, 0, ntiles};  // the one-parent view: offsets {0, n}, tiles {0, ntiles}
   CK(cudaMemcpyAsync(rb.one.p, one, sizeof(one), cudaMemcpyHostToDevice, h->stream));
   CK(cudaMemcpyAsync(h->peer_ptrs.p, peer_bufs, n_dest * sizeof(u64*), cudaMemcpyHostToDevice, h->stream));
   // runs leave through bulk async copies (TMA) unless HJ_PEER_NO_BULK is set (then: 8-byte stores)
-  const bool bulk = !getenv("HJ_PEER_NO_BULK") && (F % 2 == 0);
+  const bool bulk = !env().peer_no_bulk && (F % 2 == 0);
   if (reg && !bulk) return HJ_EINVAL;
   auto k = reg              ? rx_scatter_kernel<32, 2, true, 1, true>
            : peer_ipt == 16 ? rx_scatter_kernel<16, 2, true, 0, true>
@@ -1587,7 +1709,7 @@ static int peer_scatter_impl(hj_handle* h, const uint64_t* in, uint64_t n, uint3
   size_t smem = (size_t)tile * 8 + (size_t)F * 16 + (bulk ? sc_bulk_extra(F) : 0);
   CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int grid = grid_for(h, (const void*)k, kScThreads, smem);
-  if (getenv("HJ_PEER_CTAS")) grid = h->sm_count * atoi(getenv("HJ_PEER_CTAS"));
+  if (env().peer_ctas > 0) grid = h->sm_count * env().peer_ctas;
   if (max_ctas && (u32)grid > max_ctas) grid = (int)max_ctas;
   if ((u64)grid > ntiles) grid = (int)(ntiles ? ntiles : 1);
   k<<<grid, kScThreads, smem, h->stream>>>((const u64*)in, nullptr, dg, F, 1, rb.one.p, rb.one.p + 2, (u64*)cursors,
@@ -1605,6 +1727,7 @@ static int peer_scatter_impl(hj_handle* h, const uint64_t* in, uint64_t n, uint3
 int hj_join_pass1(hj_handle* h, const uint64_t* R1, uint64_t n, const uint64_t* offR1, const uint64_t* S1,
                   uint64_t m, const uint64_t* offS1, hj_result* res) {
   if (!h || !R1 || !S1 || !is_device_ptr(R1) || !is_device_ptr(S1)) return HJ_EINVAL;
+  if (need_aligned16(h, R1, "hj_join_pass1(R1)") || need_aligned16(h, S1, "hj_join_pass1(S1)")) return HJ_EINVAL;
   CK(cudaSetDevice(h->device));
   if (res) memset(res, 0, sizeof(*res));
   reset_events(h);
@@ -1624,6 +1747,7 @@ int hj_join_regions(hj_handle* h, const uint64_t* R1, uint64_t n, const uint64_t
   if (!h || !R1 || !S1 || !curR || !curS || !n_src || !is_device_ptr(R1) || !is_device_ptr(S1) ||
       !is_device_ptr(curR) || !is_device_ptr(curS))
     return HJ_EINVAL;
+  if (need_aligned16(h, R1, "hj_join_regions(R1)") || need_aligned16(h, S1, "hj_join_regions(S1)")) return HJ_EINVAL;
   CK(cudaSetDevice(h->device));
   if (res) memset(res, 0, sizeof(*res));
   reset_events(h);

@@ -527,6 +527,28 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
   }
 }
 
+// One pass into more partitions than a shared-memory tile can hold a run for (2^13 .. 2^15 digits;
+// the reference builds NUM_RADIX_BITS=14, NUM_PASSES=1 with the plain scatter of
+// parallel_radix_join.c:622-626): the same loop, one global claim per tuple.  Equal digits inside a
+// warp (sorted or skewed inputs) are claimed together.
+__global__ void __launch_bounds__(256) rx_scatter_direct_kernel(const u64* __restrict__ in, u64 n,
+                                                                 u64* __restrict__ out, Digit dg,
+                                                                 u64* __restrict__ cursors) {
+  const u64 stride = (u64)gridDim.x * blockDim.x;
+  const u64 rounds = (n + stride - 1) / stride;  // all lanes stay in the loop: the claim is a warp collective
+  u64 i = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+  for (u64 r = 0; r < rounds; r++, i += stride) {
+    const u64 v = i < n ? ld_stream(in + i) : 0ull;
+    const u32 d = v ? digit_of(dg, v) : 0xffffffffu - lane_id();
+    const u32 peers = __match_any_sync(0xffffffffu, d);
+    const u32 leader = __ffs(peers) - 1;
+    u64 base = 0;
+    if (v && lane_id() == leader) base = atomicAdd(cursors + d, (u64)__popc(peers));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (v) out[base + __popc(peers & ((1u << lane_id()) - 1u))] = v;
+  }
+}
+
 // ---- optimistic (histogram-free) layout helpers -----------------------------------------------
 // cursors[q] = q * cap for q < count
 __global__ void __launch_bounds__(256) rx_opt_init_kernel(u64* __restrict__ a, u32 na, u64 capa, u64* __restrict__ b,

@@ -121,10 +121,22 @@ const char *hj_last_error(const hj_handle *h); /* last CUDA error text */
  * allocation happens inside a timed call (the reference allocates before its
  * timer too, AtomicHashBuild.hpp:25-34). */
 int hj_reserve(hj_handle *h, uint64_t max_r, uint64_t max_s);
+/* The same for the H2D staging buffers of HOST inputs (hj_reserve cannot know where the
+ * inputs will live): after both, a join of <= max_r / max_s host tuples allocates nothing. */
+int hj_reserve_staging(hj_handle *h, uint64_t max_r, uint64_t max_s);
+/* Device allocations the handle has made so far (a reserved handle must not add any in hj_join). */
+uint64_t hj_alloc_count(const hj_handle *h);
 
 /* ---- the hot path ------------------------------------------------------------
  * R / S may be host pointers (pageable or pinned; staged H2D inside the call)
- * or device pointers on cfg.device (used in place); detected per pointer. */
+ * or device pointers on cfg.device (used in place); detected per pointer.  The
+ * radix kernels read tuples in 16-byte pairs: a device pointer that is only
+ * 8-byte aligned (a slice starting at an odd tuple) is first copied to an
+ * aligned staging buffer by hj_join / hj_join_materialize; the global-table
+ * path reads 8 bytes at a time and takes any tuple-aligned pointer in place.
+ * The building-block entry points further down (hj_radix_partition, hj_peer_*,
+ * hj_join_pass1, hj_join_regions) require 16-byte aligned device pointers and
+ * return HJ_EINVAL otherwise. */
 
 /* AtomicHashBuild.hpp:37-67 / NoCCHashBuild.hpp:37-62: (re)build the global
  * table from R.  res may be NULL. */

@@ -1,0 +1,177 @@
+"""GPU tests added in round 2: the bitmap-claimed global table (edge cases of the claim runs,
+the home-only and the sector probe), misaligned device inputs, a reserved handle that allocates
+nothing, stale-table protection, 1-pass plans beyond 2^12, wide pass 1."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+# ---- global table: bitmap claims ---------------------------------------------------------------
+@pytest.mark.parametrize("tsize", [1, 2, 4, 16])
+@pytest.mark.parametrize("case", ["dups_adjacent", "dups_far", "two_homes_collide", "wrap", "all_same", "tiny"])
+def test_global_table_claim_edge_cases(hj, oracle, case, tsize):
+    """Inputs built to hit every branch of claim_slot / the loser ranking: duplicate keys in neighbouring
+    lanes (a run that asks for one bit twice), duplicates far apart (different warps), keys whose windows
+    overlap, homes at the very end of the table (wrap-around), one key repeated (everything overflows),
+    and a relation smaller than one warp."""
+    rng = np.random.default_rng(3)
+    if case == "dups_adjacent":
+        R = np.repeat(np.arange(1, 20001, dtype=np.uint64), 3)          # k k k, sorted
+    elif case == "dups_far":
+        R = np.tile(np.arange(1, 20001, dtype=np.uint64), 3)            # k ... k ... k
+    elif case == "two_homes_collide":
+        base = np.arange(1, 30001, dtype=np.uint64)
+        R = np.concatenate([base, base + np.uint64(1), base[::2]])      # windows overlap everywhere
+    elif case == "wrap":
+        n = 1 << 12                                                     # table = 2^13 slots
+        R = np.concatenate([np.full(7, (1 << 13) - 1, dtype=np.uint64), np.arange(1, n - 6, dtype=np.uint64)])
+    elif case == "all_same":
+        R = np.full(5000, 77, dtype=np.uint64)
+    else:
+        R = np.array([5, 5, 6, 900, 5], dtype=np.uint64)
+    R = R | (rng.integers(0, 1 << 20, R.size, dtype=np.uint64) << np.uint64(32))   # payloads: tuples differ
+    S = np.concatenate([np.arange(1, 40001, dtype=np.uint64), np.array([(1 << 13) - 1, 77, 5], dtype=np.uint64)])
+    want = oracle.true_join(R, S, 0xFFFFFFFF)
+    with hj.HashJoin("atomic", key_mask=0xFFFFFFFF, transaction_size=tsize) as h:
+        res = h.join(R, S)
+        assert (res.matches, res.checksum) == want
+        sums = h.checksums(R)
+        assert sums.table_sum + sums.overflow_sum == sums.input_sum == oracle.sum(R)   # no tuple lost
+        assert res.window_matches <= res.matches
+        if case == "all_same":
+            assert res.conflicts == R.size - 4            # a window of probeLength slots, the rest overflows
+        # the probe is idempotent and independent of S's order
+        p = h.probe(S[::-1].copy())
+        assert (p.matches, p.checksum) == want
+
+
+@pytest.mark.parametrize("probe_length", [1, 2, 3, 4, 7, 9, 33])
+def test_global_table_probe_lengths(hj, oracle, probe_length):
+    """--probeLength other than 4: windows of 1..33 slots (several sectors, several bitmap words)."""
+    n = 1 << 16
+    R = hj.generate_data("uniform", n, n // 4, 16)       # heavy duplication: long displacement chains
+    S = hj.generate_data("sorted", n // 4)
+    want = oracle.true_join(R, S)
+    with hj.HashJoin("atomic", probe_length=probe_length) as h:
+        res = h.join(R, S)
+        assert (res.matches, res.checksum) == want
+        sums = h.checksums(R)
+        assert sums.table_sum + sums.overflow_sum == sums.input_sum
+
+
+def test_home_only_probe_is_taken_and_exact(hj, oracle):
+    """Unique keys: the build displaces nothing (probe_steps == 0), the probe reads one slot per tuple.
+    Keys that differ only above the table mask must not match (same home, different key)."""
+    n = 1 << 18
+    R = hj.generate_data("shuffle", n)
+    with hj.HashJoin("atomic") as h:
+        b = h.build(R)
+        assert b.probe_steps == 0 and b.conflicts == 0
+        S = np.concatenate([hj.generate_data("sorted", n), R[:1000] + np.uint64(1 << 19)])  # same home, other key
+        p = h.probe(S)
+        assert (p.matches, p.checksum) == oracle.true_join(R, S) and p.matches == n
+        assert p.window_matches == n
+
+
+def test_nocc_and_atomic_agree_on_unique_keys(hj, oracle):
+    n = (1 << 18) + 3
+    R = hj.generate_data("local_shuffle", n, n, 256)
+    S = hj.generate_data("sorted", n)
+    want = oracle.true_join(R, S)
+    for algo in ("atomic", "nocc"):
+        with hj.HashJoin(algo) as h:
+            res = h.join(R, S)
+            assert (res.matches, res.checksum) == want
+            sums = h.checksums(R)
+            assert sums.table_sum == sums.input_sum and sums.overflow_sum == 0
+
+
+# ---- ADVICE round 1 -----------------------------------------------------------------------------
+@pytest.mark.parametrize("algo", ["radix", "adaptive", "atomic", "sortmerge"])
+def test_misaligned_device_inputs(hj, oracle, algo):
+    """Device pointers that are only 8-byte aligned (ptr + 8): hj_join re-stages them for the radix
+    kernels' 16-byte loads; the building blocks refuse them with HJ_EINVAL instead of faulting."""
+    n, m = (1 << 17) + 1, (1 << 18) + 1
+    R, S = hj.generate_data("shuffle", n), hj.generate_data("shuffle", m)
+    want = oracle.true_join(R[1:], S[1:])
+    with hj.HashJoin(algo) as h:
+        dR, dS = h.to_device(R), h.to_device(S)
+        res = h.join((dR[0] + 8, n - 1), (dS[0] + 8, m - 1))
+        assert (res.matches, res.checksum) == want
+        if algo == "radix":
+            d_out, d_off = h.device_alloc(n * 8), h.device_alloc(129 * 8)
+            with pytest.raises(hj.HJError) as e:
+                h.radix_partition(dR[0] + 8, n - 1, 0, 7, d_out, d_off)
+            assert e.value.code == hj.HJ_EINVAL and "16-byte" in str(e.value)
+            res = h.join((dR[0], n), (dS[0], m))          # the context is still healthy
+            assert (res.matches, res.checksum) == oracle.true_join(R, S)
+            h.device_free(d_out); h.device_free(d_off)
+        h.device_free(dR[0]); h.device_free(dS[0])
+
+
+@pytest.mark.parametrize("algo,kw", [("radix", {}), ("radix", dict(num_partitions=1 << 7, passes=1)), ("atomic", {}),
+                                     ("adaptive", {}), ("sortmerge", {})])
+def test_reserved_handle_allocates_nothing(hj, algo, kw):
+    """hj_reserve + hj_reserve_staging size what hj_join uses: no cudaMalloc inside the (timed) call."""
+    n, m = 1 << 18, 1 << 20
+    R, S = hj.mc_relation_pk(n), hj.mc_relation_fk(m, n)
+    with hj.HashJoin(algo, key_mask=0xFFFFFFFF, **kw) as h:
+        h.reserve(n, m)
+        h.reserve_staging(n, m)
+        before = h.alloc_count()
+        assert before > 0
+        res = h.join(R, S)
+        assert res.matches == m
+        assert h.alloc_count() == before, "hj_join allocated after hj_reserve"
+        dR, dS = h.to_device(R), h.to_device(S)
+        res = h.join(dR, dS)
+        assert res.matches == m and h.alloc_count() == before
+        h.device_free(dR[0]); h.device_free(dS[0])
+
+
+def test_stale_table_is_not_probed(hj, oracle):
+    """hj_build, then a radix call on the same handle (counters zeroed, maybe the table reused), then
+    hj_probe: must be refused, not silently wrong.  Same after hj_reserve grew the table."""
+    n = 1 << 16
+    R = hj.generate_data("uniform", n, n // 8, 16)
+    S = hj.generate_data("sorted", n // 8)
+    with hj.HashJoin("atomic") as h:
+        h.build(R)
+        p = h.probe(S)
+        assert (p.matches, p.checksum) == oracle.true_join(R, S)
+        _, pairs = h.join_materialize(R, S)
+        assert pairs == p.matches
+        with pytest.raises(hj.HJError) as e:
+            h.probe(S)
+        assert e.value.code == hj._capi.HJ_ESTATE
+        h.build(R)
+        h.reserve(8 * n)                       # a larger table: the old contents are gone
+        with pytest.raises(hj.HJError) as e:
+            h.probe(S)
+        assert e.value.code == hj._capi.HJ_ESTATE
+        h.build(R)
+        p = h.probe(S)
+        assert (p.matches, p.checksum) == oracle.true_join(R, S)
+
+
+# ---- BASELINE configs[2]: 1 pass up to 2^14, any split of two passes -----------------------------
+@pytest.mark.parametrize("bits,passes,b1", [(13, 1, 0), (14, 1, 0), (15, 1, 0), (13, 2, 9), (14, 2, 3), (15, 2, 12)])
+def test_radix_one_pass_beyond_4096_and_wide_pass1(hj, oracle, bits, passes, b1):
+    n, m = 1 << 17, (3 << 17) + 11
+    R = hj.mc_relation_pk(n)
+    S = hj.mc_relation_fk(m, n)
+    want = oracle.true_join(R, S, 0xFFFFFFFF)
+    with hj.HashJoin("radix", num_partitions=1 << bits, passes=passes, key_mask=0xFFFFFFFF, pass1_bits=b1) as h:
+        res = h.join(R, S)
+        assert (res.matches, res.checksum) == want
+        assert (res.radix_bits, res.passes) == (bits, passes)
+    if passes == 1:   # PRO build-only checksum (closed form) through the direct scatter
+        assert hj.PRO(R, None, radix_bits=bits, passes=1) == (n // 2) * (n // (1 << bits) - 1)
+
+
+def test_pass1_bits_out_of_range_is_einval(hj):
+    with hj.HashJoin("radix", num_partitions=1 << 14, passes=2, pass1_bits=13) as h:
+        with pytest.raises(hj.HJError) as e:
+            h.join(hj.mc_relation_pk(1 << 12), hj.mc_relation_pk(1 << 12))
+        assert e.value.code == hj.HJ_EINVAL

@@ -2,7 +2,7 @@
 """Small fixed workload for ncu captures: two identical joins (the first is warm-up).
 
   python tools/profile_join.py radix   # |R|=2^25 PK, |S|=2^28 FK, 2^11 partitions in 2 passes (C3's partition size)
-  python tools/profile_join.py global  # atomic table, |R|=|S|=2^24, uniform then sorted
+  python tools/profile_join.py global [log_n]  # atomic table, |R|=|S|=2^log_n (24), uniform, sorted, local_shuffle 256
   python tools/profile_join.py mat     # hj_join_materialize on the radix workload (count / scan / write kernels)
 """
 import sys
@@ -35,10 +35,10 @@ elif what == "mat":
             assert r.matches == m == pairs
             print({k: round(v, 1) for k, v in r.as_dict().items() if k.startswith("us_") and v})
 else:
-    n = 1 << 24
+    n = 1 << (int(sys.argv[2]) if len(sys.argv) > 2 else 24)
     S = hj.generate_data("sorted", n)
-    for dist in ("uniform", "sorted"):
-        R = hj.generate_data(dist, n)
+    for dist in ("uniform", "sorted", "local_shuffle"):
+        R = hj.generate_data(dist, n, n, 256 if dist == "local_shuffle" else 16)
         with hj.HashJoin("atomic") as h:
             dR, dS = h.to_device(R), h.to_device(S)
             for _ in range(2):

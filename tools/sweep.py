@@ -39,6 +39,10 @@ def med(h, dR, dS, reps=5, warm=2):
 def emit(tag, n_tuples, o):
     us = o["us_total"]
     o2 = {"tag": tag, "Mtuples/s": round(n_tuples / us, 1), "roofline_frac": round(o["hbm_bytes"] / (us * 1e-6) / (PEAK * 1e9), 4)}
+    if o.get("path_taken") == 1 and o.get("us_build", 0) + o.get("us_probe", 0) > 0:
+        bp = o["us_build"] + o["us_probe"]  # the reference's timed region: build + probe, table zeroed before
+        o2["us_build+probe"] = round(bp, 1)
+        o2["roofline_frac_build+probe"] = round(o["hbm_bytes"] / (bp * 1e-6) / (PEAK * 1e9), 4)
     o2.update({k: (round(v, 1) if isinstance(v, float) else v) for k, v in o.items() if not (k.startswith("us_") and v == 0)})
     print(json.dumps(o2), flush=True)
 
