@@ -50,7 +50,8 @@ def parse_args():
     ap.add_argument("--peer-ctas", type=int, default=48, help="CTAs of an overlapped peer scatter (NVLink-bound)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--extras", action="store_true", help="also time configs[0] (atomic 16M uniform) etc.")
+    ap.add_argument("--no-global-table", action="store_true", help="skip the global_table key (BASELINE configs[0]/[1])")
+    ap.add_argument("--cpu-also-log-n", type=int, default=27, help="log2 |R| of the cpu_baseline.also runs (atomic / nocc / PRO)")
     return ap.parse_args()
 
 
@@ -112,82 +113,142 @@ class ClockSampler:
 # reference arm / cpu_baseline: the reference's own CPU code from oracle/_ref
 # (the only place besides tests/ and smoke() that may execute oracle/)
 # =============================================================================
-def _mc_run(exe, algo, nthreads, r, s, timeout=600):
-    out = subprocess.run([exe, f"--algo={algo}", f"--nthreads={nthreads}", f"--r-size={r}", f"--s-size={s}"],
-                         capture_output=True, text=True, timeout=timeout)
-    lines = (out.stdout + "\n" + out.stderr).splitlines()
-    usecs = result = None
+def _mc_bench(algo, nthreads, r, s, reps, warmup, timeout=1700):
+    """oracle/_ref/mc_bench_b14_p2 (oracle/ref_bench.c around the reference's unmodified mc/src): relations
+    generated ONCE with the reference's generators and seeds, the entry point called warmup + reps times.
+    Returns (list of the callee's own TOTAL-TIME-USECS of the timed calls, list of results, generation seconds)."""
+    exe = os.path.join(ROOT, "oracle", "_ref", "mc_bench_b14_p2")
+    out = subprocess.run([exe, f"--algo={algo}", f"--nthreads={nthreads}", f"--r-size={r}", f"--s-size={s}",
+                          f"--reps={reps}", f"--warmup={warmup}"], capture_output=True, text=True, timeout=timeout)
+    if out.returncode != 0:
+        raise RuntimeError("mc_bench failed: " + (out.stdout + out.stderr)[-400:])
+    # the callee prints half of its timing block to stderr (no_partitioning_join.c:322-330): parse stdout only
+    lines = out.stdout.splitlines()
+    usecs, results, gen_s, last = [], [], None, None
     for i, l in enumerate(lines):
+        if l.startswith("GENERATED"):
+            gen_s = float(l.split("GEN_US")[1]) / 1e6
         if l.startswith("TOTAL-TIME-USECS") and i + 1 < len(lines):
-            usecs = float(lines[i + 1].split()[0])
-        if "Results =" in l:
-            result = int(l.split("=")[1].split(".")[0])
-    if usecs is None:
-        raise RuntimeError("mc output not understood: " + "\n".join(lines[-8:]))
-    return usecs, result
+            last = float(lines[i + 1].split()[0])
+        if l.startswith("RUN "):
+            f = l.split()
+            if f[-1] == "TIMED":
+                usecs.append(last)
+                results.append(int(f[5]))
+    if not usecs:
+        raise RuntimeError("mc_bench output not understood: " + "\n".join(lines[-8:]))
+    return usecs, results, gen_s
+
+
+def host_desc():
+    model = "unknown CPU"
+    try:
+        for l in open("/proc/cpuinfo"):
+            if l.startswith("model name"):
+                model = l.split(":", 1)[1].strip()
+                break
+    except OSError:
+        pass
+    return model
+
+
+def mem_available_gib():
+    try:
+        for l in open("/proc/meminfo"):
+            if l.startswith("MemAvailable"):
+                return int(l.split()[1]) / (1 << 20)
+    except OSError:
+        pass
+    return 0.0
 
 
 def cpu_reference_join(log_r, log_s, steps, warmup):
-    """mc NPO (no_partitioning_join.c:537), the reference's complete build+probe with an FK
-    S, all host threads, on a bounded sample with the workload's |S|/|R| ratio.  Returns
-    (Mtuples/s, descriptor)."""
-    exe = os.path.join(ROOT, "oracle", "_ref", "mc_b14_p2")
+    """mc NPO (no_partitioning_join.c:537), the reference's complete build+probe with an FK S, on all host
+    threads.  Returns (Mtuples/s, descriptor, median us); (None, descriptor, None) when oracle/_ref is absent."""
+    exe = os.path.join(ROOT, "oracle", "_ref", "mc_bench_b14_p2")
     cores = os.cpu_count() or 1
     if not os.path.exists(exe):
-        return None, {"kind": "reference", "cores": cores, "sample": "oracle/_ref not built"}
+        return None, {"kind": "reference", "cores": cores, "sample": "oracle/_ref not built"}, None
     r, s = 1 << log_r, 1 << log_s
-    times = []
-    for i in range(warmup + steps):
-        us, result = _mc_run(exe, "NPO", cores, r, s)
-        assert result == s, f"reference NPO returned {result}, expected {s}"
-        if i >= warmup:
-            times.append(us)
-    med = float(np.median(times))
-    desc = {"kind": "reference", "cores": cores,
+    usecs, results, gen_s = _mc_bench("NPO", cores, r, s, steps, warmup)
+    assert all(x == s for x in results), f"reference NPO returned {results}, expected {s}"
+    med = float(np.median(usecs))
+    desc = {"kind": "reference", "cores": cores, "cpu": host_desc(),
             "sample": f"mc NPO build+probe (latched bucket chaining, {cores} pthreads), |R|=2^{log_r} PK, "
-                      f"|S|=2^{log_s} FK, median of {steps} runs after {warmup} warm-ups; the reference's "
-                      f"PRO never probes S (parallel_radix_join.c:262-276) so NPO is its only complete FK join"}
+                      f"|S|=2^{log_s} FK from the reference's generators (seeds 12345/54321, generated once in "
+                      f"{gen_s:.0f} s), median of {steps} calls after {warmup} warm-up calls in one process "
+                      f"(oracle/ref_bench.c); the reference's PRO never probes S (parallel_radix_join.c:262-276) "
+                      f"so NPO is its only complete FK join",
+            "runs_us": [round(x) for x in usecs]}
     return (r + s) / med, desc, med
 
 
-def cpu_reference_extras():
-    """Other reference CPU paths on bounded samples (informational)."""
-    extra = {}
+def cpu_reference_extras(log_n=27, reps=5):
+    """The reference's other CPU paths (north_star: atomic, nocc, PRJ) on the host cores: AtomicHashBuild /
+    NoCCHashBuild compiled unmodified (build+probe, S = sorted 1..n as main.cpp:93), sorted and fully shuffled
+    R, and PRO 14 bits / 2 passes (partition + build of R only, as the reference measured it).  BASELINE.md
+    section 2.4: `reps` repetitions, median."""
+    extra = {"n": f"2^{log_n}", "reps": reps, "cores": os.cpu_count() or 1, "cpu": host_desc()}
     cores = os.cpu_count() or 1
+    n = 1 << log_n
     try:
-        exe = os.path.join(ROOT, "oracle", "_ref", "mc_b14_p2")
-        us, _ = _mc_run(exe, "PRO", cores, 1 << 24, 2)
-        extra["PRO_partition+build_R_only_2^24_Mtuples/s"] = round((1 << 24) / us, 1)
+        usecs, _, _ = _mc_bench("PRO", cores, n, 2, reps, 1)
+        extra["PRO_b14_p2_partition+build_R_only_Mtuples/s"] = round(n / float(np.median(usecs)), 1)
     except Exception as e:  # noqa: BLE001
-        extra["PRO_error"] = str(e)[:80]
+        extra["PRO_error"] = str(e)[:120]
     try:
         from tests.oracle_lib import Reference
+        import htm_hashjoin_b200 as hj
         ref = Reference(probe=True)
         if ref.available:
-            n = 1 << 24
-            R = ref.generate_data("uniform", n, n, 16)
-            S = ref.generate_data("sorted", n, n, 16)
-            for algo in ("atomic", "nocc"):
-                j = ref.hash_build(algo, R, S, num_partitions=max(64, cores))
-                extra[f"{algo}_build+probe_uniform_2^24_Mtuples/s"] = round(2 * n / j["hashBuildTimeInMicroseconds"], 1)
-            extra["htm"] = "not run: host CPU has no rtm flag" if "rtm" not in open("/proc/cpuinfo").read() else "rtm present"
+            S = hj.generate_data("sorted", n, n, 16)
+            for dist in ("sorted", "shuffle"):
+                R = hj.generate_data(dist, n, n, 16)
+                for algo in ("atomic", "nocc"):
+                    ts = []
+                    for _ in range(reps):
+                        j = ref.hash_build(algo, R, S, num_partitions=max(64, cores))
+                        assert j["totalMatches"] == n
+                        ts.append(j["hashBuildTimeInMicroseconds"])
+                    extra[f"{algo}_build+probe_{dist}_Mtuples/s"] = round(2 * n / float(np.median(ts)), 1)
+                del R
+            extra["scheduler"] = "tbb/tbb.h stand-in (oracle/tbb_shim: one std::thread per hardware thread), TBB is not installed"
+        extra["htm"] = ("not run: host CPU has no rtm flag" if " rtm" not in open("/proc/cpuinfo").read()
+                        else "rtm present (HTMHashBuild.hpp's probe does not compile: not timed)")
     except Exception as e:  # noqa: BLE001
-        extra["atomic_error"] = str(e)[:80]
+        extra["atomic_error"] = str(e)[:120]
     return extra
 
 
 def run_reference(args):
+    """--impl reference: the reference's own CPU join on the bench's config (2^27 PK x 2^30 FK per GPU unless
+    --log-r/--log-s say otherwise), all host threads.  A step = one NPO call on relations generated once."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    log_r, log_s = min(args.log_r, 24), min(args.log_s, 27)
+    log_r, log_s = args.log_r, args.log_s
+    same = True
+    need_gib = (8.0 * ((1 << log_r) + (1 << log_s)) + 32.0 * (1 << log_r)) / (1 << 30) + 2
+    avail = mem_available_gib()
+    while avail and need_gib > 0.8 * avail and log_s > 20:  # BASELINE.md 2.5: only if host RAM allows
+        log_r, log_s, same = log_r - 1, log_s - 1, False
+        need_gib = (8.0 * ((1 << log_r) + (1 << log_s)) + 32.0 * (1 << log_r)) / (1 << 30) + 2
+    if log_r > 30 or log_s > 30:  # the reference's sizes are int32_t (mc/src/generator.h)
+        log_r, log_s, same = min(log_r, 27), min(log_s, 30), False
     t0 = time.time()
     val, desc, med_us = cpu_reference_join(log_r, log_s, args.steps, args.warmup)
+    if val is None:
+        print(json.dumps({"impl": "reference", "unavailable": desc["sample"]}))
+        return 0
     line = {
         "impl": "reference", "metric": METRIC, "value": round(val, 2), "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(med_us / 1000.0, 3),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-        "config": {"workload": "radix join |R|=2^27 PK x |S|=2^30 FK per GPU (BASELINE configs[2]; configs[4] at 8 GPUs)",
+        "config": {"workload": f"join |R|=2^{log_r} PK x |S|=2^{log_s} FK "
+                               + ("(BASELINE configs[2], the per-GPU workload of the B200 arm)" if same else
+                                  f"(REDUCED from 2^{args.log_r} x 2^{args.log_s}: host RAM {avail:.0f} GiB / int32 sizes)"),
+                   "same_config_as_b200_arm": same,
+                   "note": "one host runs ONE GPU's share of the weak-scaling workload; at N GPUs the B200 arm joins N times as much",
                    "reference_sample": desc["sample"]},
         "cpu_baseline": dict(desc, value=round(val, 2), unit=UNIT),
         "e2e": {"value": round(val, 2), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -300,7 +361,11 @@ class Rank:
             self.recvS = torch.empty(cap_s, dtype=torch.int64, device=dev)
             self.offR = torch.empty(G + 1, dtype=torch.int64, device=dev)
             self.offS = torch.empty(G + 1, dtype=torch.int64, device=dev)
-        self.h.reserve(self.n + self.n // 16 + 65536, self.m + self.m // 16 + 65536)
+        if G == 1:
+            self.h.reserve(self.n, self.m)
+            self.h.reserve_staging(self.n, self.m)
+        else:
+            self.h.reserve(self.n + self.n // 16 + 65536, self.m + self.m // 16 + 65536)
         self.last = None
         self.launches = 0
         self.nvlink_bytes = 0
@@ -517,28 +582,45 @@ class Rank:
         return ms, {k: v / steps for k, v in phases.items()}
 
 
-def global_table_extras(rk):
-    """BASELINE configs[0]/[1] on the global table, device resident (informational keys)."""
+# ncu --set full, profiles/r02_ncu_global_*: DRAM bytes per tuple of the two kernels (read + write) -- filled from the
+# committed captures; None = not captured for that input
+GT_TRAFFIC = {}
+
+
+def global_table_lines(rk, reps=5, warm=2):
+    """BASELINE configs[0] / [1] on the global table (north_star's first subsystem), device resident:
+    C1 = --algo atomic --rSize 16M --dataDistr uniform; sorted and local_shuffle W=2^8 at |R|=|S|=2^27.
+    Time = build + probe (the reference's timed region, AtomicHashBuild.hpp:34-88: the table is zeroed
+    before the timer there too); algorithmic bytes 16 B per R tuple + 16 B per S tuple."""
     hj = rk.hj
     peak, _ = load_peaks()
     out = {}
-    n = 1 << 24
-    S = hj.generate_data("sorted", n)
-    for name, dist, rng in (("c1_atomic_uniform_16M", "uniform", 16), ("c2_atomic_sorted_16M", "sorted", 16),
-                            ("c2_atomic_shuffle_16M", "shuffle", 16)):
+    for name, dist, rng, log_n in (("c1_atomic_uniform_16M", "uniform", 16, 24),
+                                   ("c2_atomic_sorted_2^27", "sorted", 16, 27),
+                                   ("c2_atomic_local_shuffle_W256_2^27", "local_shuffle", 256, 27)):
+        n = 1 << log_n
         R = hj.generate_data(dist, n, n, rng)
         with hj.HashJoin("atomic", device=rk.local) as h:
-            dR, dS = h.to_device(R), h.to_device(S)
-            ts = []
-            for i in range(6):
-                r = h.join(dR, dS)
-                if i >= 2:
-                    ts.append(r.us_build + r.us_probe)
-            us = float(np.median(ts))
-            out[name] = {"Mtuples/s": round(2 * n / us, 1), "us_build+probe": round(us, 1),
-                         "roofline_frac": round(32.0 * n / (us * 1e-6) / (peak * 1e9), 4),
-                         "conflicts": int(r.conflicts), "matches": int(r.matches)}
-            h.device_free(dR[0]); h.device_free(dS[0])
+            dR = h.to_device(R)
+            del R
+            dS = h.device_alloc(n * 8)
+            h.generate(0, 0, n, 1, 0, dS)  # S = sorted 1..n (main.cpp:93)
+            h.reserve(n, n)
+            rows = []
+            for i in range(reps + warm):
+                r = h.join(dR, (dS, n))
+                assert r.matches == n, (name, r.matches)
+                if i >= warm:
+                    rows.append((r.us_build, r.us_probe, r.us_clear))
+            ub, up, uc = (float(np.median([x[k] for x in rows])) for k in range(3))
+            us = ub + up
+            b = 32.0 * n
+            out[name] = {"Mtuples/s": round(2 * n / us, 1), "us_build": round(ub, 1), "us_probe": round(up, 1),
+                         "us_table_clear_untimed": round(uc, 1), "algorithmic_bytes": int(b),
+                         "achieved_GBs": round(b / (us * 1e-6) / 1e9, 1), "frac": round(b / (us * 1e-6) / 1e9 / peak, 4),
+                         "traffic": GT_TRAFFIC.get(name), "conflicts": int(r.conflicts), "matches": int(r.matches),
+                         "launches_per_join": int(r.kernel_launches)}
+            h.device_free(dR[0]); h.device_free(dS)
     return out
 
 
@@ -634,12 +716,22 @@ def run_b200(args):
             if rk.chunks == 1:
                 line["nvlink_gbs_in_peer_scatter"] = round(nvl / (rk.fused_ms[sc] * 1e-3) / 1e9, 1)
             line["region_fallbacks"] = getattr(rk, "region_fallbacks", 0)
+    if G == 1 and not args.no_global_table:
+        try:
+            rk.h.close()  # its 28 GiB of radix buffers are not needed any more
+            line["global_table"] = global_table_lines(rk)
+        except Exception as e:  # noqa: BLE001  (the headline line is printed no matter what)
+            line["global_table"] = {"error": str(e)[:200]}
     if G == 1 and not args.no_cpu_baseline:
-        v, desc, _ = cpu_reference_join(24, 27, 1, 1)
-        line["cpu_baseline"] = dict(desc, value=round(v, 2), unit=UNIT)
-        line["cpu_baseline"]["also"] = cpu_reference_extras()
-    if G == 1 and args.extras:
-        line["global_table"] = global_table_extras(rk)
+        try:
+            # bounded sample (1/8 of the workload, same |S|/|R|); `--impl reference` runs the full config
+            v, desc, _ = cpu_reference_join(24, 27, 3, 1)
+            line["cpu_baseline"] = dict(desc, value=None if v is None else round(v, 2), unit=UNIT)
+            if v is not None:
+                line["cpu_baseline"]["also"] = cpu_reference_extras(args.cpu_also_log_n)
+        except Exception as e:  # noqa: BLE001
+            line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "reference",
+                                    "sample": "failed: " + str(e)[:200]}
     print(json.dumps(line))
     return 0
 

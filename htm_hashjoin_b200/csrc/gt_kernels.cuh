@@ -18,26 +18,34 @@
 // B200 shape of the insert (round 2).  The reference's compare_exchange (:47-58)
 // needs the slot's old value, so a CAS on the table itself drags every 32-byte
 // sector of the (DRAM-resident, 2 GiB at |R| = 2^27) table through L2 before it
-// is written: 24 B of DRAM traffic per tuple for 16 algorithmic, and one L2
-// atomic per 8 bytes.  Here the atomic is taken on a CLAIM BITMAP instead -- one
-// bit per slot, slots/8 bytes, 32 MB at 2^27: L2-resident -- and the tuple is then
-// written with a plain store:
-//   * the claim of a warp's load instruction is warp-cooperative: lanes whose
-//     slots fall into the same 32-slot word (every lane of a sorted or locally
-//     shuffled relation) are found with one shuffle + ballot, their bits are
-//     OR-reduced (REDUX) and ONE atomicOr per word claims them all; its return
-//     value tells every lane whether its bit was free;
-//   * a lane that lost sees the word's whole occupancy and goes straight to the
-//     next free slot of its window instead of stepping one CAS round trip at a
-//     time;
-//   * the stores of a warp to consecutive slots leave as full sectors, so the
-//     table is written without ever being read: 16 B/tuple of DRAM traffic.
+// is written -- 24 B of DRAM traffic per tuple for 16 algorithmic -- and costs one
+// L2 atomic per 8 bytes: round 1's kernel ran at the SM's ATOMG issue rate
+// (139 G atomics/s), not at HBM speed.  Here the atomic is taken on a CLAIM BITMAP
+// instead -- one bit per slot, slots/8 bytes, 32 MB at 2^27: L2-resident -- and the
+// tuple is then written with a plain store.  The claims of a CTA tile are
+// write-combined in shared memory, the way rx_scatter combines its output runs:
+//   * the tile's tuples set their bits in a shared-memory copy of the band of the
+//     bitmap the tile touches (home slots of a sorted / locally shuffled tile lie
+//     within tile + 2W slots of each other); a bit that is already set there is a
+//     duplicate request inside the tile and loses at once;
+//   * ONE global atomicOr per non-empty 32-slot word claims everything the tile
+//     wants in it -- 65 atomics for 2048 sorted tuples instead of 2048 -- and its
+//     return value tells every requester whether its bit was free;
+//   * a tuple that lost sees the word's whole occupancy and goes straight to the
+//     next free slot of its window instead of stepping one round trip at a time;
+//   * tuples whose slot lies outside the band (fully shuffled inputs) claim their
+//     bit with an atomic of their own, all of a thread's in flight together;
+//   * winners store their tuple: the stores of a tile to neighbouring slots meet
+//     in L2 and leave as full sectors, so the table is written without ever being
+//     read -- 16 B/tuple of DRAM traffic.
 #pragma once
 #include "hj_common.cuh"
 
 namespace hj {
 
 constexpr int kGtThreads = 256;
+constexpr int kGtBandWords = 1024;                 // shared-memory band of the claim bitmap: 32768 slots
+constexpr u64 kGtBand = 32ull * kGtBandWords;
 
 // Which tuples a launch covers: nslices segments of seg_len tuples, segment s
 // starting at s*slice_stride + slice_off (the 64 work slices of
@@ -56,50 +64,26 @@ __device__ __forceinline__ u32 ld_relaxed_u32(const u32* p) {
   return r;
 }
 
-// Warp-cooperative claim of one slot per lane in the claim bitmap.  Lanes whose slots share a
-// 32-slot word AND sit in consecutive lanes (a run) are served by one atomicOr from the run's
-// first lane; a run whose members ask for the same bit twice (duplicate keys), and every lane
-// that is alone with its word, claims for itself.  Aggregation is an optimisation only: any
-// grouping gives the same table.  `view` = occupancy of the word right after the attempt.
-// Must be called by all 32 lanes (want = false: nothing to claim).
-__device__ __forceinline__ bool claim_slot(u32* __restrict__ claim, u64 slot, bool want, u32& view) {
-  const u32 lane = lane_id();
-  const u32 word = want ? (u32)(slot >> 5) : 0xffffffffu - lane;  // dummies never form a run
-  const u32 req = want ? 1u << ((u32)slot & 31u) : 0u;
-  const u32 prev = __shfl_up_sync(0xffffffffu, word, 1);
-  const u32 heads = __ballot_sync(0xffffffffu, lane == 0 || word != prev);
-  const u32 le = 0xffffffffu >> (31u - lane);              // lanes <= mine
-  const u32 start = 31u - __clz(heads & le);               // first lane of my run
-  const u32 above = heads & ~le;
-  const u32 end = above ? __ffs(above) - 1u : 32u;         // one past its last lane
-  const u32 peers = (end == 32u ? 0xffffffffu : (1u << end) - 1u) & ~((1u << start) - 1u);
-  const u32 ormask = __reduce_or_sync(peers, req);
-  u32 old;
-  if (__popc(ormask) == __popc(peers)) {  // uniform over the run: every member wants its own bit
-    old = 0;
-    if (lane == start) old = atomicOr(claim + word, ormask);
-    old = __shfl_sync(peers, old, start);
-    view = old | ormask;  // (a run of this kind has no dummy lanes)
-  } else if (want) {
-    old = atomicOr(claim + word, req);
-    view = old | req;
-  } else {
-    old = 0xffffffffu;  // `view` stays what the caller had (the sampling round's peek)
-  }
-  return want && !(old & req);
-}
-
 // IPT tuples per thread ("transaction size": how many inserts a thread has in
-// flight before it looks at any outcome), loaded as IPT coalesced 8-byte loads so
-// that consecutive lanes hold consecutive tuples (the claim runs above).
-// STATS: the sampling round of the adaptive switch -- peeks at the word before
+// flight before it looks at any outcome), loaded as IPT coalesced 8-byte loads.
+// STATS: the sampling round of the adaptive switch -- peeks at the bitmap before
 // claiming (only a load-then-claim can tell a lost race from an old occupant).
+//
+// A tuple is "in band" when its whole window [home, home + L + 32) lies inside the tile's band and
+// below the table end (no wrap-around): then every attempt it ever makes goes through shared memory
+// and its position is one 32-bit offset.  Everything else ("far": fully shuffled inputs, the last
+// few slots of the table) claims with global atomics of its own.
+constexpr u32 kGtFar = 0xffffffffu;
+
 template <int IPT, bool STATS>
 __global__ void __launch_bounds__(kGtThreads, 4)
 gt_build_kernel(const u64* __restrict__ R, SegMap sm, u64* __restrict__ table, u32* __restrict__ claim, u64 mask,
                 u64 key_mask, u32 L, u64* __restrict__ ovf_list, u64* __restrict__ ctr) {
   constexpr int TILE = kGtThreads * IPT;
-  const u32 tid = threadIdx.x;
+  __shared__ u32 s_want[kGtBandWords];  // bits the tile asks for this round
+  __shared__ u32 s_old[kGtBandWords];   // what the global word held before the tile's atomicOr
+  __shared__ u64 s_min[kGtThreads / 32], s_max[kGtThreads / 32];
+  const u32 tid = threadIdx.x, lane = lane_id();
   const u64 chunks_per_seg = (sm.seg_len + TILE - 1) / TILE;
   const u64 nchunks = chunks_per_seg * sm.nslices;
   u32 retries = 0, steps = 0;
@@ -111,89 +95,155 @@ gt_build_kernel(const u64* __restrict__ R, SegMap sm, u64* __restrict__ table, u
     const u64 seg_begin = slice * sm.slice_stride + sm.slice_off;
     u64 seg_end = seg_begin + sm.seg_len;
     if (seg_end > sm.n) seg_end = sm.n;
-    const u64 base = seg_begin + w * TILE;
+    const u64 tbase = seg_begin + w * TILE;
 
     u64 v[IPT];
 #pragma unroll
     for (int j = 0; j < IPT; j++) {
-      const u64 i = base + (u64)j * kGtThreads + tid;
+      const u64 i = tbase + (u64)j * kGtThreads + tid;
       v[j] = i < seg_end ? ld_stream(R + i) : 0ull;
     }
 
-    if (STATS) {
-      // working-set signal: how wide is the band of table slots one CTA chunk touches?
-      __shared__ u64 smin[kGtThreads / 32], smax[kGtThreads / 32];
-      u64 lo = ~0ull, hi = 0ull;
+    // the band: 32768 slots starting at the tile's lowest home slot (rounded down to a bitmap word)
+    u64 lo = ~0ull, hi = 0ull;
 #pragma unroll
-      for (int j = 0; j < IPT; j++)
-        if (v[j]) {
-          const u64 hm = (v[j] & key_mask) & mask;
-          lo = hm < lo ? hm : lo;
-          hi = hm > hi ? hm : hi;
-        }
+    for (int j = 0; j < IPT; j++)
+      if (v[j]) {
+        const u64 hm = (v[j] & key_mask) & mask;
+        lo = hm < lo ? hm : lo;
+        if (STATS) hi = hm > hi ? hm : hi;
+      }
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
-        hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
-      }
-      if (lane_id() == 0) { smin[tid >> 5] = lo; smax[tid >> 5] = hi; }
-      __syncthreads();
-      if (tid == 0) {
-        for (int w2 = 1; w2 < kGtThreads / 32; w2++) { lo = min(lo, smin[w2]); hi = max(hi, smax[w2]); }
-        if (hi >= lo) { span += hi - lo + 1; chunks += 1; }
-      }
-      __syncthreads();
+    for (int o = 16; o > 0; o >>= 1) {
+      lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
+      if (STATS) hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
     }
+    if (lane == 0) { s_min[tid >> 5] = lo; if (STATS) s_max[tid >> 5] = hi; }
+    __syncthreads();
+#pragma unroll
+    for (int w2 = 0; w2 < kGtThreads / 32; w2++) lo = min(lo, s_min[w2]);
+    if (STATS && tid == 0) {
+      // working-set signal: how wide is the band of table slots one CTA chunk touches?
+      for (int w2 = 0; w2 < kGtThreads / 32; w2++) hi = max(hi, s_max[w2]);
+      if (hi >= lo) { span += hi - lo + 1; chunks += 1; }
+    }
+    const u64 base = lo & ~31ull;  // (an empty tile has lo = ~0: nothing is pending, no round runs)
+    u32* const gband = claim + (base >> 5);
 
+    u32 rel[IPT];  // home - base, or kGtFar
     u32 att[IPT];  // offset from home of the next slot to try
     u32 pend = 0;  // bit j: tuple j still has to be placed
+    u32 farbits = 0;
 #pragma unroll
     for (int j = 0; j < IPT; j++) {
       att[j] = 0;
-      if (v[j]) pend |= 1u << j;
+      rel[j] = kGtFar;
+      if (v[j]) {
+        pend |= 1u << j;
+        const u64 hm = (v[j] & key_mask) & mask;
+        const u64 r = hm - base;
+        if (r + L + 32 < kGtBand && hm + L + 32 <= mask) rel[j] = (u32)r;
+        else farbits |= 1u << j;
+      }
     }
     u32 failed_bits = 0;
 
-    // Rounds: every pending tuple of the batch makes its next attempt.  AtomicHashBuild.hpp:46-60
+    // Rounds: every pending tuple of the tile makes its next attempt.  AtomicHashBuild.hpp:46-60
     // with the claim bitmap standing in for the slot's old value.
-#pragma unroll 1
-    while (__any_sync(0xffffffffu, pend != 0)) {  // warp-uniform: the claim is a warp collective
+    while (__syncthreads_or(pend != 0)) {  // (also: everybody is done with s_want / s_old / s_min)
 #pragma unroll
-      for (int j = 0; j < IPT; j++) {
-        bool want = pend >> j & 1u;
-        if (!__any_sync(0xffffffffu, want)) continue;
-        const u64 slot = (((v[j] & key_mask) & mask) + att[j]) & mask;
-        u32 view = 0;
-        bool occupied = false;
-        if (STATS) {  // peek: an occupied slot costs a step, not a retry
-          if (want) {
-            view = ld_relaxed_u32(claim + (slot >> 5));
-            occupied = view >> ((u32)slot & 31u) & 1u;
+      for (int k = 0; k < kGtBandWords / kGtThreads; k++) s_want[k * kGtThreads + tid] = 0u;
+      __syncthreads();
+      u32 far_old[IPT];  // far tuples: what their own atomicOr (STATS: peek) returned
+      u32 pre = 0;       // bit j: lost before asking (duplicate request in the tile / STATS: seen occupied)
+      u32 peeked[IPT];
+      if (pend & farbits) {  // all of a thread's far claims in flight together
+#pragma unroll
+        for (int j = 0; j < IPT; j++) {
+          if (pend & farbits & (1u << j)) {
+            const u64 slot = (((v[j] & key_mask) & mask) + att[j]) & mask;
+            const u32 bit = 1u << ((u32)slot & 31u);
+            if (STATS) {
+              far_old[j] = ld_relaxed_u32(claim + (slot >> 5));
+              if (far_old[j] & bit) { pre |= 1u << j; continue; }
+            }
+            far_old[j] = atomicOr(claim + (slot >> 5), bit);
           }
         }
-        const bool won = claim_slot(claim, slot, want && !occupied, view);
-        if (STATS && want && !occupied && !won) ++retries;  // free when looked at, taken when claimed
-        if (won) {
-          table[slot] = v[j];
-          pend &= ~(1u << j);
-          want = false;
+      }
+#pragma unroll
+      for (int j = 0; j < IPT; j++) {
+        // warp-uniform: the aggregation below is a warp collective
+        const bool inb = (pend & ~farbits) >> j & 1u;
+        if (!__any_sync(0xffffffffu, inb)) continue;
+        const u32 cur = rel[j] + att[j];
+        const u32 bit = 1u << (cur & 31u);
+        bool ask = inb;
+        if (STATS && inb) {  // peek: an occupied slot costs a step, not a retry
+          peeked[j] = ld_relaxed_u32(gband + (cur >> 5));
+          if (peeked[j] & bit) { pre |= 1u << j; ask = false; }
         }
-        // losers: tuples of one load instruction that lost the SAME slot (duplicate keys sit next to
-        // each other in sorted / locally shuffled inputs) would chase each other down the window one
-        // round at a time; rank them and let rank r take the (r+1)-th free slot above.  The lower
-        // ranks take the slots in between, so the probe's walk from home never meets a gap.
-        if (__any_sync(0xffffffffu, want)) {
-          // same home AND same attempt count: the same slot with the same budget left -- what the
-          // lower ranks skip to, they also reach (or they overflow, and then so does every higher rank)
-          const u32 same = __match_any_sync(
-              0xffffffffu, want ? ((((v[j] & key_mask) & mask) << 11) | att[j]) : ~0ull - lane_id());
-          if (want) {
+        // Lanes of a run (consecutive lanes, same bitmap word: every lane of a sorted or locally shuffled
+        // relation) OR their bits together and the run's first lane sets them with ONE shared-memory atomic
+        // (32 lanes on one word would serialise 32-fold).  A run that asks for a bit twice (duplicate keys)
+        // falls back to one atomic per lane: its return value is what tells the duplicates apart.
+        const u32 word = ask ? cur >> 5 : kGtFar - lane;  // dummies never form a run
+        const u32 prevw = __shfl_up_sync(0xffffffffu, word, 1);
+        const u32 heads = __ballot_sync(0xffffffffu, lane == 0 || word != prevw);
+        const u32 le = 0xffffffffu >> (31u - lane);
+        const u32 start = 31u - __clz(heads & le);
+        const u32 above = heads & ~le;
+        const u32 end = above ? __ffs(above) - 1u : 32u;
+        const u32 peers = (end == 32u ? 0xffffffffu : (1u << end) - 1u) & ~((1u << start) - 1u);
+        const u32 ormask = __reduce_or_sync(peers, ask ? bit : 0u);
+        u32 prev = 0;
+        if (__popc(ormask) == __popc(peers)) {  // uniform over the run
+          if (lane == start) prev = atomicOr(&s_want[word], ormask);
+          prev = __shfl_sync(peers, prev, start);
+        } else if (ask) {
+          prev = atomicOr(&s_want[word], bit);
+        }
+        if (ask && (prev & bit)) pre |= 1u << j;  // somebody in the tile asked first
+      }
+      __syncthreads();
+      // one global atomic per non-empty word of the band
+#pragma unroll
+      for (int k = 0; k < kGtBandWords / kGtThreads; k++) {
+        const u32 wi = k * kGtThreads + tid;
+        const u32 want = s_want[wi];
+        if (want) s_old[wi] = atomicOr(gband + wi, want);
+      }
+      __syncthreads();
+#pragma unroll
+      for (int j = 0; j < IPT; j++) {
+        if (pend >> j & 1u) {
+          u32 b, view;
+          bool won;
+          if (farbits >> j & 1u) {
+            const u64 slot = (((v[j] & key_mask) & mask) + att[j]) & mask;
+            b = (u32)slot & 31u;
+            view = far_old[j] | (1u << b);
+            won = !(pre >> j & 1u) && !(far_old[j] >> b & 1u);
+          } else {
+            const u32 cur = rel[j] + att[j];
+            const u32 wi = cur >> 5;
+            b = cur & 31u;
+            const u32 want = s_want[wi];
+            const u32 old = want ? s_old[wi] : 0u;  // (STATS: a word nobody asked for was never claimed this round)
+            view = old | want | (STATS ? peeked[j] : 0u);
+            won = !(pre >> j & 1u) && !(old >> b & 1u);
+          }
+          if (STATS && !(pre >> j & 1u) && !won) ++retries;  // free when looked at, taken when claimed
+          if (won) {
+            table[(((v[j] & key_mask) & mask) + att[j]) & mask] = v[j];
+            pend &= ~(1u << j);
+          } else {
+            // on to the next slot the view shows free; none left in this word: the next word's first slot.
+            // Everything skipped is occupied (or asked for by this tile, hence occupied when the round ends),
+            // so the probe's walk from the home slot never meets a gap before the tuple.
             ++steps;
-            const u32 b = (u32)slot & 31u;
-            u32 freeb = b == 31u ? 0u : (~view & (0xffffffffu << (b + 1u)));
-            u32 r = __popc(same & ((1u << lane_id()) - 1u));
-            while (r && freeb) { freeb &= freeb - 1u; --r; }
-            att[j] += freeb ? (u32)__ffs(freeb) - 1u - b : 32u - b;  // none left in this word: on to the next
+            const u32 freeb = b == 31u ? 0u : (~view & (0xffffffffu << (b + 1u)));
+            att[j] += freeb ? (u32)__ffs(freeb) - 1u - b : 32u - b;
             if (att[j] >= L) {  // AtomicHashBuild.hpp:62-63: budget exhausted
               pend &= ~(1u << j);
               failed_bits |= 1u << j;
@@ -209,10 +259,10 @@ gt_build_kernel(const u64* __restrict__ R, SegMap sm, u64* __restrict__ table, u
         // locality signal: distinct 32 B table sectors this warp's inserts start in
         const u64 sec = v[j] ? (((v[j] & key_mask) & mask) >> 2) : ~0ull;
         const u32 peers = __match_any_sync(0xffffffffu, sec);
-        const bool leader = v[j] && (__ffs(peers) - 1 == (int)lane_id());
+        const bool leader = v[j] && (__ffs(peers) - 1 == (int)lane);
         const u32 leaders = __ballot_sync(0xffffffffu, leader);
         const u32 valid = __ballot_sync(0xffffffffu, v[j] != 0ull);
-        if (lane_id() == 0) {
+        if (lane == 0) {
           sectors += __popc(leaders);
           sampled += __popc(valid);
         }
@@ -226,10 +276,10 @@ gt_build_kernel(const u64* __restrict__ R, SegMap sm, u64* __restrict__ table, u
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
         const u32 y = __shfl_up_sync(0xffffffffu, incl, o);
-        if ((int)lane_id() >= o) incl += y;
+        if ((int)lane >= o) incl += y;
       }
       u64 base2 = 0;
-      if (lane_id() == 31) base2 = atomicAdd(ctr + C_CONFLICTS, (u64)incl);
+      if (lane == 31) base2 = atomicAdd(ctr + C_CONFLICTS, (u64)incl);
       base2 = __shfl_sync(0xffffffffu, base2, 31);
       u64 dst = base2 + (incl - mine);
 #pragma unroll
@@ -364,13 +414,18 @@ __global__ void __launch_bounds__(256) gt_ovf_insert_kernel(const u64* __restric
         slot[j] = ovf_hash(v[j] & key_mask, omask);
       }
     }
-    // rounds: kOvfIPT independent CAS in flight per thread (load <= 0.5: terminates)
+    // rounds: kOvfIPT independent probes in flight per thread (load <= 0.5: terminates).  Look before
+    // claiming: a plain load costs a fraction of an atomic, and duplicate keys (same hash) would otherwise
+    // queue their CAS on one slot after the other.
 #pragma unroll 1
     while (pend) {
       u64 res[kOvfIPT];
 #pragma unroll
       for (int j = 0; j < kOvfIPT; j++)
-        if (pend >> j & 1u) res[j] = atomicCAS(ovf_table + slot[j], 0ull, v[j]);
+        if (pend >> j & 1u) res[j] = ld_relaxed(ovf_table + slot[j]);
+#pragma unroll
+      for (int j = 0; j < kOvfIPT; j++)
+        if ((pend >> j & 1u) && res[j] == 0ull) res[j] = atomicCAS(ovf_table + slot[j], 0ull, v[j]);
 #pragma unroll
       for (int j = 0; j < kOvfIPT; j++)
         if (pend >> j & 1u) {
@@ -437,27 +492,33 @@ gt_span_kernel(const u64* __restrict__ R, SegMap sm, u64 mask, u64 key_mask, u64
 // ---- probe --------------------------------------------------------------------
 // AtomicHashBuild.hpp:75-83 per S tuple, plus the overflow table.  Per-thread
 // counts are reduced warp -> CTA -> one atomicAdd per CTA ("warp-aggregated").
+// A warp reads IPT rows of 32 consecutive S tuples (row j of warp w = tuples (w*IPT + j)*32 + lane of
+// the tile), so that on a sorted S -- the only probe side the reference has, main.cpp:93 -- the home
+// slots of a warp are IPT*32 consecutive table slots.
 //
-// Two paths, chosen from the build's own device-side counters (no host round trip):
+// Three paths, chosen from the build's own device-side counters and the warp's keys (no host round trip):
 //   * home-only: the build displaced nothing (probe_steps == 0, conflicts == 0), so every R tuple
 //     sits in its home slot and a key can only match there -- ONE coalesced 8-byte read per S
 //     tuple: the 16 B/tuple of SURVEY 8d exactly.  Every unique-key input (sorted, shuffle,
 //     local_shuffle) takes this path.
+//   * dense (probeLength <= 4, the warp's homes are consecutive slots): slot home+k of lane l is the
+//     home slot of lane l+k -- the window is assembled with shuffles from ONE coalesced read per row
+//     (plus three slots past the last row) instead of probeLength reads per tuple.
 //   * general: the window is read as whole 32-byte sectors (one LDG.256 for the sector of the home
-//     slot, a second one only if the walk runs over its end), then, for windows without an empty
-//     slot whose home has overflowed tuples (ovfmap), the overflow table.
+//     slot, the next one only if the walk runs over its end).
+// Windows without an empty slot whose home has overflowed tuples (ovfmap) then consult the overflow table.
 __device__ __forceinline__ void ld_sector(const u64* p, u64 (&c)[4]) {
   asm volatile("ld.global.nc.v4.u64 {%0, %1, %2, %3}, [%4];"
                : "=l"(c[0]), "=l"(c[1]), "=l"(c[2]), "=l"(c[3]) : "l"(p));
 }
 
 template <int IPT>
-__global__ void __launch_bounds__(kGtThreads, 4)
+__global__ void __launch_bounds__(kGtThreads, 3)
 gt_probe_kernel(const u64* __restrict__ S, u64 m, const u64* __restrict__ table, u64 mask, u64 key_mask, u32 L,
                 const u64* __restrict__ ovf_table, u64 ovf_capacity, const u32* __restrict__ ovfmap,
                 u64* __restrict__ ctr) {
   constexpr int TILE = kGtThreads * IPT;
-  const u32 tid = threadIdx.x;
+  const u32 tid = threadIdx.x, lane = lane_id(), warp = tid >> 5;
   const u64 ovf_count = ctr[C_CONFLICTS];
   const bool home_only = ovf_count == 0 && ctr[C_PROBE_STEPS] == 0;
   u64 omask = 0;
@@ -471,11 +532,11 @@ gt_probe_kernel(const u64* __restrict__ S, u64 m, const u64* __restrict__ table,
   const u64 nchunks = (m + TILE - 1) / TILE;
 
   for (u64 c = blockIdx.x; c < nchunks; c += gridDim.x) {
-    const u64 base = c * TILE;
+    const u64 base = c * TILE + (u64)warp * (IPT * 32) + lane;
     u64 s[IPT];
 #pragma unroll
     for (int j = 0; j < IPT; j++) {
-      const u64 i = base + (u64)j * kGtThreads + tid;
+      const u64 i = base + (u64)j * 32;
       s[j] = i < m ? ld_stream(S + i) : 0ull;
     }
     if (home_only) {
@@ -487,39 +548,71 @@ gt_probe_kernel(const u64* __restrict__ S, u64 m, const u64* __restrict__ table,
         if (cur[j] != 0ull && (cur[j] & key_mask) == (s[j] & key_mask)) { ++wmatches; checksum += cur[j] + s[j]; }
       continue;
     }
-    // general path, in rounds of one sector per tuple still walking
-    u32 pend = 0, full = 0;  // bit j: still walking / window exhausted without an empty slot
-    u32 off[IPT];            // slots of the window already walked
+    u32 full = 0;  // bit j: window exhausted without an empty slot
+    // dense: homes of the warp = h0 .. h0 + IPT*32 - 1, no wrap-around, every tuple valid
+    const u64 h0 = __shfl_sync(0xffffffffu, (s[0] & key_mask) & mask, 0);
+    bool dense = L <= 4 && h0 + IPT * 32 + 4 <= mask;
 #pragma unroll
-    for (int j = 0; j < IPT; j++) {
-      off[j] = 0;
-      if (s[j]) pend |= 1u << j;
-    }
-#pragma unroll 1
-    while (pend) {
-      u64 a[IPT][4];
+    for (int j = 0; j < IPT; j++) dense = dense && s[j] != 0ull && ((s[j] & key_mask) & mask) == h0 + j * 32 + lane;
+    if (__all_sync(0xffffffffu, dense)) {
+      u64 w0[IPT + 1];
 #pragma unroll
-      for (int j = 0; j < IPT; j++)
-        if (pend >> j & 1u) ld_sector(table + (((((s[j] & key_mask) & mask) + off[j]) & mask) & ~3ull), a[j]);
+      for (int j = 0; j < IPT; j++) w0[j] = __ldg(table + h0 + j * 32 + lane);
+      w0[IPT] = lane < 3 ? __ldg(table + h0 + IPT * 32 + lane) : 0ull;  // the slots past the last row
 #pragma unroll
       for (int j = 0; j < IPT; j++) {
-        if (pend >> j & 1u) {
-          const u64 key = s[j] & key_mask;
-          const u32 i0 = (u32)((key & mask) + off[j]) & 3u;
-          bool stop = false;
+        const u64 key = s[j] & key_mask;
+        bool walking = true;
 #pragma unroll
-          for (u32 i = 0; i < 4; i++) {
-            if (i >= i0 && !stop) {
-              if (off[j] >= L) { stop = true; full |= 1u << j; }
-              else if (a[j][i] == 0ull) stop = true;
-              else {
-                if ((a[j][i] & key_mask) == key) { ++wmatches; checksum += a[j][i] + s[j]; }
-                ++off[j];
+        for (u32 k = 0; k < 4; k++) {
+          u64 cw = w0[j];
+          if (k) {  // slot home+k: lane+k's word of this row, or lane+k-32's of the next
+            const u64 a = __shfl_sync(0xffffffffu, w0[j], (lane + k) & 31u);
+            const u64 b = __shfl_sync(0xffffffffu, w0[j + 1], (lane + k) & 31u);
+            cw = lane + k < 32u ? a : b;
+          }
+          if (k < L && walking) {
+            if (cw == 0ull) walking = false;
+            else if ((cw & key_mask) == key) { ++wmatches; checksum += cw + s[j]; }
+          }
+        }
+        if (walking) full |= 1u << j;
+      }
+    } else {
+      // general path, in rounds of one sector per tuple still walking
+      u32 pend = 0;
+      u32 off[IPT];  // slots of the window already walked
+#pragma unroll
+      for (int j = 0; j < IPT; j++) {
+        off[j] = 0;
+        if (s[j]) pend |= 1u << j;
+      }
+#pragma unroll 1
+      while (pend) {
+        u64 a[IPT][4];
+#pragma unroll
+        for (int j = 0; j < IPT; j++)
+          if (pend >> j & 1u) ld_sector(table + (((((s[j] & key_mask) & mask) + off[j]) & mask) & ~3ull), a[j]);
+#pragma unroll
+        for (int j = 0; j < IPT; j++) {
+          if (pend >> j & 1u) {
+            const u64 key = s[j] & key_mask;
+            const u32 i0 = (u32)((key & mask) + off[j]) & 3u;
+            bool stop = false;
+#pragma unroll
+            for (u32 i = 0; i < 4; i++) {
+              if (i >= i0 && !stop) {
+                if (off[j] >= L) { stop = true; full |= 1u << j; }
+                else if (a[j][i] == 0ull) stop = true;
+                else {
+                  if ((a[j][i] & key_mask) == key) { ++wmatches; checksum += a[j][i] + s[j]; }
+                  ++off[j];
+                }
               }
             }
+            if (!stop && off[j] >= L) { stop = true; full |= 1u << j; }
+            if (stop) pend &= ~(1u << j);
           }
-          if (!stop && off[j] >= L) { stop = true; full |= 1u << j; }
-          if (stop) pend &= ~(1u << j);
         }
       }
     }

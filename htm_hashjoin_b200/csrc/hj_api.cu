@@ -802,6 +802,87 @@ int choose_radix(hj_handle* h, u64 n, bool has_s, bool pre1, bool pre1_known, bo
   return HJ_OK;
 }
 
+// The per-partition shared-memory join over h->rb[0].out / h->rb[1].out (exact layout: offsets; histogram-free
+// layout: regions of capR / capS tuples whose fill levels are the scatter's cursors).
+int launch_partition_join(hj_handle* h, const RadixPlan& pl, u64 need, bool opt, u64 n, bool has_s, u64 m, u64 capR,
+                          u64 capS) {
+  int rc;
+  const u32 nparts = 1u << pl.bits;
+  // 32-bit-key fast path first (returns at once if rx_hist saw wider keys), then the generic
+  // kernel (returns at once if the fast path took the join).  Build-only PRO is generic.
+  const bool try32 = has_s && pl.bits >= 1 && (h->cfg.key_mask & 0xffffffffull) == 0xffffffffull &&
+                     !env().no_join32;
+  if (try32) {
+    const int forced = env().j32_variant;
+    // CTAs/SM by table size (chunk capacity = 0.75 * slots): 4 -> 5.3k, 2 -> 10.8k, 1 -> 21.7k tuples
+    const int variant = forced >= 0 ? forced : need <= 5300 ? 7 : need <= 10800 ? 3 : 10;
+    const void* k;
+    int threads, ctas;
+    int W = 4;
+#define J32V(T, B, M, WW) k = (const void*)rx_join32_kernel<T, B, M, WW>; threads = T; ctas = M; W = WW; break
+    switch (variant) {  // measured at C3 (profiles/r01_join32_variants.jsonl): 7 is the fastest
+      case 0: J32V(512, 8, 2, 4);
+      case 2: J32V(512, 4, 3, 2);
+      case 3: J32V(512, 8, 2, 2);
+      case 5: J32V(256, 8, 4, 2);
+      case 10: J32V(1024, 4, 1, 2);
+      case 11: J32V(1024, 6, 1, 2);
+      case 12: J32V(1024, 8, 1, 2);
+      default: J32V(384, 4, 4, 2);
+    }
+#undef J32V
+    // table: 4 slots per expected R tuple if shared memory allows `ctas` CTAs per SM with it
+    cudaFuncAttributes fa;
+    CK(cudaFuncGetAttributes(&fa, k));
+    const size_t per_sm = 228 * 1024, reserved = 1024;
+    size_t avail = per_sm / ctas - reserved - fa.sharedSizeBytes;
+    if (avail > h->smem_optin - fa.sharedSizeBytes) avail = h->smem_optin - fa.sharedSizeBytes;
+    u64 want = (n >> pl.bits) + 1;
+    if (want < 64) want = 64;
+    // want = expected R tuples per partition -> 4 slots each; buckets hold W slots in 8*W bytes
+    u32 nbuckets = (u32)(want * 32 <= avail ? want * 4 / W : avail / (8 * W));
+    nbuckets &= ~1u;  // key array = whole 16-byte words for either W
+    const size_t smem = (size_t)nbuckets * 8 * W;
+    CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int grid = grid_for(h, k, threads, smem);
+    if ((u32)grid > nparts) grid = (int)nparts;
+    // histogram-free layout: the partitions' ends are the scatter's final cursors
+    const u64 *aR = h->rb[0].out.p, *aoR = opt ? h->rb[0].cursors.p : h->rb[0].offsets.p, *aS = h->rb[1].out.p,
+              *aoS = opt ? h->rb[1].cursors.p : h->rb[1].offsets.p;
+    u32 a_np = nparts, a_bits = pl.bits;
+    u64* a_ctr = h->ctr;
+    u64 a_capR = capR, a_capS = capS;
+    // tasks = (partition, S slice): S partitions beyond 4x the mean are probed by several CTAs
+    u64 slice = 4 * (m >> pl.bits);
+    if (slice < 32768) slice = 32768;
+    if (env().join_slice) slice = env().join_slice;
+    slice &= ~1ull;
+    const u64 max_tasks = (u64)nparts + m / slice + 1;
+    if ((rc = ensure(h, h->tasks, max_tasks))) return rc;
+    rx_tasks_kernel<<<1, 1024, 0, h->stream>>>(aoS, nparts, capS, slice, h->tasks.p, max_tasks, h->ctr);
+    const u64* a_tasks = h->tasks.p;
+    void* args[] = {&aR, &aoR, &aS, &aoS, &a_np, &a_bits, &nbuckets, &a_ctr, &a_capR, &a_capS, &a_tasks, &slice};
+    CK(cudaLaunchKernel(k, dim3(grid), dim3(threads), args, smem, h->stream));
+    h->launches += 2;
+  }
+  {
+    size_t smem = (size_t)pl.slots * 8;
+    // <loads in flight per thread, CTAs/SM the register budget is set for>
+    const int variant = env().join_variant;
+    auto k = variant == 1 ? rx_join_kernel<4, 3> : variant == 2 ? rx_join_kernel<6, 3> : rx_join_kernel<8, 2>;
+    CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int grid = grid_for(h, (const void*)k, kJoinThreads, smem);
+    if ((u32)grid > nparts) grid = (int)nparts;
+    k<<<grid, kJoinThreads, smem, h->stream>>>(h->rb[0].out.p, opt ? h->rb[0].cursors.p : h->rb[0].offsets.p,
+                                               has_s ? h->rb[1].out.p : nullptr,
+                                               has_s ? (opt ? h->rb[1].cursors.p : h->rb[1].offsets.p) : nullptr, nparts,
+                                               pl.bits, pl.slots, h->cfg.key_mask, h->ctr, try32 ? 1 : 0, capR, capS);
+    h->launches++;
+    CK(cudaGetLastError());
+  }
+  return HJ_OK;
+}
+
 // materialisation request (hj_join_materialize): out may be null (count only)
 struct MatReq {
   ulonglong2* out;
@@ -999,78 +1080,7 @@ int run_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS
     h->launches += 3;
     CK(cudaGetLastError());
   }
-  // 32-bit-key fast path first (returns at once if rx_hist saw wider keys), then the generic
-  // kernel (returns at once if the fast path took the join).  Build-only PRO is generic.
-  const bool try32 = !use_l2 && dS && pl.bits >= 1 && (h->cfg.key_mask & 0xffffffffull) == 0xffffffffull &&
-                     !env().no_join32;
-  if (try32) {
-    const int forced = env().j32_variant;
-    // CTAs/SM by table size (chunk capacity = 0.75 * slots): 4 -> 5.3k, 2 -> 10.8k, 1 -> 21.7k tuples
-    const int variant = forced >= 0 ? forced : need <= 5300 ? 7 : need <= 10800 ? 3 : 10;
-    const void* k;
-    int threads, ctas;
-    int W = 4;
-#define J32V(T, B, M, WW) k = (const void*)rx_join32_kernel<T, B, M, WW>; threads = T; ctas = M; W = WW; break
-    switch (variant) {  // measured at C3 (profiles/r01_join32_variants.jsonl): 7 is the fastest
-      case 0: J32V(512, 8, 2, 4);
-      case 2: J32V(512, 4, 3, 2);
-      case 3: J32V(512, 8, 2, 2);
-      case 5: J32V(256, 8, 4, 2);
-      case 10: J32V(1024, 4, 1, 2);
-      case 11: J32V(1024, 6, 1, 2);
-      case 12: J32V(1024, 8, 1, 2);
-      default: J32V(384, 4, 4, 2);
-    }
-#undef J32V
-    // table: 4 slots per expected R tuple if shared memory allows `ctas` CTAs per SM with it
-    cudaFuncAttributes fa;
-    CK(cudaFuncGetAttributes(&fa, k));
-    const size_t per_sm = 228 * 1024, reserved = 1024;
-    size_t avail = per_sm / ctas - reserved - fa.sharedSizeBytes;
-    if (avail > h->smem_optin - fa.sharedSizeBytes) avail = h->smem_optin - fa.sharedSizeBytes;
-    u64 want = (n >> pl.bits) + 1;
-    if (want < 64) want = 64;
-    // want = expected R tuples per partition -> 4 slots each; buckets hold W slots in 8*W bytes
-    u32 nbuckets = (u32)(want * 32 <= avail ? want * 4 / W : avail / (8 * W));
-    nbuckets &= ~1u;  // key array = whole 16-byte words for either W
-    const size_t smem = (size_t)nbuckets * 8 * W;
-    CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int grid = grid_for(h, k, threads, smem);
-    if ((u32)grid > nparts) grid = (int)nparts;
-    // histogram-free layout: the partitions' ends are the scatter's final cursors
-    const u64 *aR = h->rb[0].out.p, *aoR = opt ? h->rb[0].cursors.p : h->rb[0].offsets.p, *aS = h->rb[1].out.p,
-              *aoS = opt ? h->rb[1].cursors.p : h->rb[1].offsets.p;
-    u32 a_np = nparts, a_bits = pl.bits;
-    u64* a_ctr = h->ctr;
-    u64 a_capR = capR, a_capS = capS;
-    // tasks = (partition, S slice): S partitions beyond 4x the mean are probed by several CTAs
-    u64 slice = 4 * (m >> pl.bits);
-    if (slice < 32768) slice = 32768;
-    if (env().join_slice) slice = env().join_slice;
-    slice &= ~1ull;
-    const u64 max_tasks = (u64)nparts + m / slice + 1;
-    if ((rc = ensure(h, h->tasks, max_tasks))) return rc;
-    rx_tasks_kernel<<<1, 1024, 0, h->stream>>>(aoS, nparts, capS, slice, h->tasks.p, max_tasks, h->ctr);
-    const u64* a_tasks = h->tasks.p;
-    void* args[] = {&aR, &aoR, &aS, &aoS, &a_np, &a_bits, &nbuckets, &a_ctr, &a_capR, &a_capS, &a_tasks, &slice};
-    CK(cudaLaunchKernel(k, dim3(grid), dim3(threads), args, smem, h->stream));
-    h->launches += 2;
-  }
-  if (!use_l2) {
-    size_t smem = (size_t)pl.slots * 8;
-    // <loads in flight per thread, CTAs/SM the register budget is set for>
-    const int variant = env().join_variant;
-    auto k = variant == 1 ? rx_join_kernel<4, 3> : variant == 2 ? rx_join_kernel<6, 3> : rx_join_kernel<8, 2>;
-    CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int grid = grid_for(h, (const void*)k, kJoinThreads, smem);
-    if ((u32)grid > nparts) grid = (int)nparts;
-    k<<<grid, kJoinThreads, smem, h->stream>>>(h->rb[0].out.p, opt ? h->rb[0].cursors.p : h->rb[0].offsets.p,
-                                               dS ? h->rb[1].out.p : nullptr,
-                                               dS ? (opt ? h->rb[1].cursors.p : h->rb[1].offsets.p) : nullptr, nparts,
-                                               pl.bits, pl.slots, h->cfg.key_mask, h->ctr, try32 ? 1 : 0, capR, capS);
-    h->launches++;
-    CK(cudaGetLastError());
-  }
+  if (!use_l2 && (rc = launch_partition_join(h, pl, need, opt, n, dS != nullptr, m, capR, capS))) return rc;
   mark(h, E_JOIN);
   mark(h, E_END);
   if ((rc = fetch_counters(h))) return rc;
