@@ -24,6 +24,8 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# one hardware queue per stream (compute + one copy stream per peer): no false dependencies between them
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 
 METRIC = "join M tuples/s (|R|+|S|)"
 UNIT = "Mtuples/s"
@@ -41,12 +43,16 @@ def parse_args():
     ap.add_argument("--passes", type=int, default=0)
     ap.add_argument("--algo", default="radix", choices=["radix", "atomic", "adaptive", "nocc"])
     ap.add_argument("--r-dist", default="shuffle", help="DataGen distribution of R at N=1 (host generated)")
-    ap.add_argument("--exchange", default="regions", choices=["regions", "fused", "nccl"],
-                    help="N>1: exchange fused with radix pass 1 over peer memory -- histogram-free into fixed-capacity "
-                         "regions (default), or with exact counts first (fused) -- or partition + NCCL all-to-all")
-    ap.add_argument("--chunks", type=int, default=1,
-                    help="fused exchange: split S into this many chunks and overlap the exchange of chunk c+1 "
-                         "with pass 2 + join of chunk c (a join is additive over disjoint parts of S)")
+    ap.add_argument("--exchange", default="xchg", choices=["xchg", "regions", "fused", "nccl"],
+                    help="N>1: xchg = local scatter + copy-engine transfers pipelined under pass 2 + join (default); "
+                         "regions / fused = SM stores over NVLink fused with radix pass 1 (histogram-free / exact "
+                         "counts first); nccl = partition + NCCL all-to-all")
+    ap.add_argument("--chunks", type=int, default=0,
+                    help="split S into this many chunks so the exchange of chunk c+1 overlaps pass 2 + join of chunk c "
+                         "(a join is additive over disjoint parts of S); 0 = 4 for xchg, 1 otherwise")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: every GPU holds 2^log-r x 2^log-s; strong: those are the GLOBAL sizes, split over the GPUs "
+                         "(BASELINE configs[4]: --scaling strong --log-r 30 --log-s 33)")
     ap.add_argument("--peer-ctas", type=int, default=48, help="CTAs of an overlapped peer scatter (NVLink-bound)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -261,11 +267,9 @@ def run_reference(args):
 # =============================================================================
 # B200 arm
 # =============================================================================
-def expected_result(G, log_r, log_s):
-    """FK S over PK R: every S tuple matches exactly one R tuple with r == s, so
-    matches = |S| and checksum = 2 * sum(S); S = |S|/D permutations of 1..D."""
-    D = G << log_r
-    m = G << log_s
+def expected_result(D, m):
+    """FK S (m tuples) over PK R = a permutation of 1..D: every S tuple matches exactly one R tuple with
+    r == s, so matches = |S| and checksum = 2 * sum(S); S = |S|/D permutations of 1..D."""
     blocks, rest = divmod(m, D)
     assert rest == 0
     return m, (2 * blocks * (D * (D + 1) // 2)) % (1 << 64)
@@ -291,7 +295,13 @@ class Rank:
             self.exchange = exchange
         G = self.world
         self.n, self.m = 1 << args.log_r, 1 << args.log_s
+        if args.scaling == "strong":  # global sizes, split over the ranks
+            assert self.n % G == 0 and self.m % G == 0
+            self.n, self.m = self.n // G, self.m // G
         self.domain = G * self.n
+        if args.chunks == 0:
+            args.chunks = 4 if (G > 1 and args.exchange == "xchg") else 1
+        self.xchg = G > 1 and args.exchange == "xchg"
         self.h = hj.HashJoin(args.algo, device=self.local, num_partitions=(1 << args.radix_bits) if args.radix_bits else 0,
                              passes=args.passes)
         dev = torch.device("cuda", self.local)
@@ -319,7 +329,22 @@ class Rank:
         if G > 1:
             cap_r = self.n + self.n // 32 + 65536
             cap_s = self.m + self.m // 32 + 65536
-        if self.fused:
+        if self.xchg:
+            # pipelined exchange over the copy engines (include/hj_b200.h, hj_xchg_*): local scatter by
+            # (owner GPU, low b1 bits) into G << b1 <= 256 regions, pass 2 takes the remaining bits
+            bits, _, _, passes = self.h.radix_plan(self.n)
+            assert passes == 2, "the exchange needs the 2-pass plan"
+            self.b1 = min(6, (256 // G).bit_length() - 1, bits - 1)
+            self.h.close()
+            self.h = hj.HashJoin(args.algo, device=self.local, num_partitions=1 << bits, passes=2, pass1_bits=self.b1)
+            self.f1 = 1 << self.b1
+            self.chunks = max(1, args.chunks)
+            dom_bits = self.exchange.domain_bits_for(self.domain)
+            win, self.window_bytes = self.h.xchg_create(G, self.rank, self.n, self.m, self.chunks, dom_bits)
+            handles = self.exchange.exchange_ipc_handles(self.h.ipc_export(win))
+            self.h.xchg_connect([win if g == self.rank else self.h.ipc_open(handles[g]) for g in range(G)])
+            self.epoch = 0
+        elif self.fused:
             # exchange == radix pass 1: every rank stores straight into the owners' pass-1 buffers
             # (CUDA IPC over NVLink).  The fan-out is fixed so all ranks agree on b1.
             bits, self.b1, _, passes = self.h.radix_plan(self.n)
@@ -364,6 +389,8 @@ class Rank:
         if G == 1:
             self.h.reserve(self.n, self.m)
             self.h.reserve_staging(self.n, self.m)
+        elif self.xchg:
+            pass  # hj_xchg_create sized everything
         else:
             self.h.reserve(self.n + self.n // 16 + 65536, self.m + self.m // 16 + 65536)
         self.last = None
@@ -394,6 +421,8 @@ class Rank:
             self.h.copy(self.dS.data_ptr(), self.hS.ctypes.data, self.m * 8)
         ex = self.exchange
         dom_bits = ex.domain_bits_for(self.domain)
+        if self.xchg:
+            return self.step_xchg()
         if self.regions and self.chunks == 1:
             out = self.step_regions(dom_bits)
             if out is not None:
@@ -420,6 +449,32 @@ class Rank:
         self.last = res
         # 4. {matches, checksum} summed over ranks
         return ex.reduce_result(res.matches, res.checksum, "cuda")
+
+    def step_xchg(self):
+        """Pipelined exchange over the copy engines: one enqueue, one wait, one all-reduce (which is also the
+        barrier the next epoch needs)."""
+        t = [time.perf_counter()]
+        self.epoch += 1
+        self.h.xchg_start(self.dR.data_ptr(), self.dS.data_ptr(), self.epoch)
+        t.append(time.perf_counter())
+        ovf = 0
+        try:
+            res = self.h.xchg_finish()
+            matches, checksum = res.matches, res.checksum
+            self.launches += res.kernel_launches
+            self.last = res
+        except self.hj.HJError as e:
+            if e.code != self.hj.HJ_EOVERFLOW:
+                raise
+            ovf, matches, checksum = 1, 0, 0
+        t.append(time.perf_counter())
+        out = self.exchange.reduce_result3(matches, checksum, ovf, "cuda")
+        t.append(time.perf_counter())
+        self.fused_ms = [round((b - a) * 1e3, 3) for a, b in zip(t, t[1:])]  # enqueue, pipeline, allreduce
+        if out[2]:
+            raise RuntimeError("hj_xchg: a region overflowed on some rank (skewed keys): run with --exchange fused")
+        self.nvlink_bytes += 8 * (self.n + self.m) * (self.world - 1) // self.world  # uniform keys: (G-1)/G leaves
+        return out[0], out[1]
 
     def step_fused(self, dom_bits):
         """Exchange fused with radix pass 1 (include/hj_b200.h, hj_peer_*)."""
@@ -575,6 +630,7 @@ class Rank:
             for k in ("us_total", "us_hist", "us_scan", "us_scatter1", "us_scatter2", "us_join", "us_build",
                       "us_probe", "us_clear", "us_h2d"):
                 phases[k] = phases.get(k, 0.0) + getattr(r, k)
+            phases["us_wait"] = phases.get("us_wait", 0.0) + r.us_reserved[0]
         e1.record()
         torch.cuda.synchronize()
         ms = self.max_over_ranks(e0.elapsed_time(e1))
@@ -627,7 +683,7 @@ def global_table_lines(rk, reps=5, warm=2):
 def run_b200(args):
     rk = Rank(args)
     G = rk.world
-    want = expected_result(G, args.log_r, args.log_s) if args.algo in ("radix", "adaptive", "atomic") else None
+    want = expected_result(G * rk.n, G * rk.m) if args.algo in ("radix", "adaptive", "atomic") else None
     peak, peak_src = load_peaks()
     tuples = G * (rk.n + rk.m)
     # ---- device-resident: `value` ----
@@ -662,24 +718,33 @@ def run_b200(args):
         n_loc, m_loc = rk.n, rk.m  # per-GPU tuples (exact at N=1, +-0.1% after the exchange)
         sc_us = ph["us_scatter1"] + ph["us_scatter2"]
         sc_bytes = 16.0 * P * (n_loc + m_loc)  # every scatter launch reads 8 B and writes 8 B per tuple
+        n_launch = 2 * P
+        local_bytes = float(last.hbm_bytes)  # what ran on this GPU inside us_total
+        if getattr(rk, "xchg", False):
+            # both passes are local kernels (the copy engines move the blocks in between); they share HBM with
+            # the DMA traffic of the exchange (8 B read + 8 B written per tuple that travels)
+            n_launch = 2 * (1 + rk.chunks)
         if getattr(rk, "fused", False):
             # pass 1 ran as the peer scatter (NVLink-bound, timed on the host as fused_ms[2]); the
             # HBM roofline line is pass 2 alone
             P = 1
+            n_launch = 2
             sc_us, sc_bytes = ph["us_scatter2"], 16.0 * (n_loc + m_loc)
-        roof = {"bound": "hbm", "kernel": f"rx_scatter_kernel<16> ({2 * P} launches/step: R and S x {P} passes)",
+            local_bytes = 24.0 * (n_loc + m_loc)  # us_total of hj_join_regions/_pass1 holds pass 2 + join only
+        roof = {"bound": "hbm", "kernel": f"rx_scatter_kernel<16> ({n_launch} launches/step: R and S (chunks) x {P} passes)",
                 "achieved": round(sc_bytes / (sc_us * 1e-6) / 1e9, 1), "peak": peak, "unit": "GB/s",
                 "frac": round(sc_bytes / (sc_us * 1e-6) / 1e9 / peak, 4),
                 # ncu --set full, profiles/r01_ncu_radix_v4_raw.csv: the S launches over 2^28 tuples moved
                 # dram__bytes_read 2.148 GB + dram__bytes_write 2.100 GB = 15.83 B/tuple (algorithmic: 16)
-                "traffic": int(15.83 * sc_bytes / 16.0 / (2 * P)),
+                "traffic": int(15.83 * sc_bytes / 16.0 / n_launch),
                 "traffic_source": "15.83 B/tuple measured by ncu at |S|=2^28 (profiles/r01_ncu_radix_v4_raw.csv), "
                                   "scaled to this launch size",
-                "peak_source": peak_src, "avg_launch_us": round(sc_us / (2 * P), 1),
-                "algorithmic_bytes_per_launch": int(sc_bytes / (2 * P)),
-                "whole_join": {"algorithmic_bytes": int(last.hbm_bytes),
-                               "achieved": round(last.hbm_bytes / (ph["us_total"] * 1e-6) / 1e9, 1),
-                               "frac": round(last.hbm_bytes / (ph["us_total"] * 1e-6) / 1e9 / peak, 4)}}
+                "peak_source": peak_src, "avg_launch_us": round(sc_us / n_launch, 1),
+                "algorithmic_bytes_per_launch": int(sc_bytes / n_launch),
+                "whole_join": {"algorithmic_bytes": int(local_bytes),
+                               "achieved": round(local_bytes / (ph["us_total"] * 1e-6) / 1e9, 1),
+                               "frac": round(local_bytes / (ph["us_total"] * 1e-6) / 1e9 / peak, 4),
+                               "note": "algorithmic bytes of the kernels inside us_total on one GPU / that time"}}
     else:
         us = ph["us_build"] + ph["us_probe"]
         b = 16.0 * (rk.n + rk.m)
@@ -688,13 +753,19 @@ def run_b200(args):
                 "peak_source": peak_src}
     line = {
         "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": G, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 3), "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 3), "higher_is_better": True, "scaling": args.scaling,
         "vs_baseline": None, "dtype": "u64", "data": f"synthetic: R = {rk.r_desc}; S = {rk.s_desc}",
-        "config": {"workload": f"radix join |R|=2^{args.log_r} PK x |S|=2^{args.log_s} FK per GPU "
-                               f"(BASELINE configs[2] at N=1; x8 = configs[4])",
+        "config": {"workload": (f"radix join |R|=2^{args.log_r} PK x |S|=2^{args.log_s} FK per GPU "
+                                f"(BASELINE configs[2] at N=1; x8 = configs[4])" if args.scaling == "weak" else
+                                f"radix join |R|=2^{args.log_r} PK x |S|=2^{args.log_s} FK in total, split over {G} GPUs "
+                                f"(BASELINE configs[4] is 2^30 x 2^33)"),
                    "algo": args.algo, "radix_bits": int(last.radix_bits), "passes": int(last.passes),
                    "tuples_per_step": tuples, "l2": "inputs (9 GiB/GPU) larger than L2, no flush needed",
-                   "exchange": "none" if G == 1 else ("fused with radix pass 1, histogram-free: TMA stores into fixed-capacity regions of the owners' pass-1 buffers over NVLink (CUDA IPC)"
+                   "exchange": "none" if G == 1 else (f"pipelined over the copy engines: local scatter by (owner GPU, low {rk.b1} bits) into "
+                                                      f"fixed-capacity regions, one device-to-device copy per (peer, stage) over NVLink "
+                                                      f"(CUDA IPC) under pass 2 + join of the previous stage; S in {rk.chunks} chunks"
+                                                      if args.exchange == "xchg" else
+                                                      "fused with radix pass 1, histogram-free: TMA stores into fixed-capacity regions of the owners' pass-1 buffers over NVLink (CUDA IPC)"
                                                       if args.exchange == "regions" else
                                                       "fused with radix pass 1: stores into the owners' pass-1 buffers over NVLink (CUDA IPC)"
                                                       if args.exchange == "fused" else
@@ -705,6 +776,11 @@ def run_b200(args):
     }
     if G > 1:
         line["nvlink_bytes_per_gpu_per_step"] = int(nvl)
+        if getattr(rk, "xchg", False):
+            line["xchg_ms_last_step"] = dict(zip(["enqueue", "pipeline (device)", "allreduce"], rk.fused_ms))
+            line["xchg_wait_us_per_step"] = round(float(ph.get("us_wait", 0.0)), 1)
+            line["nvlink_gbs_over_step"] = round(nvl / (ms / args.steps * 1e-3) / 1e9, 1)
+            line["window_bytes"] = int(rk.window_bytes)
         if getattr(rk, "fused", False):
             if getattr(rk, "regions", False) and rk.chunks == 1 and not getattr(rk, "region_fallbacks", 0):
                 names, sc = ["peer_scatter", "cursor all-gather (= barrier)", "pass2+join", "allreduce"], 0

@@ -243,6 +243,26 @@ class HashJoin:
                                       int(d_offS1) if d_offS1 else None, C.byref(res)), "hj_join_pass1")
         return res
 
+    # ---- pipelined exchange over the copy engines (include/hj_b200.h, hj_xchg_*) ----
+    def xchg_create(self, n_ranks, rank, n_local, m_local, s_chunks, domain_bits):
+        """Returns (window device pointer, window bytes): export the window with ipc_export()."""
+        w, nb = C.c_void_p(), C.c_uint64()
+        self._check(lib.hj_xchg_create(self._h, int(n_ranks), int(rank), int(n_local), int(m_local), int(s_chunks),
+                                       int(domain_bits), C.byref(w), C.byref(nb)), "hj_xchg_create")
+        return w.value, nb.value
+
+    def xchg_connect(self, peer_windows):
+        arr = (C.c_uint64 * len(peer_windows))(*[int(p) if p else 0 for p in peer_windows])
+        self._check(lib.hj_xchg_connect(self._h, arr), "hj_xchg_connect")
+
+    def xchg_start(self, d_R, d_S, epoch):
+        self._check(lib.hj_xchg_start(self._h, int(d_R), int(d_S), int(epoch)), "hj_xchg_start")
+
+    def xchg_finish(self):
+        res = hj_result()
+        self._check(lib.hj_xchg_finish(self._h, C.byref(res)), "hj_xchg_finish")
+        return res
+
     def generate(self, kind, first, count, domain, seed, d_out):
         self._check(lib.hj_generate(self._h, kind, int(first), int(count), int(domain), int(seed), int(d_out)),
                     "hj_generate")

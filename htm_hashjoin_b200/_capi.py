@@ -24,6 +24,7 @@ ABI_SYMBOLS = [
     "hj_radix_plan", "hj_ipc_export", "hj_ipc_open", "hj_ipc_close", "hj_peer_hist", "hj_peer_scatter",
     "hj_join_pass1", "hj_join_materialize", "hj_peer_scatter_async",
     "hj_peer_scatter_regions", "hj_join_regions", "hj_reserve_staging", "hj_alloc_count",
+    "hj_xchg_create", "hj_xchg_connect", "hj_xchg_start", "hj_xchg_finish",
 ]
 # host-side mirror of the reference interface (csrc/ref_entry.hpp, csrc/datagen.hpp)
 HOST_SYMBOLS = ["hj_ref_run", "hj_ref_set_radix", "hj_ref_set_device", "hj_ref_last_status",
@@ -108,6 +109,11 @@ def load():
         "hj_join_pass1": (C.c_int, [H, u64p, C.c_uint64, u64p, u64p, C.c_uint64, u64p, C.POINTER(hj_result)]),
         "hj_join_materialize": (C.c_int, [H, u64p, C.c_uint64, u64p, C.c_uint64, u64p, C.c_uint64,
                                           C.POINTER(C.c_uint64), C.POINTER(hj_result)]),
+        "hj_xchg_create": (C.c_int, [H, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32,
+                                     C.POINTER(vp), C.POINTER(C.c_uint64)]),
+        "hj_xchg_connect": (C.c_int, [H, C.POINTER(C.c_uint64)]),
+        "hj_xchg_start": (C.c_int, [H, u64p, u64p, C.c_uint64]),
+        "hj_xchg_finish": (C.c_int, [H, C.POINTER(hj_result)]),
         "hj_generate": (C.c_int, [H, C.c_int, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, u64p]),
         "hj_device_alloc": (C.c_int, [H, C.c_uint64, C.POINTER(vp)]),
         "hj_device_free": (C.c_int, [H, vp]),

@@ -24,17 +24,18 @@
 // instead -- one bit per slot, slots/8 bytes, 32 MB at 2^27: L2-resident -- and the
 // tuple is then written with a plain store.  The claims of a CTA tile are
 // write-combined in shared memory, the way rx_scatter combines its output runs:
-//   * the tile's tuples set their bits in a shared-memory copy of the band of the
-//     bitmap the tile touches (home slots of a sorted / locally shuffled tile lie
-//     within tile + 2W slots of each other); a bit that is already set there is a
-//     duplicate request inside the tile and loses at once;
-//   * ONE global atomicOr per non-empty 32-slot word claims everything the tile
-//     wants in it -- 65 atomics for 2048 sorted tuples instead of 2048 -- and its
-//     return value tells every requester whether its bit was free;
-//   * a tuple that lost sees the word's whole occupancy and goes straight to the
-//     next free slot of its window instead of stepping one round trip at a time;
-//   * tuples whose slot lies outside the band (fully shuffled inputs) claim their
-//     bit with an atomic of their own, all of a thread's in flight together;
+//   * the tile's tuples do their linear probing against a shared-memory image of
+//     the band of the bitmap the tile touches (home slots of a sorted / locally
+//     shuffled tile lie within tile + 2W slots of each other): an ATOMS.OR per
+//     attempt, whose return value shows the whole word, so a tuple that finds its
+//     slot taken goes straight to the next free slot of its window -- duplicates and
+//     displacement chains are resolved on chip, without a global round trip each;
+//   * then ONE global atomicOr per touched 32-slot word commits everything the tile
+//     claimed in it -- 65 atomics for 2048 sorted tuples instead of 2048.  Bits
+//     that another CTA got first come back in the return value: only those tuples
+//     (tile borders, duplicates across tiles) probe on and commit again;
+//   * tuples whose window lies outside the band (fully shuffled inputs) claim their
+//     bit with a global atomic of their own, all of a thread's in flight together;
 //   * winners store their tuple: the stores of a tile to neighbouring slots meet
 //     in L2 and leave as full sectors, so the table is written without ever being
 //     read -- 16 B/tuple of DRAM traffic.
@@ -58,30 +59,32 @@ struct SegMap {
   u64 nslices;
 };
 
-__device__ __forceinline__ u32 ld_relaxed_u32(const u32* p) {
-  u32 r;
-  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(r) : "l"(p) : "memory");
-  return r;
-}
-
-// IPT tuples per thread ("transaction size": how many inserts a thread has in
-// flight before it looks at any outcome), loaded as IPT coalesced 8-byte loads.
-// STATS: the sampling round of the adaptive switch -- peeks at the bitmap before
-// claiming (only a load-then-claim can tell a lost race from an old occupant).
-//
 // A tuple is "in band" when its whole window [home, home + L + 32) lies inside the tile's band and
 // below the table end (no wrap-around): then every attempt it ever makes goes through shared memory
 // and its position is one 32-bit offset.  Everything else ("far": fully shuffled inputs, the last
 // few slots of the table) claims with global atomics of its own.
 constexpr u32 kGtFar = 0xffffffffu;
 
+// next attempt of a tuple that found bit b of its word taken: the first slot above b that `view` shows
+// free, or the first slot of the next word.  Everything skipped is occupied, so the probe's walk from the
+// home slot never meets a gap before the tuple.
+__device__ __forceinline__ u32 gt_advance(u32 view, u32 b) {
+  const u32 freeb = b == 31u ? 0u : (~view & (0xffffffffu << (b + 1u)));
+  return freeb ? (u32)__ffs(freeb) - 1u - b : 32u - b;
+}
+
+// IPT tuples per thread ("transaction size": how many inserts a thread has in
+// flight before it looks at any outcome), loaded as IPT coalesced 8-byte loads.
+// STATS: the sampling round of the adaptive switch: cas_retries = claims lost to another CTA at
+// commit time (the HTM-abort stand-in), probe_steps = occupied slots stepped over.
 template <int IPT, bool STATS>
 __global__ void __launch_bounds__(kGtThreads, 4)
 gt_build_kernel(const u64* __restrict__ R, SegMap sm, u64* __restrict__ table, u32* __restrict__ claim, u64 mask,
                 u64 key_mask, u32 L, u64* __restrict__ ovf_list, u64* __restrict__ ctr) {
   constexpr int TILE = kGtThreads * IPT;
-  __shared__ u32 s_want[kGtBandWords];  // bits the tile asks for this round
-  __shared__ u32 s_old[kGtBandWords];   // what the global word held before the tile's atomicOr
+  __shared__ u32 s_occ[kGtBandWords];    // what the tile knows to be occupied: its own claims + what commits returned
+  __shared__ u32 s_theirs[kGtBandWords]; // bits another CTA got first (learned at commit)
+  __shared__ u32 s_mine[kGtBandWords];   // bits this tile owns (committed)
   __shared__ u64 s_min[kGtThreads / 32], s_max[kGtThreads / 32];
   const u32 tid = threadIdx.x, lane = lane_id();
   const u64 chunks_per_seg = (sm.seg_len + TILE - 1) / TILE;
@@ -111,29 +114,36 @@ gt_build_kernel(const u64* __restrict__ R, SegMap sm, u64* __restrict__ table, u
       if (v[j]) {
         const u64 hm = (v[j] & key_mask) & mask;
         lo = hm < lo ? hm : lo;
-        if (STATS) hi = hm > hi ? hm : hi;
+        hi = hm > hi ? hm : hi;
       }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
       lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
-      if (STATS) hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
+      hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
     }
-    if (lane == 0) { s_min[tid >> 5] = lo; if (STATS) s_max[tid >> 5] = hi; }
+    __syncthreads();  // the previous tile is done with the shared arrays
+    if (lane == 0) { s_min[tid >> 5] = lo; s_max[tid >> 5] = hi; }
     __syncthreads();
 #pragma unroll
-    for (int w2 = 0; w2 < kGtThreads / 32; w2++) lo = min(lo, s_min[w2]);
-    if (STATS && tid == 0) {
-      // working-set signal: how wide is the band of table slots one CTA chunk touches?
-      for (int w2 = 0; w2 < kGtThreads / 32; w2++) hi = max(hi, s_max[w2]);
-      if (hi >= lo) { span += hi - lo + 1; chunks += 1; }
+    for (int w2 = 0; w2 < kGtThreads / 32; w2++) { lo = min(lo, s_min[w2]); hi = max(hi, s_max[w2]); }
+    if (STATS && tid == 0 && hi >= lo) {  // working-set signal: how wide is the band of slots one CTA chunk touches?
+      span += hi - lo + 1;
+      chunks += 1;
     }
-    const u64 base = lo & ~31ull;  // (an empty tile has lo = ~0: nothing is pending, no round runs)
+    const u64 base = lo & ~31ull;  // (an empty tile has lo = ~0, hi = 0: nothing is pending)
     u32* const gband = claim + (base >> 5);
+    // words of the band this tile can touch
+    u32 nwords = 0;
+    if (hi >= lo) {
+      const u64 nw = ((hi - base + L + 64) >> 5) + 1;
+      nwords = nw < (u64)kGtBandWords ? (u32)nw : (u32)kGtBandWords;
+    }
+    for (u32 wi = tid; wi < nwords; wi += kGtThreads) { s_occ[wi] = 0u; s_theirs[wi] = 0u; s_mine[wi] = 0u; }
 
     u32 rel[IPT];  // home - base, or kGtFar
     u32 att[IPT];  // offset from home of the next slot to try
     u32 pend = 0;  // bit j: tuple j still has to be placed
-    u32 farbits = 0;
+    u32 farbits = 0, failed_bits = 0;
 #pragma unroll
     for (int j = 0; j < IPT; j++) {
       att[j] = 0;
@@ -146,111 +156,121 @@ gt_build_kernel(const u64* __restrict__ R, SegMap sm, u64* __restrict__ table, u
         else farbits |= 1u << j;
       }
     }
-    u32 failed_bits = 0;
 
-    // Rounds: every pending tuple of the tile makes its next attempt.  AtomicHashBuild.hpp:46-60
-    // with the claim bitmap standing in for the slot's old value.
-    while (__syncthreads_or(pend != 0)) {  // (also: everybody is done with s_want / s_old / s_min)
+    // ---- far tuples: AtomicHashBuild.hpp:46-60 with one global atomic per attempt, in rounds ----------
+    if (pend & farbits) {
+      u32 fp = pend & farbits;
+#pragma unroll 1
+      while (fp) {
+        u32 old[IPT];
 #pragma unroll
-      for (int k = 0; k < kGtBandWords / kGtThreads; k++) s_want[k * kGtThreads + tid] = 0u;
-      __syncthreads();
-      u32 far_old[IPT];  // far tuples: what their own atomicOr (STATS: peek) returned
-      u32 pre = 0;       // bit j: lost before asking (duplicate request in the tile / STATS: seen occupied)
-      u32 peeked[IPT];
-      if (pend & farbits) {  // all of a thread's far claims in flight together
-#pragma unroll
-        for (int j = 0; j < IPT; j++) {
-          if (pend & farbits & (1u << j)) {
+        for (int j = 0; j < IPT; j++)
+          if (fp >> j & 1u) {
             const u64 slot = (((v[j] & key_mask) & mask) + att[j]) & mask;
-            const u32 bit = 1u << ((u32)slot & 31u);
-            if (STATS) {
-              far_old[j] = ld_relaxed_u32(claim + (slot >> 5));
-              if (far_old[j] & bit) { pre |= 1u << j; continue; }
+            old[j] = atomicOr(claim + (slot >> 5), 1u << ((u32)slot & 31u));
+          }
+#pragma unroll
+        for (int j = 0; j < IPT; j++)
+          if (fp >> j & 1u) {
+            const u64 slot = (((v[j] & key_mask) & mask) + att[j]) & mask;
+            const u32 b = (u32)slot & 31u;
+            if (!(old[j] >> b & 1u)) {
+              table[slot] = v[j];
+              fp &= ~(1u << j);
+            } else {
+              ++steps;
+              att[j] += gt_advance(old[j] | (1u << b), b);
+              if (att[j] >= L) { fp &= ~(1u << j); failed_bits |= 1u << j; }  // AtomicHashBuild.hpp:62-63
             }
-            far_old[j] = atomicOr(claim + (slot >> 5), bit);
+          }
+      }
+      pend &= ~farbits;
+    }
+    __syncthreads();  // the shared arrays are cleared
+
+    // ---- in-band tuples: probe in shared memory, commit, repeat for what another CTA took -------------
+    bool first = true;
+    while (true) {
+      u32 tent = 0;  // bit j: tentatively placed in this iteration
+#pragma unroll
+      for (int j = 0; j < IPT; j++) {
+        bool go = pend >> j & 1u;
+        u32 cur = rel[j] + att[j];
+        u32 prev = 0, bit = 1u << (cur & 31u);
+        bool asked = false;
+        if (first) {
+          // First attempt of a warp's row, warp-cooperative: rows of a sorted or locally shuffled relation
+          // span at most three bitmap words -- their bits are OR-reduced (full-mask REDUX) and set by ONE
+          // shared-memory atomic per word instead of 32 atomics serialising on one address.  Rows that ask
+          // for a bit twice (duplicate keys) or span more words take one atomic per lane.
+          const u32 word = go ? cur >> 5 : kGtFar;
+          const u32 wmin = __reduce_min_sync(0xffffffffu, word);
+          if (wmin != kGtFar) {
+            const u32 d = word - wmin;  // (idle lanes: huge)
+            if (__all_sync(0xffffffffu, !go || d <= 2u)) {
+              const u32 or0 = __reduce_or_sync(0xffffffffu, go && d == 0u ? bit : 0u);
+              const u32 or1 = __reduce_or_sync(0xffffffffu, go && d == 1u ? bit : 0u);
+              const u32 or2 = __reduce_or_sync(0xffffffffu, go && d == 2u ? bit : 0u);
+              if (__popc(or0) + __popc(or1) + __popc(or2) == __popc(__ballot_sync(0xffffffffu, go))) {
+                u32 p = 0;
+                const u32 mine = lane == 0 ? or0 : lane == 1 ? or1 : or2;
+                if (lane < 3 && mine) p = atomicOr(&s_occ[wmin + lane], mine);
+                const u32 p0 = __shfl_sync(0xffffffffu, p, 0), p1 = __shfl_sync(0xffffffffu, p, 1),
+                          p2 = __shfl_sync(0xffffffffu, p, 2);
+                // what the word looked like before + everything this row asked for (all of it ends up occupied)
+                prev = d == 0u ? p0 : d == 1u ? p1 : p2;
+                if (go) {
+                  asked = true;
+                  if (prev & bit) prev |= d == 0u ? or0 : d == 1u ? or1 : or2;
+                }
+              }
+            }
           }
         }
+        // the tuple's own probing: AtomicHashBuild.hpp:46-60 against the shared-memory image
+        while (go) {
+          if (!asked) prev = atomicOr(&s_occ[cur >> 5], bit);
+          asked = false;
+          if (!(prev & bit)) { tent |= 1u << j; break; }
+          ++steps;
+          att[j] += gt_advance(prev | bit, cur & 31u);
+          if (att[j] >= L) {  // budget exhausted
+            pend &= ~(1u << j);
+            failed_bits |= 1u << j;
+            break;
+          }
+          cur = rel[j] + att[j];
+          bit = 1u << (cur & 31u);
+        }
       }
-#pragma unroll
-      for (int j = 0; j < IPT; j++) {
-        // warp-uniform: the aggregation below is a warp collective
-        const bool inb = (pend & ~farbits) >> j & 1u;
-        if (!__any_sync(0xffffffffu, inb)) continue;
-        const u32 cur = rel[j] + att[j];
-        const u32 bit = 1u << (cur & 31u);
-        bool ask = inb;
-        if (STATS && inb) {  // peek: an occupied slot costs a step, not a retry
-          peeked[j] = ld_relaxed_u32(gband + (cur >> 5));
-          if (peeked[j] & bit) { pre |= 1u << j; ask = false; }
+      first = false;
+      __syncthreads();
+      // commit: one global atomic per word the tile claimed something new in
+      for (u32 wi = tid; wi < nwords; wi += kGtThreads) {
+        const u32 fresh = s_occ[wi] & ~s_theirs[wi] & ~s_mine[wi];
+        if (fresh) {
+          const u32 old = atomicOr(gband + wi, fresh);
+          s_mine[wi] |= fresh & ~old;
+          s_theirs[wi] |= old & ~s_mine[wi];
+          s_occ[wi] |= old;
         }
-        // Lanes of a run (consecutive lanes, same bitmap word: every lane of a sorted or locally shuffled
-        // relation) OR their bits together and the run's first lane sets them with ONE shared-memory atomic
-        // (32 lanes on one word would serialise 32-fold).  A run that asks for a bit twice (duplicate keys)
-        // falls back to one atomic per lane: its return value is what tells the duplicates apart.
-        const u32 word = ask ? cur >> 5 : kGtFar - lane;  // dummies never form a run
-        const u32 prevw = __shfl_up_sync(0xffffffffu, word, 1);
-        const u32 heads = __ballot_sync(0xffffffffu, lane == 0 || word != prevw);
-        const u32 le = 0xffffffffu >> (31u - lane);
-        const u32 start = 31u - __clz(heads & le);
-        const u32 above = heads & ~le;
-        const u32 end = above ? __ffs(above) - 1u : 32u;
-        const u32 peers = (end == 32u ? 0xffffffffu : (1u << end) - 1u) & ~((1u << start) - 1u);
-        const u32 ormask = __reduce_or_sync(peers, ask ? bit : 0u);
-        u32 prev = 0;
-        if (__popc(ormask) == __popc(peers)) {  // uniform over the run
-          if (lane == start) prev = atomicOr(&s_want[word], ormask);
-          prev = __shfl_sync(peers, prev, start);
-        } else if (ask) {
-          prev = atomicOr(&s_want[word], bit);
-        }
-        if (ask && (prev & bit)) pre |= 1u << j;  // somebody in the tile asked first
       }
       __syncthreads();
-      // one global atomic per non-empty word of the band
-#pragma unroll
-      for (int k = 0; k < kGtBandWords / kGtThreads; k++) {
-        const u32 wi = k * kGtThreads + tid;
-        const u32 want = s_want[wi];
-        if (want) s_old[wi] = atomicOr(gband + wi, want);
-      }
-      __syncthreads();
+      u32 lost = 0;
 #pragma unroll
       for (int j = 0; j < IPT; j++) {
-        if (pend >> j & 1u) {
-          u32 b, view;
-          bool won;
-          if (farbits >> j & 1u) {
-            const u64 slot = (((v[j] & key_mask) & mask) + att[j]) & mask;
-            b = (u32)slot & 31u;
-            view = far_old[j] | (1u << b);
-            won = !(pre >> j & 1u) && !(far_old[j] >> b & 1u);
+        if (tent >> j & 1u) {
+          const u32 cur = rel[j] + att[j];
+          if (s_theirs[cur >> 5] >> (cur & 31u) & 1u) {
+            lost |= 1u << j;  // another CTA got this slot first: probe on (the bit now reads as occupied)
+            if (STATS) ++retries;
           } else {
-            const u32 cur = rel[j] + att[j];
-            const u32 wi = cur >> 5;
-            b = cur & 31u;
-            const u32 want = s_want[wi];
-            const u32 old = want ? s_old[wi] : 0u;  // (STATS: a word nobody asked for was never claimed this round)
-            view = old | want | (STATS ? peeked[j] : 0u);
-            won = !(pre >> j & 1u) && !(old >> b & 1u);
-          }
-          if (STATS && !(pre >> j & 1u) && !won) ++retries;  // free when looked at, taken when claimed
-          if (won) {
             table[(((v[j] & key_mask) & mask) + att[j]) & mask] = v[j];
             pend &= ~(1u << j);
-          } else {
-            // on to the next slot the view shows free; none left in this word: the next word's first slot.
-            // Everything skipped is occupied (or asked for by this tile, hence occupied when the round ends),
-            // so the probe's walk from the home slot never meets a gap before the tuple.
-            ++steps;
-            const u32 freeb = b == 31u ? 0u : (~view & (0xffffffffu << (b + 1u)));
-            att[j] += freeb ? (u32)__ffs(freeb) - 1u - b : 32u - b;
-            if (att[j] >= L) {  // AtomicHashBuild.hpp:62-63: budget exhausted
-              pend &= ~(1u << j);
-              failed_bits |= 1u << j;
-            }
           }
         }
       }
+      if (!__syncthreads_or(lost != 0)) break;
     }
 
     if (STATS) {
@@ -512,6 +532,36 @@ __device__ __forceinline__ void ld_sector(const u64* p, u64 (&c)[4]) {
                : "=l"(c[0]), "=l"(c[1]), "=l"(c[2]), "=l"(c[3]) : "l"(p));
 }
 
+// home-only path: launched in front of gt_probe_kernel, exactly one of the two does the work
+template <int IPT>
+__global__ void __launch_bounds__(kGtThreads)
+gt_probe_home_kernel(const u64* __restrict__ S, u64 m, const u64* __restrict__ table, u64 mask, u64 key_mask,
+                     u64* __restrict__ ctr) {
+  if (ctr[C_CONFLICTS] != 0 || ctr[C_PROBE_STEPS] != 0) return;
+  constexpr int TILE = kGtThreads * IPT;
+  const u32 tid = threadIdx.x;
+  u64 checksum = 0;
+  u32 wmatches = 0;
+  const u64 nchunks = (m + TILE - 1) / TILE;
+  for (u64 c = blockIdx.x; c < nchunks; c += gridDim.x) {
+    const u64 base = c * TILE + tid;
+    u64 s[IPT], cur[IPT];
+#pragma unroll
+    for (int j = 0; j < IPT; j++) {
+      const u64 i = base + (u64)j * kGtThreads;
+      s[j] = i < m ? ld_stream(S + i) : 0ull;
+    }
+#pragma unroll
+    for (int j = 0; j < IPT; j++) cur[j] = s[j] ? __ldg(table + ((s[j] & key_mask) & mask)) : 0ull;
+#pragma unroll
+    for (int j = 0; j < IPT; j++)
+      if (cur[j] != 0ull && (cur[j] & key_mask) == (s[j] & key_mask)) { ++wmatches; checksum += cur[j] + s[j]; }
+  }
+  u64 v[3] = {(u64)wmatches, checksum, (u64)wmatches};
+  u64* const d[3] = {ctr + C_MATCHES, ctr + C_CHECKSUM, ctr + C_WINDOW_MATCHES};
+  block_sum_atomic<3, kGtThreads>(v, d);
+}
+
 template <int IPT>
 __global__ void __launch_bounds__(kGtThreads, 3)
 gt_probe_kernel(const u64* __restrict__ S, u64 m, const u64* __restrict__ table, u64 mask, u64 key_mask, u32 L,
@@ -520,7 +570,7 @@ gt_probe_kernel(const u64* __restrict__ S, u64 m, const u64* __restrict__ table,
   constexpr int TILE = kGtThreads * IPT;
   const u32 tid = threadIdx.x, lane = lane_id(), warp = tid >> 5;
   const u64 ovf_count = ctr[C_CONFLICTS];
-  const bool home_only = ovf_count == 0 && ctr[C_PROBE_STEPS] == 0;
+  if (ovf_count == 0 && ctr[C_PROBE_STEPS] == 0) return;  // gt_probe_home_kernel took the probe
   u64 omask = 0;
   if (ovf_count) {
     u64 slots = ovf_slots_for(ovf_count);
@@ -538,15 +588,6 @@ gt_probe_kernel(const u64* __restrict__ S, u64 m, const u64* __restrict__ table,
     for (int j = 0; j < IPT; j++) {
       const u64 i = base + (u64)j * 32;
       s[j] = i < m ? ld_stream(S + i) : 0ull;
-    }
-    if (home_only) {
-      u64 cur[IPT];
-#pragma unroll
-      for (int j = 0; j < IPT; j++) cur[j] = s[j] ? __ldg(table + ((s[j] & key_mask) & mask)) : 0ull;
-#pragma unroll
-      for (int j = 0; j < IPT; j++)
-        if (cur[j] != 0ull && (cur[j] & key_mask) == (s[j] & key_mask)) { ++wmatches; checksum += cur[j] + s[j]; }
-      continue;
     }
     u32 full = 0;  // bit j: window exhausted without an empty slot
     // dense: homes of the warp = h0 .. h0 + IPT*32 - 1, no wrap-around, every tuple valid
@@ -616,21 +657,36 @@ gt_probe_kernel(const u64* __restrict__ S, u64 m, const u64* __restrict__ table,
         }
       }
     }
-    // the window is full: tuples of this home slot may have overflowed
+    // the window is full: tuples of this home slot may have overflowed.  The chains of all of a thread's
+    // tuples are walked together, one slot each per round (a walk is a chain of dependent L2 / DRAM loads).
     if (ovf_count && full) {
+      u32 act = 0;
+      u64 os[IPT];
 #pragma unroll
       for (int j = 0; j < IPT; j++) {
         if (full >> j & 1u) {
           const u64 key = s[j] & key_mask;
           const u64 home = key & mask;
-          if (!(__ldg(ovfmap + (home >> 5)) >> ((u32)home & 31u) & 1u)) continue;
-          u64 os = ovf_hash(key, omask);
+          if (__ldg(ovfmap + (home >> 5)) >> ((u32)home & 31u) & 1u) {
+            act |= 1u << j;
+            os[j] = ovf_hash(key, omask);
+          }
+        }
+      }
 #pragma unroll 1
-          while (true) {
-            const u64 o = __ldg(ovf_table + os);
-            if (o == 0ull) break;
-            if ((o & key_mask) == key) { ++omatches; checksum += o + s[j]; }
-            os = (os + 1) & omask;
+      while (act) {
+        u64 o[IPT];
+#pragma unroll
+        for (int j = 0; j < IPT; j++)
+          if (act >> j & 1u) o[j] = __ldg(ovf_table + os[j]);
+#pragma unroll
+        for (int j = 0; j < IPT; j++) {
+          if (act >> j & 1u) {
+            if (o[j] == 0ull) act &= ~(1u << j);
+            else {
+              if ((o[j] & key_mask) == (s[j] & key_mask)) { ++omatches; checksum += o[j] + s[j]; }
+              os[j] = (os[j] + 1) & omask;
+            }
           }
         }
       }

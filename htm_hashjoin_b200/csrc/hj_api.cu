@@ -74,6 +74,7 @@ const Env& env() { return g_env; }
 
 }  // namespace
 
+struct Xchg;
 struct hj_handle {
   hj_config cfg;
   int device = 0;
@@ -100,6 +101,7 @@ struct hj_handle {
   DevBuf peer_ptrs;  // device copy of the peers' pass-1 buffer pointers (fused exchange)
   DevBuf tasks;      // join tasks (partition, S slice) of rx_join32 (skew handling)
   DevBuf mat_cnt;    // per-partition pair counts / offsets of the materialising join
+  struct Xchg* xc = nullptr;  // pipelined exchange state (hj_xchg_*)
   u32 launches = 0;
   u64 allocs = 0;  // cudaMalloc calls made by ensure() over the handle's life (hj_alloc_count)
   char err[256];
@@ -216,15 +218,23 @@ int launch_build(hj_handle* h, const u64* R, const SegMap& sm, bool nocc, bool s
 
 template <int IPT>
 int launch_probe_t(hj_handle* h, const u64* S, u64 m) {
+  if (m == 0) return HJ_OK;
+  {  // every tuple sits in its home slot (decided on the device from the build's counters): one read per S tuple
+    constexpr int HIPT = IPT >= 4 ? 8 : IPT;
+    auto k = gt_probe_home_kernel<HIPT>;
+    int grid = grid_for(h, (const void*)k, kGtThreads, 0);
+    const u64 chunks = (m + kGtThreads * HIPT - 1) / (kGtThreads * HIPT);
+    if ((u64)grid > chunks) grid = (int)chunks;
+    k<<<grid, kGtThreads, 0, h->stream>>>(S, m, h->table.p, h->mask, h->cfg.key_mask, h->ctr);
+  }
   auto k = gt_probe_kernel<IPT>;
   int grid = grid_for(h, (const void*)k, kGtThreads, 0);
   u64 chunks = (m + kGtThreads * IPT - 1) / (kGtThreads * IPT);
-  if (chunks == 0) return HJ_OK;
   if ((u64)grid > chunks) grid = (int)chunks;
   k<<<grid, kGtThreads, 0, h->stream>>>(S, m, h->table.p, h->mask, h->cfg.key_mask, h->cfg.probe_length,
                                         h->ovf_table.p, h->ovf_table.cap, reinterpret_cast<const u32*>(h->ovfmap.p),
                                         h->ctr);
-  h->launches++;
+  h->launches += 2;
   CK(cudaGetLastError());
   return HJ_OK;
 }
@@ -1133,6 +1143,8 @@ int run_global_join(hj_handle* h, const u64* dR, u64 n, const u64* dS, u64 m, bo
 
 }  // namespace
 
+void xchg_free(hj_handle* h);  // defined with the pipelined exchange at the end of this file
+
 // ===========================================================================
 // C ABI
 // ===========================================================================
@@ -1216,6 +1228,7 @@ void hj_destroy(hj_handle* h) {
   if (!h) return;
   cudaSetDevice(h->device);
   if (h->stream) cudaStreamSynchronize(h->stream);
+  xchg_free(h);
   DevBuf* bufs[] = {&h->table, &h->ovf_table, &h->ovf_list, &h->claim, &h->ovfmap, &h->stageR, &h->stageS, &h->flush,
                     &h->peer_ptrs, &h->tasks, &h->mat_cnt};
   for (DevBuf* b : bufs)
@@ -1831,6 +1844,354 @@ int hj_sync(hj_handle* h) {
   CK(cudaSetDevice(h->device));
   CK(cudaStreamSynchronize(h->stream));
   CK(cudaStreamSynchronize(h->copy_stream));
+  return HJ_OK;
+}
+
+}  // extern "C"
+
+// ===========================================================================
+// Pipelined exchange over the copy engines (multi-GPU)
+// ===========================================================================
+// The fused exchange of round 1 stores over NVLink from the SMs: the whole chip scatters for 13.4 ms at
+// N=8 and only then joins for 7.9 ms.  Here the SMs never touch the link:
+//   * a stage (stage 0 = this rank's slice of R, stages 1..C = C chunks of its slice of S) is scattered
+//     LOCALLY, at HBM speed, by (owner GPU, low b1 key bits) into per-destination blocks -- the same
+//     tile-sorting kernel, same fixed-capacity regions, every destination pointer local;
+//   * one stream per peer then ships block `dest` of the stage to rank dest's receive window with a plain
+//     device-to-device copy (copy engines over NVLink through the CUDA-IPC mapping), followed by the
+//     block's fill levels (the scatter's final cursors) and a flag word carrying the step's epoch;
+//   * the compute stream scatters stage t+1, then waits (rx_xchg_wait_kernel, bounded) for the flags of
+//     stage t from every peer, runs pass 2 on what arrived (one parent per (source, low bits) region) and
+//     joins it -- so the copies of stage t+1 run under pass 2 + join of stage t, and nothing but the final
+//     counter read-back ever synchronises with the host.
+// Contract: all ranks call hj_xchg_start with the same, strictly increasing epoch, and nobody starts epoch
+// e+1 before every rank finished epoch e (the all-reduce of the result is that barrier).
+struct XStage {
+  u64 n_local, cap, stride, recv_off, fill_off, flag_off;
+  u64* send;
+  cudaEvent_t scattered;
+  cudaEvent_t ev[8];  // scatter0/1, wait0/1, pass2 0/1, join end, spare
+};
+constexpr u32 kXMaxStages = 17;
+constexpr u64 kXScratch = (u64)kScThreads * 32 + 2;  // diverted claims of one scatter tile (+ alignment)
+struct Xchg {
+  u32 G = 0, rank = 0, b1 = 0, F1 = 0, nstages = 0, domain_bits = 0;
+  bool connected = false, started = false;
+  u64 window_elems = 0, epoch = 0;
+  u64* window = nullptr;
+  u64* peer_window[kScMaxPeers];
+  XStage st[kXMaxStages];
+  u64 *cur = nullptr, *caps_dev = nullptr, *epoch_word = nullptr, *ones = nullptr;
+  u64** dest_ptrs = nullptr;  // device [nstages][kScMaxPeers]: where the local scatter puts block `dest`
+  cudaStream_t cs[kScMaxPeers];
+  RadixPlan pl;
+  u64 C2R = 0, C2S = 0, nR = 0, mS = 0;
+  cudaEvent_t ev_begin, ev_end;
+};
+
+static u64 xchg_region_cap(u64 n_stage, u32 G, u32 F1) {
+  const u64 mean = n_stage / ((u64)G * F1) + 1;
+  u64 r = 1;
+  while (r * r < mean) r++;
+  return (mean + 8 * r + 64 + 1) & ~1ull;
+}
+
+void xchg_free(hj_handle* h) {
+  Xchg* x = h->xc;
+  if (!x) return;
+  for (u32 p = 0; p < x->G; p++)
+    if (x->cs[p]) { cudaStreamSynchronize(x->cs[p]); cudaStreamDestroy(x->cs[p]); }
+  for (u32 t = 0; t < x->nstages; t++) {
+    if (x->st[t].send) cudaFree(x->st[t].send);
+    if (x->st[t].scattered) cudaEventDestroy(x->st[t].scattered);
+    for (cudaEvent_t e : x->st[t].ev)
+      if (e) cudaEventDestroy(e);
+  }
+  void* bufs[] = {x->window, x->cur, x->caps_dev, x->epoch_word, x->ones, x->dest_ptrs};
+  for (void* b : bufs)
+    if (b) cudaFree(b);
+  if (x->ev_begin) cudaEventDestroy(x->ev_begin);
+  if (x->ev_end) cudaEventDestroy(x->ev_end);
+  delete x;
+  h->xc = nullptr;
+}
+
+extern "C" {
+
+int hj_xchg_create(hj_handle* h, uint32_t n_ranks, uint32_t rank, uint64_t n_local, uint64_t m_local,
+                   uint32_t s_chunks, uint32_t domain_bits, void** window, uint64_t* window_bytes) {
+  if (!h || !window || !window_bytes || n_ranks < 2 || n_ranks > (uint32_t)kScMaxPeers || (n_ranks & (n_ranks - 1)) ||
+      rank >= n_ranks || !n_local || !m_local || s_chunks < 1 || s_chunks + 1 > kXMaxStages || domain_bits > 62 ||
+      m_local % (2ull * s_chunks))
+    return HJ_EINVAL;
+  if (h->cfg.algo != HJ_ALGO_RADIX) return HJ_ESTATE;
+  CK(cudaSetDevice(h->device));
+  xchg_free(h);
+  int rc;
+  RadixChoice ch;
+  if ((rc = choose_radix(h, n_local, true, true, true, false, false, &ch))) return rc;
+  if (!ch.opt || ch.pl.passes != 2 || (n_ranks << ch.pl.b1) > (uint32_t)kScParentCache) {
+    snprintf(h->err, sizeof(h->err), "hj_xchg_create: needs the 2-pass shared-memory plan with n_ranks << pass1_bits <= %d "
+             "(got bits %u, pass 1 %u)", kScParentCache, ch.pl.bits, ch.pl.b1);
+    return HJ_EINVAL;
+  }
+  Xchg* x = new (std::nothrow) Xchg();
+  if (!x) return HJ_ENOMEM;
+  memset(x->peer_window, 0, sizeof(x->peer_window));
+  memset(x->st, 0, sizeof(x->st));
+  memset(x->cs, 0, sizeof(x->cs));
+  x->ev_begin = x->ev_end = nullptr;
+  h->xc = x;
+  x->G = n_ranks; x->rank = rank; x->pl = ch.pl; x->b1 = ch.pl.b1; x->F1 = 1u << ch.pl.b1;
+  x->nstages = 1 + s_chunks; x->domain_bits = domain_bits;
+  x->nR = n_local; x->mS = m_local / s_chunks;
+  x->C2R = opt_region_cap(x->nR, ch.pl.bits);
+  x->C2S = opt_region_cap(x->mS, ch.pl.bits);
+  const u32 G = x->G, F1 = x->F1, gf = G * F1;
+  // window layout (identical on every rank): the stages' G source blocks, then fill levels, then flags
+  u64 off = 0;
+  for (u32 t = 0; t < x->nstages; t++) {
+    XStage& st = x->st[t];
+    st.n_local = t == 0 ? n_local : x->mS;
+    st.cap = xchg_region_cap(st.n_local, G, F1);
+    st.stride = ((u64)F1 * st.cap + kXScratch + 31) & ~31ull;
+    st.recv_off = off;
+    off += (u64)G * st.stride;
+  }
+  for (u32 t = 0; t < x->nstages; t++) { x->st[t].fill_off = off; off += (gf + 31) & ~31u; }
+  for (u32 t = 0; t < x->nstages; t++) { x->st[t].flag_off = off; off += 32; }
+  x->window_elems = off;
+  auto fail = [&](int code) { xchg_free(h); return code; };
+#define XCK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { \
+    snprintf(h->err, sizeof(h->err), "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+    return fail(e_ == cudaErrorMemoryAllocation ? HJ_ENOMEM : HJ_ECUDA); } } while (0)
+  XCK(cudaMalloc(&x->window, off * sizeof(u64)));
+  h->allocs++;
+  XCK(cudaMemset(x->window + x->st[0].fill_off, 0, (off - x->st[0].fill_off) * sizeof(u64)));  // fills + flags
+  for (u32 t = 0; t < x->nstages; t++) {
+    XCK(cudaMalloc(&x->st[t].send, (u64)G * x->st[t].stride * sizeof(u64)));
+    h->allocs++;
+    XCK(cudaEventCreateWithFlags(&x->st[t].scattered, cudaEventDisableTiming));
+    for (cudaEvent_t& e : x->st[t].ev) XCK(cudaEventCreate(&e));
+  }
+  XCK(cudaEventCreate(&x->ev_begin));
+  XCK(cudaEventCreate(&x->ev_end));
+  XCK(cudaMalloc(&x->cur, (u64)x->nstages * gf * sizeof(u64)));
+  XCK(cudaMalloc(&x->caps_dev, x->nstages * sizeof(u64)));
+  XCK(cudaMalloc(&x->epoch_word, 32));
+  XCK(cudaMalloc(&x->ones, (u64)x->nstages * 4 * sizeof(u64)));
+  XCK(cudaMalloc(&x->dest_ptrs, (u64)x->nstages * kScMaxPeers * sizeof(u64*)));
+  {
+    u64 caps[kXMaxStages], ones[kXMaxStages * 4];
+    const u64 tile = (u64)kScThreads * 16;
+    for (u32 t = 0; t < x->nstages; t++) {
+      caps[t] = x->st[t].cap;
+      const u64 n = x->st[t].n_local;
+      ones[4 * t] = 0; ones[4 * t + 1] = n; ones[4 * t + 2] = 0; ones[4 * t + 3] = (n + tile - 1) / tile;
+    }
+    XCK(cudaMemcpy(x->caps_dev, caps, x->nstages * sizeof(u64), cudaMemcpyHostToDevice));
+    XCK(cudaMemcpy(x->ones, ones, x->nstages * 4 * sizeof(u64), cudaMemcpyHostToDevice));
+  }
+  for (u32 p = 0; p < G; p++)
+    if (p != rank) XCK(cudaStreamCreateWithFlags(&x->cs[p], cudaStreamNonBlocking));
+#undef XCK
+  // pass 2 + join buffers for what arrives (expected: as much as was sent)
+  if ((rc = ensure_rel(h, h->rb[0], x->nR, x->pl, true, true, G))) return fail(rc);
+  if ((rc = ensure_rel(h, h->rb[1], x->mS, x->pl, true, true, G))) return fail(rc);
+  {
+    u64 slice = 4 * (x->mS >> x->pl.bits);
+    if (slice < 32768) slice = 32768;
+    if ((rc = ensure(h, h->tasks, (1ull << x->pl.bits) + 2 * x->mS / slice + 1))) return fail(rc);
+  }
+  *window = x->window;
+  *window_bytes = off * sizeof(u64);
+  return HJ_OK;
+}
+
+int hj_xchg_connect(hj_handle* h, void* const* peer_windows) {
+  if (!h || !h->xc || !peer_windows) return HJ_EINVAL;
+  Xchg* x = h->xc;
+  CK(cudaSetDevice(h->device));
+  u64* dest[kXMaxStages * kScMaxPeers];
+  memset(dest, 0, sizeof(dest));
+  for (u32 p = 0; p < x->G; p++) {
+    x->peer_window[p] = p == x->rank ? x->window : (u64*)peer_windows[p];
+    if (!x->peer_window[p] || ((uintptr_t)x->peer_window[p] & 15)) return HJ_EINVAL;
+  }
+  for (u32 t = 0; t < x->nstages; t++)
+    for (u32 d = 0; d < x->G; d++)  // the own block is written in place, the others into the send buffer
+      dest[t * kScMaxPeers + d] = d == x->rank ? x->window + x->st[t].recv_off + (u64)x->rank * x->st[t].stride
+                                               : x->st[t].send + (u64)d * x->st[t].stride;
+  CK(cudaMemcpy(x->dest_ptrs, dest, (u64)x->nstages * kScMaxPeers * sizeof(u64*), cudaMemcpyHostToDevice));
+  x->connected = true;
+  return HJ_OK;
+}
+
+}  // extern "C"
+
+namespace {
+
+// local scatter of stage t + the copies that ship it
+int xchg_scatter_stage(hj_handle* h, Xchg* x, u32 t, const u64* in) {
+  XStage& st = x->st[t];
+  const u32 G = x->G, F1 = x->F1, gf = G * F1, F = gf;
+  Digit dg;
+  memset(&dg, 0, sizeof(dg));
+  dg.key_mask = h->cfg.key_mask; dg.mode = 3; dg.ndest = G; dg.domain_bits = x->domain_bits; dg.b1 = x->b1;
+  constexpr int IPT = 16;  // 8192-tuple tiles, two CTAs per SM: the HBM-speed shape of the local passes
+  const u32 tile = kScThreads * IPT;
+  auto k = rx_scatter_kernel<IPT, 2, true, 1, true>;
+  const size_t smem = (size_t)tile * 8 + (size_t)F * 16 + sc_bulk_extra(F);
+  CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int grid = grid_for(h, (const void*)k, kScThreads, smem);
+  const u64 ntiles = (st.n_local + tile - 1) / tile;
+  if ((u64)grid > ntiles) grid = (int)(ntiles ? ntiles : 1);
+  const u64* one = x->ones + 4 * t;
+  ScOpt so{one + 1, st.cap, (u64)F1 * st.cap, h->ctr, 0, F1 - 1u, 1u, 0u};
+  cudaEventRecord(st.ev[0], h->stream);
+  k<<<grid, kScThreads, smem, h->stream>>>(in, nullptr, dg, F, 1, one, one + 2, x->cur + (u64)t * gf,
+                                           reinterpret_cast<u64* const*>(x->dest_ptrs + (u64)t * kScMaxPeers), so);
+  h->launches++;
+  CK(cudaGetLastError());
+  cudaEventRecord(st.ev[1], h->stream);
+  CK(cudaEventRecord(st.scattered, h->stream));
+  // own block: written in place by the scatter; its fill levels go next to the others'
+  CK(cudaMemcpyAsync(x->window + st.fill_off + (u64)x->rank * F1, x->cur + (u64)t * gf + (u64)x->rank * F1,
+                     F1 * sizeof(u64), cudaMemcpyDeviceToDevice, h->stream));
+  for (u32 p = 0; p < G; p++) {
+    if (p == x->rank) continue;
+    cudaStream_t cs = x->cs[p];
+    u64* pw = x->peer_window[p];
+    CK(cudaStreamWaitEvent(cs, st.scattered, 0));
+    CK(cudaMemcpyAsync(pw + st.recv_off + (u64)x->rank * st.stride, st.send + (u64)p * st.stride,
+                       (u64)F1 * st.cap * sizeof(u64), cudaMemcpyDeviceToDevice, cs));
+    CK(cudaMemcpyAsync(pw + st.fill_off + (u64)x->rank * F1, x->cur + (u64)t * gf + (u64)p * F1, F1 * sizeof(u64),
+                       cudaMemcpyDeviceToDevice, cs));
+    CK(cudaMemcpyAsync(pw + st.flag_off + x->rank, x->epoch_word, sizeof(u64), cudaMemcpyDeviceToDevice, cs));
+  }
+  return HJ_OK;
+}
+
+int xchg_wait_stage(hj_handle* h, Xchg* x, u32 t) {
+  XStage& st = x->st[t];
+  cudaEventRecord(st.ev[2], h->stream);
+  rx_xchg_wait_kernel<<<1, 32, 0, h->stream>>>(x->window + st.flag_off, x->G, x->rank, x->epoch, h->ctr,
+                                               10ull * 1000 * 1000 * 1000);
+  h->launches++;
+  CK(cudaGetLastError());
+  cudaEventRecord(st.ev[3], h->stream);
+  return HJ_OK;
+}
+
+// pass 2 of what stage t delivered: one parent per (source, low bits) region of the window
+int xchg_pass2_stage(hj_handle* h, Xchg* x, u32 t) {
+  XStage& st = x->st[t];
+  RelBufs& rb = h->rb[t == 0 ? 0 : 1];
+  const RadixPlan& pl = x->pl;
+  const u32 nb = 1u << pl.bits, F1 = x->F1, F2 = 1u << pl.b2, nparent = x->G * F1;
+  const u64 C2 = t == 0 ? x->C2R : x->C2S;
+  const u32 ipt = sc_opt_ipt();
+  const u32 tile = kScThreads * ipt;
+  cudaEventRecord(st.ev[4], h->stream);
+  rx_opt_init_kernel<<<(nb + 255) / 256, 256, 0, h->stream>>>(rb.pcur.p, 0, 0, rb.cursors.p, nb, C2);
+  rx_xchg_parents_kernel<<<1, 1024, 0, h->stream>>>(x->window + st.fill_off, nparent, F1, st.cap, st.stride, tile,
+                                                    rb.poff.p, rb.pend.p, rb.ptiles.p);
+  h->launches += 2;
+  const bool bulk2 = sc_bulk_for(F2, tile);
+  ScKernel k = ipt == 32 ? sc_opt_kernel<32>(1, bulk2) : ipt == 16 ? sc_opt_kernel<16>(1, bulk2) : sc_opt_kernel<8>(1, bulk2);
+  const size_t smem = (size_t)tile * 8 + (size_t)F2 * 16 + (bulk2 ? sc_bulk_extra(F2) : 0);
+  CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int grid = grid_for(h, (const void*)k, kScThreads, smem);
+  Digit d2;
+  memset(&d2, 0, sizeof(d2));
+  d2.key_mask = h->cfg.key_mask; d2.mode = 0; d2.shift = pl.b1; d2.bits = pl.b2;
+  ScOpt o{rb.pend.p, C2, (u64)nb * C2, h->ctr, 0, F1 - 1u, 0, 0};
+  k<<<grid, kScThreads, smem, h->stream>>>(x->window + st.recv_off, rb.out.p, d2, F2, nparent, rb.poff.p, rb.ptiles.p,
+                                           rb.cursors.p, nullptr, o);
+  h->launches++;
+  CK(cudaGetLastError());
+  cudaEventRecord(st.ev[5], h->stream);
+  return HJ_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int hj_xchg_start(hj_handle* h, const uint64_t* R, const uint64_t* S, uint64_t epoch) {
+  if (!h || !h->xc || !R || !S || !is_device_ptr(R) || !is_device_ptr(S)) return HJ_EINVAL;
+  Xchg* x = h->xc;
+  if (!x->connected || x->started || epoch <= x->epoch) return HJ_ESTATE;
+  if (need_aligned16(h, R, "hj_xchg_start(R)") || need_aligned16(h, S, "hj_xchg_start(S)")) return HJ_EINVAL;
+  CK(cudaSetDevice(h->device));
+  reset_events(h);
+  h->built = false;
+  int rc;
+  const u32 gf = x->G * x->F1, C = x->nstages - 1;
+  x->epoch = epoch;
+  CK(cudaEventRecord(x->ev_begin, h->stream));
+  CK(cudaMemsetAsync(h->ctr, 0, C_COUNT * sizeof(u64), h->stream));
+  rx_xchg_init_kernel<<<(x->nstages * gf + 255) / 256, 256, 0, h->stream>>>(x->cur, x->nstages, gf, x->F1 - 1u,
+                                                                            x->caps_dev, x->epoch_word, epoch);
+  h->launches++;
+  auto stage_in = [&](u32 t) { return t == 0 ? (const u64*)R : (const u64*)S + (u64)(t - 1) * x->mS; };
+  // one stage ahead: stage t+1 is scattered (and starts travelling) before stage t is waited for
+  if ((rc = xchg_scatter_stage(h, x, 0, stage_in(0)))) return rc;
+  if ((rc = xchg_scatter_stage(h, x, 1, stage_in(1)))) return rc;
+  const u64 per = (x->nR >> x->pl.bits) + 1;
+  u64 need = per + 64;
+  for (u64 r = 1; r * r < per * 64; r++) need = per + 64 + r;
+  for (u32 c = 1; c <= C; c++) {
+    if (c + 1 <= C && (rc = xchg_scatter_stage(h, x, c + 1, stage_in(c + 1)))) return rc;
+    if (c == 1) {
+      if ((rc = xchg_wait_stage(h, x, 0))) return rc;
+      if ((rc = xchg_pass2_stage(h, x, 0))) return rc;
+    }
+    if ((rc = xchg_wait_stage(h, x, c))) return rc;
+    if ((rc = xchg_pass2_stage(h, x, c))) return rc;
+    if ((rc = launch_partition_join(h, x->pl, need, true, x->nR, true, x->mS, x->C2R, x->C2S))) return rc;
+    cudaEventRecord(x->st[c].ev[6], h->stream);
+  }
+  CK(cudaEventRecord(x->ev_end, h->stream));
+  x->started = true;
+  return HJ_OK;
+}
+
+int hj_xchg_finish(hj_handle* h, hj_result* res) {
+  if (!h || !h->xc) return HJ_EINVAL;
+  Xchg* x = h->xc;
+  if (!x->started) return HJ_ESTATE;
+  CK(cudaSetDevice(h->device));
+  x->started = false;
+  int rc;
+  if ((rc = fetch_counters(h))) return rc;  // waits for the compute stream
+  for (u32 p = 0; p < x->G; p++)
+    if (x->cs[p]) CK(cudaStreamSynchronize(x->cs[p]));  // the send buffers are free again
+  if (res) {
+    memset(res, 0, sizeof(*res));
+    fill_common(h, res);
+    auto span = [&](cudaEvent_t a, cudaEvent_t b) { float ms = 0.f; return cudaEventElapsedTime(&ms, a, b) == cudaSuccess ? ms * 1000.f : 0.f; };
+    res->us_total = span(x->ev_begin, x->ev_end);
+    for (u32 t = 0; t < x->nstages; t++) {
+      res->us_scatter1 += span(x->st[t].ev[0], x->st[t].ev[1]);
+      res->us_reserved[0] += span(x->st[t].ev[2], x->st[t].ev[3]);  // waiting for the peers' copies
+      res->us_scatter2 += span(x->st[t].ev[4], x->st[t].ev[5]);
+      if (t) res->us_join += span(x->st[t].ev[5], x->st[t].ev[6]);
+    }
+    res->path_taken = HJ_PATH_RADIX;
+    res->radix_bits = x->pl.bits;
+    res->passes = 2;
+    res->hbm_bytes = 40ull * (x->nR + x->mS * (x->nstages - 1));  // 8*(2P+1) per tuple, P = 2
+  }
+  if (h->h_ctr[C_XCHG_TIMEOUT]) {
+    snprintf(h->err, sizeof(h->err), "hj_xchg: a peer's stage did not arrive within 10 s (epoch %llu)", x->epoch);
+    return HJ_ECUDA;
+  }
+  if (h->h_ctr[C_OPT_OVF]) {
+    snprintf(h->err, sizeof(h->err), "hj_xchg: a fixed-capacity region overflowed (skewed keys): redo the step with the exact "
+             "protocol (hj_peer_hist / hj_peer_scatter / hj_join_pass1)");
+    return HJ_EOVERFLOW;
+  }
   return HJ_OK;
 }
 

@@ -31,6 +31,7 @@ enum Counter {
   C_TILE0, C_TILE1,  // tile tickets of the L2 join kernels (rx_joinl2.cuh)
   C_NTASKS,          // join tasks = (partition, S slice) pairs built by rx_tasks_kernel (skew handling)
   C_MAT_TOTAL,       // pairs the materialising join will write (rx_joinmat.cuh, after the count pass)
+  C_XCHG_TIMEOUT,    // a peer's stage flag did not arrive in time (pipelined exchange, rx_xchg_wait_kernel)
   C_COUNT = 24
 };
 

@@ -223,6 +223,8 @@ constexpr int kScMaxPeers = 16;
 // rx_hist costs (8 of the 48 B/tuple the 2-pass join moves).  Parents are [parent_off[p],
 // parent_end[p]) (gaps between regions), and since rx_hist is gone the key-width flag
 // ctr[C_KEY_HI] is gathered here.
+// low_mask (!PEER): parents that share an output partition by their LOW bits (source-major blocks of the
+// pipelined exchange, hj_xchg_*): cursor index ((parent >> parent_shift) & low_mask) * F + digit.
 // parent_shift: parents that share an output partition -- after a histogram-free EXCHANGE the pass-1
 // partition `low` arrives as one region per source rank, parent = low * n_src + src, so the cursor
 // index is (parent >> parent_shift) * F + digit.  PEER && OPT (the sending side of that exchange):
@@ -432,7 +434,11 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
           hist[b] = 0;  // ready for the next tile (nobody reads hist after this scan)
           lbase[b] = run;
           if (c) {
-            const u64 q = (u64)(OPT ? p >> opt.parent_shift : p) * F + b;
+            // (!PEER: low_mask, when set, keeps only the low bits of the parent index -- the blocks of the
+            // pipelined exchange are source-major: parent = src * F1 + low, partition = low)
+            u32 pq = OPT ? p >> opt.parent_shift : p;
+            if (OPT && !PEER && opt.low_mask) pq &= opt.low_mask;
+            const u64 q = (u64)pq * F + b;
             u64 g = atomicAdd(cursors + q, (u64)c);
             const u64 rend = (PEER && OPT) ? ((u64)(b & opt.low_mask) * opt.ndest + opt.rank + 1) * opt.region_cap
                                            : (q + 1) * opt.region_cap;
@@ -596,6 +602,71 @@ __global__ void __launch_bounds__(1024) rx_opt_parents_kernel(const u64* __restr
   }
 }
 
+
+// ---- pipelined exchange over the copy engines (hj_xchg_*, hj_api.cu) --------------------------------
+// Stage t (0 = R, 1.. = the chunks of S) of a rank's receive window: G source blocks of `stride` tuples,
+// block src = F1 regions of cap tuples (region low = pass-1 partition `low` as scattered by rank src) + a
+// scratch zone.  fill[src * F1 + low] = the sender's final cursor for that region, RELATIVE to its block.
+// Parent p = src * F1 + low of pass 2 = [start, start + fill - low * cap), clamped to the region.
+__global__ void __launch_bounds__(1024) rx_xchg_parents_kernel(const u64* __restrict__ fill, u32 nparent, u32 F1,
+                                                                u64 cap, u64 stride, u32 tile, u64* __restrict__ poff,
+                                                                u64* __restrict__ pend, u64* __restrict__ ptiles) {
+  for (u32 p = threadIdx.x; p < nparent; p += blockDim.x) {
+    const u32 src = p / F1, low = p - src * F1;
+    const u64 start = (u64)src * stride + (u64)low * cap;
+    u64 cnt = fill[p] - (u64)low * cap;
+    if (fill[p] < (u64)low * cap || cnt > cap) cnt = cap;  // an overflowed region (flagged by its sender) is read up to its end
+    poff[p] = start;
+    pend[p] = start + cnt;
+  }
+  if (threadIdx.x == 0) poff[nparent] = (u64)(nparent / F1) * stride;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    u64 t = 0;
+    for (u32 p = 0; p < nparent; p++) {
+      ptiles[p] = t;
+      t += (pend[p] - poff[p] + tile - 1) / tile;
+    }
+    ptiles[nparent] = t;
+  }
+}
+// cursors of every stage's local scatter: cur[t * gf + (dest << b1 | low)] = low * cap[t]; epoch word
+__global__ void __launch_bounds__(256) rx_xchg_init_kernel(u64* __restrict__ cur, u32 nstages, u32 gf, u32 f1mask,
+                                                            const u64* __restrict__ caps, u64* __restrict__ epoch_word,
+                                                            u64 epoch) {
+  const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < nstages * gf) cur[i] = (u64)((i % gf) & f1mask) * caps[i / gf];
+  if (i == 0) *epoch_word = epoch;
+}
+// Wait until every peer's flag for this stage has reached `epoch` (the peers' copy engines write it after the
+// stage's data and fill levels).  One warp; gives up after timeout_ns and raises ctr[C_XCHG_TIMEOUT] so a lost
+// peer can never hang the device.
+__device__ __forceinline__ u64 ld_acquire_sys(const u64* p) {
+  u64 r;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(r) : "l"(p) : "memory");
+  return r;
+}
+__device__ __forceinline__ u64 global_timer_ns() {
+  u64 t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__global__ void __launch_bounds__(32) rx_xchg_wait_kernel(const u64* __restrict__ flags, u32 n, u32 self, u64 epoch,
+                                                           u64* __restrict__ ctr, u64 timeout_ns) {
+  const u32 i = threadIdx.x;
+  if (i < n && i != self) {
+    const u64 t0 = global_timer_ns();
+    while (ld_acquire_sys(flags + i) < epoch) {
+      if (global_timer_ns() - t0 > timeout_ns) {
+        atomicExch(ctr + C_XCHG_TIMEOUT, 1ull);
+        break;
+      }
+      __nanosleep(256);
+    }
+  }
+  __syncwarp();
+  __threadfence_system();
+}
 
 // ---- per-partition join --------------------------------------------------------
 // Dynamic shared memory: slots * 8 bytes (slots = power of two).  R_p is inserted

@@ -41,6 +41,14 @@ def reduce_result(matches, checksum, device):
     return int(out[0]), int(out[1])
 
 
+def reduce_result3(matches, checksum, flag, device):
+    """reduce_result plus a flag (e.g. 'a region overflowed here') summed over ranks."""
+    t = torch.from_numpy(np.array([matches, checksum, flag], dtype=np.uint64).view(np.int64).copy()).to(device)
+    dist.all_reduce(t)
+    out = t.cpu().numpy().view(np.uint64)
+    return int(out[0]), int(out[1]), int(out[2])
+
+
 def domain_bits_for(domain):
     """Bits of the key domain [1, domain] used by the range split."""
     return max(1, int(domain - 1).bit_length())

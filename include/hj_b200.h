@@ -100,7 +100,7 @@ typedef struct hj_result {
   /* device time of each phase, microseconds, CUDA events on the handle's stream */
   float us_total, us_h2d, us_clear, us_sample, us_build, us_probe;
   float us_hist, us_scan, us_scatter1, us_scatter2, us_join;
-  float us_reserved[5];
+  float us_reserved[5];    /* [0]: hj_xchg: device time spent waiting for the peers' copies */
   uint64_t hbm_bytes;      /* algorithmic HBM bytes of the path taken       */
   uint64_t max_partition;  /* largest R partition seen by the radix join                */
   uint64_t reserved[6];
@@ -234,6 +234,33 @@ int hj_peer_scatter_regions(hj_handle *h, const uint64_t *in, uint64_t n, uint32
 int hj_join_regions(hj_handle *h, const uint64_t *R1, uint64_t n, const uint64_t *curR, uint64_t capR,
                     const uint64_t *S1, uint64_t m, const uint64_t *curS, uint64_t capS, uint32_t n_src,
                     hj_result *res);
+
+/* ---- pipelined exchange over the copy engines (multi-GPU, round 2) ---------------------------
+ * The SMs never touch NVLink: every rank scatters a STAGE of its slices (stage 0 = R, stages 1..s_chunks =
+ * equal chunks of S by position; a join is additive over disjoint parts of S) LOCALLY by (owner GPU, low
+ * pass-1 key bits) into per-destination blocks of fixed-capacity regions; one stream per peer ships block
+ * `dest` to rank dest's receive WINDOW with a plain device-to-device copy (copy engines over NVLink through
+ * the CUDA-IPC mapping), followed by the block's fill levels and a flag word carrying the step's epoch.  The
+ * compute stream scatters stage t+1, then waits on the device (bounded: 10 s) for stage t's flags, runs radix
+ * pass 2 on what arrived (parallel_radix_join.c:402-440 with one parent per (source, low bits) region) and
+ * joins it -- the copies of stage t+1 run under pass 2 + join of stage t, and nothing but the final counter
+ * read-back synchronises with the host.
+ *   hj_xchg_create   plans the stages, allocates the send blocks and this rank's window (one allocation:
+ *                    export it with hj_ipc_export); the handle must be HJ_ALGO_RADIX with an explicit
+ *                    2-pass plan (num_partitions, passes = 2, pass1_bits) identical on all ranks,
+ *                    n_ranks a power of two, n_ranks << pass1_bits <= 256.  n_local / m_local: tuples of
+ *                    R / S every rank holds (m_local divisible by 2 * s_chunks).
+ *   hj_xchg_connect  peer_windows[r] = rank r's window as mapped here (hj_ipc_open; entry `rank` ignored).
+ *   hj_xchg_start    enqueues the whole step (R, S: device pointers to this rank's slices); returns at once.
+ *   hj_xchg_finish   waits for it; res = this rank's share of {matches, checksum} (sum them over ranks).
+ *                    HJ_EOVERFLOW: a region overflowed (skewed keys) -- redo the step with the exact protocol.
+ * All ranks pass the same, strictly increasing epoch, and nobody may start epoch e+1 before every rank
+ * finished epoch e (the all-reduce of the result is that barrier). */
+int hj_xchg_create(hj_handle *h, uint32_t n_ranks, uint32_t rank, uint64_t n_local, uint64_t m_local,
+                   uint32_t s_chunks, uint32_t domain_bits, void **window, uint64_t *window_bytes);
+int hj_xchg_connect(hj_handle *h, void *const *peer_windows);
+int hj_xchg_start(hj_handle *h, const uint64_t *R, const uint64_t *S, uint64_t epoch);
+int hj_xchg_finish(hj_handle *h, hj_result *res);
 
 /* ---- device-side input synthesis (sizes beyond uint32_t/rand()) --
  * Counter-based generators with a bit-identical CPU restatement in oracle/:

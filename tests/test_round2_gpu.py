@@ -175,3 +175,51 @@ def test_pass1_bits_out_of_range_is_einval(hj):
         with pytest.raises(hj.HJError) as e:
             h.join(hj.mc_relation_pk(1 << 12), hj.mc_relation_pk(1 << 12))
         assert e.value.code == hj.HJ_EINVAL
+
+
+# ---- pipelined exchange over the copy engines (hj_xchg_*) with logical ranks on one GPU ----------
+@pytest.mark.parametrize("G,chunks,skewed", [(2, 1, False), (2, 3, False), (4, 2, False), (2, 2, True)])
+def test_xchg_pipeline_logical_ranks(hj, oracle, G, chunks, skewed):
+    """G logical ranks = G handles on one device; the 'peer windows' are local pointers, the copies are
+    device-to-device on the same GPU -- the protocol (stages, flags, fill levels, pass 2 over (source, low)
+    regions, join per chunk) is the one the NVLink path runs.  Two epochs on the same windows; skewed keys
+    must report the region overflow instead of a wrong result."""
+    from htm_hashjoin_b200 import exchange
+    n, m = 1 << 18, 3 << 18          # global sizes
+    R = hj.generate_data("shuffle", n)
+    S = np.concatenate([hj.generate_data("shuffle", n), hj.mc_relation_fk(n, n) & np.uint64(0xFFFFFFFF),
+                        hj.generate_data("shuffle", n)])
+    if skewed:
+        S = S.copy()
+        S[: m // 4] = 12345
+    want = oracle.true_join(R, S)
+    dom_bits = exchange.domain_bits_for(n)
+    nl, ml = n // G, m // G
+    hs = [hj.HashJoin("radix", num_partitions=1 << 8, passes=2, pass1_bits=3) for _ in range(G)]
+    try:
+        wins = [h.xchg_create(G, g, nl, ml, chunks, dom_bits)[0] for g, h in enumerate(hs)]
+        for h in hs:
+            h.xchg_connect(wins)
+        dR = [hs[g].to_device(R[g * nl:(g + 1) * nl]) for g in range(G)]
+        dS = [hs[g].to_device(S[g * ml:(g + 1) * ml]) for g in range(G)]
+        for epoch in (1, 2):
+            for g in range(G):
+                hs[g].xchg_start(dR[g][0], dS[g][0], epoch)
+            total, ovf = [0, 0], False
+            for g in range(G):
+                try:
+                    res = hs[g].xchg_finish()
+                    total[0] += res.matches
+                    total[1] = (total[1] + res.checksum) % (1 << 64)
+                    assert res.us_total > 0 and res.kernel_launches > 0
+                except hj.HJError as e:
+                    assert e.code == hj.HJ_EOVERFLOW
+                    ovf = True
+            assert ovf == skewed
+            if not skewed:
+                assert tuple(total) == want
+        with pytest.raises(hj.HJError):          # epochs must increase
+            hs[0].xchg_start(dR[0][0], dS[0][0], 2)
+    finally:
+        for h in hs:
+            h.close()
