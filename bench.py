@@ -26,6 +26,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 # one hardware queue per stream (compute + one copy stream per peer): no false dependencies between them
 os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+os.environ.setdefault("CUDA_MODULE_LOADING", "EAGER")  # no kernel is loaded (a device-wide sync) in mid-pipeline
 
 METRIC = "join M tuples/s (|R|+|S|)"
 UNIT = "Mtuples/s"

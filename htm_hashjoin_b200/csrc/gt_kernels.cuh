@@ -24,21 +24,26 @@
 // instead -- one bit per slot, slots/8 bytes, 32 MB at 2^27: L2-resident -- and the
 // tuple is then written with a plain store.  The claims of a CTA tile are
 // write-combined in shared memory, the way rx_scatter combines its output runs:
-//   * the tile's tuples do their linear probing against a shared-memory image of
-//     the band of the bitmap the tile touches (home slots of a sorted / locally
-//     shuffled tile lie within tile + 2W slots of each other): an ATOMS.OR per
-//     attempt, whose return value shows the whole word, so a tuple that finds its
-//     slot taken goes straight to the next free slot of its window -- duplicates and
-//     displacement chains are resolved on chip, without a global round trip each;
-//   * then ONE global atomicOr per touched 32-slot word commits everything the tile
-//     claimed in it -- 65 atomics for 2048 sorted tuples instead of 2048.  Bits
-//     that another CTA got first come back in the return value: only those tuples
-//     (tile borders, duplicates across tiles) probe on and commit again;
+//   * the tile's tuples set their bits in a shared-memory image of the band of the
+//     bitmap the tile touches (home slots of a sorted / locally shuffled tile lie
+//     within tile + 2W slots of each other); a bit that is already set there is a
+//     duplicate request inside the tile and loses at once;
+//   * ONE global atomicOr per non-empty 32-slot word claims everything the tile
+//     wants in it -- 65 atomics for 2048 sorted tuples instead of 2048 -- and its
+//     return value tells every requester whether its bit was free;
+//   * a tuple that lost sees the word's whole occupancy and goes straight to the
+//     next free slot of its window instead of stepping one round trip at a time;
 //   * tuples whose window lies outside the band (fully shuffled inputs) claim their
 //     bit with a global atomic of their own, all of a thread's in flight together;
 //   * winners store their tuple: the stores of a tile to neighbouring slots meet
 //     in L2 and leave as full sectors, so the table is written without ever being
 //     read -- 16 B/tuple of DRAM traffic.
+// Slot arithmetic is 32-bit: the table has at most 2^32 slots (the reference's sizes
+// are uint32_t, AtomicHashBuild.hpp:15,21).
+// Measured alternatives (profiles/r02_sweep_global_n27_v*.jsonl, |R| = 2^27 sorted / local_shuffle 2^8,
+// build in us): CAS on the table (round 1) 964 / 1392; warp-aggregated claims with per-run member masks
+// 1119 / 3083 (REDUX/SHFL with 32 different masks per instruction serialise); probing resolved in shared
+// memory with a commit per word 1238 / 998; this kernel: see DESIGN.md.
 #pragma once
 #include "hj_common.cuh"
 
@@ -46,7 +51,7 @@ namespace hj {
 
 constexpr int kGtThreads = 256;
 constexpr int kGtBandWords = 1024;                 // shared-memory band of the claim bitmap: 32768 slots
-constexpr u64 kGtBand = 32ull * kGtBandWords;
+constexpr u32 kGtBand = 32u * kGtBandWords;
 
 // Which tuples a launch covers: nslices segments of seg_len tuples, segment s
 // starting at s*slice_stride + slice_off (the 64 work slices of
@@ -66,8 +71,8 @@ struct SegMap {
 constexpr u32 kGtFar = 0xffffffffu;
 
 // next attempt of a tuple that found bit b of its word taken: the first slot above b that `view` shows
-// free, or the first slot of the next word.  Everything skipped is occupied, so the probe's walk from the
-// home slot never meets a gap before the tuple.
+// free, or the first slot of the next word.  Everything skipped is occupied (or asked for by this tile,
+// hence occupied when the round ends), so the probe's walk from the home slot never meets a gap.
 __device__ __forceinline__ u32 gt_advance(u32 view, u32 b) {
   const u32 freeb = b == 31u ? 0u : (~view & (0xffffffffu << (b + 1u)));
   return freeb ? (u32)__ffs(freeb) - 1u - b : 32u - b;
@@ -75,17 +80,17 @@ __device__ __forceinline__ u32 gt_advance(u32 view, u32 b) {
 
 // IPT tuples per thread ("transaction size": how many inserts a thread has in
 // flight before it looks at any outcome), loaded as IPT coalesced 8-byte loads.
-// STATS: the sampling round of the adaptive switch: cas_retries = claims lost to another CTA at
-// commit time (the HTM-abort stand-in), probe_steps = occupied slots stepped over.
+// hmask = (u32)(key_mask & table mask): home slot = (u32)tuple & hmask.
+// STATS: the sampling round of the adaptive switch: cas_retries = claims that found their slot taken
+// (the HTM-abort stand-in), probe_steps = slots stepped over, span of slots per CTA chunk, sectors per warp.
 template <int IPT, bool STATS>
 __global__ void __launch_bounds__(kGtThreads, 4)
-gt_build_kernel(const u64* __restrict__ R, SegMap sm, u64* __restrict__ table, u32* __restrict__ claim, u64 mask,
-                u64 key_mask, u32 L, u64* __restrict__ ovf_list, u64* __restrict__ ctr) {
+gt_build_kernel(const u64* __restrict__ R, SegMap sm, u64* __restrict__ table, u32* __restrict__ claim, u32 mask,
+                u32 hmask, u32 L, u64* __restrict__ ovf_list, u64* __restrict__ ctr) {
   constexpr int TILE = kGtThreads * IPT;
-  __shared__ u32 s_occ[kGtBandWords];    // what the tile knows to be occupied: its own claims + what commits returned
-  __shared__ u32 s_theirs[kGtBandWords]; // bits another CTA got first (learned at commit)
-  __shared__ u32 s_mine[kGtBandWords];   // bits this tile owns (committed)
-  __shared__ u64 s_min[kGtThreads / 32], s_max[kGtThreads / 32];
+  __shared__ u32 s_want[kGtBandWords];  // bits the tile asks for this round
+  __shared__ u32 s_old[kGtBandWords];   // what the global word held before the tile's atomicOr
+  __shared__ u32 s_min[kGtThreads / 32], s_max[kGtThreads / 32];
   const u32 tid = threadIdx.x, lane = lane_id();
   const u64 chunks_per_seg = (sm.seg_len + TILE - 1) / TILE;
   const u64 nchunks = chunks_per_seg * sm.nslices;
@@ -108,37 +113,31 @@ gt_build_kernel(const u64* __restrict__ R, SegMap sm, u64* __restrict__ table, u
     }
 
     // the band: 32768 slots starting at the tile's lowest home slot (rounded down to a bitmap word)
-    u64 lo = ~0ull, hi = 0ull;
+    u32 lo = 0xffffffffu, hi = 0u;
 #pragma unroll
     for (int j = 0; j < IPT; j++)
       if (v[j]) {
-        const u64 hm = (v[j] & key_mask) & mask;
-        lo = hm < lo ? hm : lo;
-        hi = hm > hi ? hm : hi;
+        const u32 hm = (u32)v[j] & hmask;
+        lo = min(lo, hm);
+        hi = max(hi, hm);
       }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o));
-      hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o));
-    }
-    __syncthreads();  // the previous tile is done with the shared arrays
+    lo = __reduce_min_sync(0xffffffffu, lo);
+    hi = __reduce_max_sync(0xffffffffu, hi);
     if (lane == 0) { s_min[tid >> 5] = lo; s_max[tid >> 5] = hi; }
     __syncthreads();
 #pragma unroll
     for (int w2 = 0; w2 < kGtThreads / 32; w2++) { lo = min(lo, s_min[w2]); hi = max(hi, s_max[w2]); }
     if (STATS && tid == 0 && hi >= lo) {  // working-set signal: how wide is the band of slots one CTA chunk touches?
-      span += hi - lo + 1;
+      span += (u64)(hi - lo) + 1;
       chunks += 1;
     }
-    const u64 base = lo & ~31ull;  // (an empty tile has lo = ~0, hi = 0: nothing is pending)
+    const u32 base = lo & ~31u;  // (an empty tile has lo = ~0, hi = 0: nothing is pending, no round runs)
     u32* const gband = claim + (base >> 5);
-    // words of the band this tile can touch
-    u32 nwords = 0;
+    u32 nwords = 0;  // words of the band this tile can touch
     if (hi >= lo) {
-      const u64 nw = ((hi - base + L + 64) >> 5) + 1;
+      const u64 nw = (((u64)hi - base + L + 64) >> 5) + 1;
       nwords = nw < (u64)kGtBandWords ? (u32)nw : (u32)kGtBandWords;
     }
-    for (u32 wi = tid; wi < nwords; wi += kGtThreads) { s_occ[wi] = 0u; s_theirs[wi] = 0u; s_mine[wi] = 0u; }
 
     u32 rel[IPT];  // home - base, or kGtFar
     u32 att[IPT];  // offset from home of the next slot to try
@@ -150,134 +149,77 @@ gt_build_kernel(const u64* __restrict__ R, SegMap sm, u64* __restrict__ table, u
       rel[j] = kGtFar;
       if (v[j]) {
         pend |= 1u << j;
-        const u64 hm = (v[j] & key_mask) & mask;
-        const u64 r = hm - base;
-        if (r + L + 32 < kGtBand && hm + L + 32 <= mask) rel[j] = (u32)r;
+        const u32 hm = (u32)v[j] & hmask;
+        const u32 r = hm - base;
+        if ((u64)r + L + 32 < kGtBand && (u64)hm + L + 32 <= mask) rel[j] = r;
         else farbits |= 1u << j;
       }
     }
 
-    // ---- far tuples: AtomicHashBuild.hpp:46-60 with one global atomic per attempt, in rounds ----------
-    if (pend & farbits) {
-      u32 fp = pend & farbits;
-#pragma unroll 1
-      while (fp) {
-        u32 old[IPT];
+    // Rounds: every pending tuple of the tile makes its next attempt.  AtomicHashBuild.hpp:46-60
+    // with the claim bitmap standing in for the slot's old value.
+    while (__syncthreads_or(pend != 0)) {  // (also: everybody is done with s_want / s_old / s_min)
+      for (u32 wi = tid; wi < nwords; wi += kGtThreads) s_want[wi] = 0u;
+      __syncthreads();
+      u32 far_old[IPT];  // far tuples: what their own atomicOr returned
+      u32 pre = 0;       // bit j: somebody in the tile asked for the same slot first
+      if (pend & farbits) {  // all of a thread's far claims in flight together
 #pragma unroll
         for (int j = 0; j < IPT; j++)
-          if (fp >> j & 1u) {
-            const u64 slot = (((v[j] & key_mask) & mask) + att[j]) & mask;
-            old[j] = atomicOr(claim + (slot >> 5), 1u << ((u32)slot & 31u));
-          }
-#pragma unroll
-        for (int j = 0; j < IPT; j++)
-          if (fp >> j & 1u) {
-            const u64 slot = (((v[j] & key_mask) & mask) + att[j]) & mask;
-            const u32 b = (u32)slot & 31u;
-            if (!(old[j] >> b & 1u)) {
-              table[slot] = v[j];
-              fp &= ~(1u << j);
-            } else {
-              ++steps;
-              att[j] += gt_advance(old[j] | (1u << b), b);
-              if (att[j] >= L) { fp &= ~(1u << j); failed_bits |= 1u << j; }  // AtomicHashBuild.hpp:62-63
-            }
+          if (pend & farbits & (1u << j)) {
+            const u32 slot = (((u32)v[j] & hmask) + att[j]) & mask;
+            far_old[j] = atomicOr(claim + (slot >> 5), 1u << (slot & 31u));
           }
       }
-      pend &= ~farbits;
-    }
-    __syncthreads();  // the shared arrays are cleared
-
-    // ---- in-band tuples: probe in shared memory, commit, repeat for what another CTA took -------------
-    bool first = true;
-    while (true) {
-      u32 tent = 0;  // bit j: tentatively placed in this iteration
 #pragma unroll
-      for (int j = 0; j < IPT; j++) {
-        bool go = pend >> j & 1u;
-        u32 cur = rel[j] + att[j];
-        u32 prev = 0, bit = 1u << (cur & 31u);
-        bool asked = false;
-        if (first) {
-          // First attempt of a warp's row, warp-cooperative: rows of a sorted or locally shuffled relation
-          // span at most three bitmap words -- their bits are OR-reduced (full-mask REDUX) and set by ONE
-          // shared-memory atomic per word instead of 32 atomics serialising on one address.  Rows that ask
-          // for a bit twice (duplicate keys) or span more words take one atomic per lane.
-          const u32 word = go ? cur >> 5 : kGtFar;
-          const u32 wmin = __reduce_min_sync(0xffffffffu, word);
-          if (wmin != kGtFar) {
-            const u32 d = word - wmin;  // (idle lanes: huge)
-            if (__all_sync(0xffffffffu, !go || d <= 2u)) {
-              const u32 or0 = __reduce_or_sync(0xffffffffu, go && d == 0u ? bit : 0u);
-              const u32 or1 = __reduce_or_sync(0xffffffffu, go && d == 1u ? bit : 0u);
-              const u32 or2 = __reduce_or_sync(0xffffffffu, go && d == 2u ? bit : 0u);
-              if (__popc(or0) + __popc(or1) + __popc(or2) == __popc(__ballot_sync(0xffffffffu, go))) {
-                u32 p = 0;
-                const u32 mine = lane == 0 ? or0 : lane == 1 ? or1 : or2;
-                if (lane < 3 && mine) p = atomicOr(&s_occ[wmin + lane], mine);
-                const u32 p0 = __shfl_sync(0xffffffffu, p, 0), p1 = __shfl_sync(0xffffffffu, p, 1),
-                          p2 = __shfl_sync(0xffffffffu, p, 2);
-                // what the word looked like before + everything this row asked for (all of it ends up occupied)
-                prev = d == 0u ? p0 : d == 1u ? p1 : p2;
-                if (go) {
-                  asked = true;
-                  if (prev & bit) prev |= d == 0u ? or0 : d == 1u ? or1 : or2;
-                }
-              }
-            }
-          }
-        }
-        // the tuple's own probing: AtomicHashBuild.hpp:46-60 against the shared-memory image
-        while (go) {
-          if (!asked) prev = atomicOr(&s_occ[cur >> 5], bit);
-          asked = false;
-          if (!(prev & bit)) { tent |= 1u << j; break; }
-          ++steps;
-          att[j] += gt_advance(prev | bit, cur & 31u);
-          if (att[j] >= L) {  // budget exhausted
-            pend &= ~(1u << j);
-            failed_bits |= 1u << j;
-            break;
-          }
-          cur = rel[j] + att[j];
-          bit = 1u << (cur & 31u);
-        }
-      }
-      first = false;
-      __syncthreads();
-      // commit: one global atomic per word the tile claimed something new in
-      for (u32 wi = tid; wi < nwords; wi += kGtThreads) {
-        const u32 fresh = s_occ[wi] & ~s_theirs[wi] & ~s_mine[wi];
-        if (fresh) {
-          const u32 old = atomicOr(gband + wi, fresh);
-          s_mine[wi] |= fresh & ~old;
-          s_theirs[wi] |= old & ~s_mine[wi];
-          s_occ[wi] |= old;
-        }
-      }
-      __syncthreads();
-      u32 lost = 0;
-#pragma unroll
-      for (int j = 0; j < IPT; j++) {
-        if (tent >> j & 1u) {
+      for (int j = 0; j < IPT; j++)
+        if ((pend & ~farbits) >> j & 1u) {
           const u32 cur = rel[j] + att[j];
-          if (s_theirs[cur >> 5] >> (cur & 31u) & 1u) {
-            lost |= 1u << j;  // another CTA got this slot first: probe on (the bit now reads as occupied)
-            if (STATS) ++retries;
+          const u32 bit = 1u << (cur & 31u);
+          if (atomicOr(&s_want[cur >> 5], bit) & bit) pre |= 1u << j;
+        }
+      __syncthreads();
+      // one global atomic per non-empty word of the band
+      for (u32 wi = tid; wi < nwords; wi += kGtThreads) {
+        const u32 want = s_want[wi];
+        if (want) s_old[wi] = atomicOr(gband + wi, want);
+      }
+      __syncthreads();
+#pragma unroll
+      for (int j = 0; j < IPT; j++) {
+        if (pend >> j & 1u) {
+          u32 b, view, old;
+          if (farbits >> j & 1u) {
+            b = ((((u32)v[j] & hmask) + att[j]) & mask) & 31u;
+            old = far_old[j];
+            view = old | (1u << b);
           } else {
-            table[(((v[j] & key_mask) & mask) + att[j]) & mask] = v[j];
+            const u32 cur = rel[j] + att[j];
+            b = cur & 31u;
+            old = s_old[cur >> 5];
+            view = old | s_want[cur >> 5];
+          }
+          if (!(pre >> j & 1u) && !(old >> b & 1u)) {
+            table[(((u32)v[j] & hmask) + att[j]) & mask] = v[j];
             pend &= ~(1u << j);
+          } else {
+            ++steps;
+            if (STATS && !(pre >> j & 1u)) ++retries;
+            att[j] += gt_advance(view, b);
+            if (att[j] >= L) {  // AtomicHashBuild.hpp:62-63: budget exhausted
+              pend &= ~(1u << j);
+              failed_bits |= 1u << j;
+            }
           }
         }
       }
-      if (!__syncthreads_or(lost != 0)) break;
     }
 
     if (STATS) {
 #pragma unroll
       for (int j = 0; j < IPT; j++) {
         // locality signal: distinct 32 B table sectors this warp's inserts start in
-        const u64 sec = v[j] ? (((v[j] & key_mask) & mask) >> 2) : ~0ull;
+        const u32 sec = v[j] ? ((u32)v[j] & hmask) >> 2 : 0xffffffffu - lane;
         const u32 peers = __match_any_sync(0xffffffffu, sec);
         const bool leader = v[j] && (__ffs(peers) - 1 == (int)lane);
         const u32 leaders = __ballot_sync(0xffffffffu, leader);

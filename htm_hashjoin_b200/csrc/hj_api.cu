@@ -176,8 +176,8 @@ int launch_build_t(hj_handle* h, const u64* R, const SegMap& sm, u64 key_mask) {
   u64 chunks = ((sm.seg_len + kGtThreads * IPT - 1) / (kGtThreads * IPT)) * sm.nslices;
   if (chunks == 0) return HJ_OK;
   if ((u64)grid > chunks) grid = (int)chunks;
-  k<<<grid, kGtThreads, 0, h->stream>>>(R, sm, h->table.p, reinterpret_cast<u32*>(h->claim.p), h->mask, key_mask,
-                                        h->cfg.probe_length, h->ovf_list.p, h->ctr);
+  k<<<grid, kGtThreads, 0, h->stream>>>(R, sm, h->table.p, reinterpret_cast<u32*>(h->claim.p), (u32)h->mask,
+                                        (u32)(key_mask & h->mask), h->cfg.probe_length, h->ovf_list.p, h->ctr);
   h->launches++;
   CK(cudaGetLastError());
   return HJ_OK;
@@ -262,6 +262,10 @@ int zero_async(hj_handle* h, u64* p, u64 elems) {
 int prepare_table(hj_handle* h, u64 n) {
   u32 scale = h->cfg.scale_output ? h->cfg.scale_output : 2;
   u64 slots = pow2_ceil_u64(n * scale < 128 ? 128 : n * scale);  // >= 4 words of the slot bitmaps
+  if (slots > (1ull << 32)) {  // 32-bit slot arithmetic (the reference's sizes are uint32_t, AtomicHashBuild.hpp:15,21)
+    snprintf(h->err, sizeof(h->err), "global table: %llu slots exceed 2^32; use the radix path for |R| > 2^31 / scaleOutput", slots);
+    return HJ_EINVAL;
+  }
   int rc;
   if ((rc = ensure(h, h->table, slots))) return rc;
   if ((rc = ensure(h, h->ovf_table, slots))) return rc;  // worst case: everything overflows, load 0.5
@@ -1889,6 +1893,28 @@ struct Xchg {
   cudaEvent_t ev_begin, ev_end;
 };
 
+// CUDA loads kernels lazily, at their first launch, and that load synchronises with running kernels: a step
+// whose first pass-2 / join launch came AFTER its wait kernel was enqueued would block the host inside
+// hj_xchg_start until the peers' stage arrived (and, with several logical ranks in one process, for ever).
+// Touch every kernel the pipeline can launch once, at create time.
+static void xchg_preload_kernels() {
+  cudaFuncAttributes fa;
+  const void* ks[] = {
+      (const void*)rx_xchg_init_kernel, (const void*)rx_xchg_wait_kernel, (const void*)rx_xchg_parents_kernel,
+      (const void*)rx_opt_init_kernel, (const void*)rx_tasks_kernel,
+      (const void*)rx_scatter_kernel<16, 2, true, 1, true>,
+      (const void*)sc_opt_kernel<8>(1, true), (const void*)sc_opt_kernel<8>(1, false),
+      (const void*)sc_opt_kernel<16>(1, true), (const void*)sc_opt_kernel<16>(1, false),
+      (const void*)sc_opt_kernel<32>(1, true), (const void*)sc_opt_kernel<32>(1, false),
+      (const void*)rx_join32_kernel<512, 8, 2, 4>, (const void*)rx_join32_kernel<512, 4, 3, 2>,
+      (const void*)rx_join32_kernel<512, 8, 2, 2>, (const void*)rx_join32_kernel<256, 8, 4, 2>,
+      (const void*)rx_join32_kernel<1024, 4, 1, 2>, (const void*)rx_join32_kernel<1024, 6, 1, 2>,
+      (const void*)rx_join32_kernel<1024, 8, 1, 2>, (const void*)rx_join32_kernel<384, 4, 4, 2>,
+      (const void*)rx_join_kernel<4, 3>, (const void*)rx_join_kernel<6, 3>, (const void*)rx_join_kernel<8, 2>};
+  for (const void* k : ks) cudaFuncGetAttributes(&fa, k);
+  cudaGetLastError();
+}
+
 static u64 xchg_region_cap(u64 n_stage, u32 G, u32 F1) {
   const u64 mean = n_stage / ((u64)G * F1) + 1;
   u64 r = 1;
@@ -1927,6 +1953,7 @@ int hj_xchg_create(hj_handle* h, uint32_t n_ranks, uint32_t rank, uint64_t n_loc
   if (h->cfg.algo != HJ_ALGO_RADIX) return HJ_ESTATE;
   CK(cudaSetDevice(h->device));
   xchg_free(h);
+  xchg_preload_kernels();
   int rc;
   RadixChoice ch;
   if ((rc = choose_radix(h, n_local, true, true, true, false, false, &ch))) return rc;

@@ -10,6 +10,15 @@
 // process exit code is left to the caller (hj_ref_last_status()).
 #pragma once
 #include <stdint.h>
+// the standard headers the three operator headers pulled in for main.cpp (HTMHashBuild.hpp:20-31), so that
+// swapping the includes at main.cpp:10-14 for this file leaves the rest of main.cpp compiling unchanged
+#include <sys/time.h>
+
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+#include <iostream>
+#include <memory>
 
 void AtomicHashBuild(uint64_t* relR, uint32_t rSize, uint32_t scaleOutput, uint32_t numPartitions,
                      uint32_t probeLength);

@@ -5,6 +5,7 @@ import pytest
 
 # one hardware queue per stream: the logical-rank exchange tests run many streams in one process
 os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+os.environ.setdefault("CUDA_MODULE_LOADING", "EAGER")  # no kernel is loaded (a device-wide sync) in mid-pipeline
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:

@@ -2,6 +2,7 @@
 include/hj_b200.h declares, rejects bad arguments, and fails LOUDLY (HJ_ECUDA, no
 fallback) when there is no CUDA device.  No compute calls here."""
 import ctypes as C
+import json
 import os
 import re
 import subprocess
@@ -121,3 +122,44 @@ def test_cli_sortmerge_is_a_known_algo():
     lib = C.CDLL(os.path.join(ROOT, "htm_hashjoin_b200", "csrc", "libhj_b200.so"))
     if lib.hj_device_count() <= 0:
         assert r.returncode == 2 and '"error"' in r.stdout and "no CPU fallback" in r.stdout
+
+
+def test_reference_main_cpp_compiles_against_ref_entry(tmp_path):
+    """INTEGRATION.md section A, executed: the reference's own main.cpp with the three operator includes
+    (main.cpp:10-14) swapped for ref_entry.hpp compiles UNCHANGED otherwise (both ENABLE_PROBE settings)
+    and links against libhj_b200.so; without a GPU the run prints the JSON error line (no CPU fallback)."""
+    import re
+    import subprocess
+    ref = "/root/reference"
+    if not os.path.exists(os.path.join(ref, "main.cpp")):
+        pytest.skip("reference checkout not present (GPU box)")
+    src = open(os.path.join(ref, "main.cpp")).read()
+    swapped, n = re.subn(r'#include "(AtomicHashBuild|HTMHashBuild|NoCCHashBuild)\.hpp"', "", src)
+    assert n == 3
+    swapped = swapped.replace('#include "config.h"', '#include "config.h"\n#include "ref_entry.hpp"', 1)
+    csrc = os.path.join(ROOT, "htm_hashjoin_b200", "csrc")
+    for probe in (0, 1):
+        cfg_dir = tmp_path / f"cfg{probe}"
+        cfg_dir.mkdir()
+        cfg = open(os.path.join(ref, "config.h")).read()
+        (cfg_dir / "config.h").write_text(re.sub(r"#define ENABLE_PROBE \d", f"#define ENABLE_PROBE {probe}", cfg))
+        (cfg_dir / "main_swapped.cpp").write_text(swapped)
+        exe = cfg_dir / "main"
+        cmd = ["g++", "-std=c++14", "-O1", "-w", "-include", "cstdint", f"-I{cfg_dir}", f"-I{ROOT}/oracle/tbb_shim",
+               f"-I{csrc}", f"-I{ref}", str(cfg_dir / "main_swapped.cpp"), "-o", str(exe), f"-L{csrc}", "-lhj_b200",
+               f"-Wl,-rpath,{csrc}", "-pthread"]
+        out = subprocess.run(cmd, capture_output=True, text=True)
+        assert out.returncode == 0, out.stderr[-2000:]
+        run = subprocess.run([str(exe), "--algo", "atomic", "--rSize", "1024", "--dataDistr", "sorted"],
+                             capture_output=True, text=True, timeout=120)
+        line = json.loads(run.stdout.strip().splitlines()[-1])
+        assert line["algo"] == "atomic" and line["rSize"] == 1024
+        try:
+            import torch
+            has_gpu = torch.cuda.is_available()
+        except Exception:
+            has_gpu = False
+        if has_gpu:
+            assert line["inputSum"] == line["outputSum"] == 1024 * 1025 // 2
+        else:
+            assert "error" in line and "hj_create" in line["error"]
