@@ -78,6 +78,34 @@ def mc_relation_fk(m, maxid, seed=54321):
     return out
 
 
+def mc_relation_nonunique(n, maxid, seed=12345, bias=0):
+    """mc --non-unique / --full-range R (generator.c:493): keys in [0, maxid) + bias (bias=1: no key 0)."""
+    out = np.empty(int(n), dtype=np.uint64)
+    lib.hj_mc_relation_nonunique(out.ctypes.data, int(n), int(maxid), int(seed), int(bias))
+    return out
+
+
+def mc_relation_fk_from_pk(m, pk, seed=54321):
+    """mc --full-range S (generator.c:448): copies of pk, Knuth-shuffled."""
+    pk = np.ascontiguousarray(pk, dtype=np.uint64)
+    out = np.empty(int(m), dtype=np.uint64)
+    lib.hj_mc_relation_fk_from_pk(out.ctypes.data, int(m), pk.ctypes.data, pk.size, int(seed))
+    return out
+
+
+def mc_relation_pk_lshuffle(n, local_shuffle_range, seed=12345):
+    out = np.empty(int(n), dtype=np.uint64)
+    lib.hj_mc_relation_pk_lshuffle(out.ctypes.data, int(n), int(local_shuffle_range), int(seed))
+    return out
+
+
+def mc_relation_zipf(m, maxid, z, seed=54321):
+    """mc --skew z (genzipf.c): zipf-distributed foreign key over a permuted alphabet 1..maxid."""
+    out = np.empty(int(m), dtype=np.uint64)
+    lib.hj_mc_relation_zipf(out.ctypes.data, int(m), int(maxid), float(z), int(seed))
+    return out
+
+
 # ---- handle --------------------------------------------------------------------
 class HashJoin:
     """One hj_handle: owns the device buffers of one GPU."""

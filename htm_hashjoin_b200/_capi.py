@@ -28,7 +28,8 @@ ABI_SYMBOLS = [
 ]
 # host-side mirror of the reference interface (csrc/ref_entry.hpp, csrc/datagen.hpp)
 HOST_SYMBOLS = ["hj_ref_run", "hj_ref_set_radix", "hj_ref_set_device", "hj_ref_last_status",
-                "hj_generate_data", "hj_mc_relation_pk", "hj_mc_relation_fk"]
+                "hj_generate_data", "hj_mc_relation_pk", "hj_mc_relation_fk", "hj_mc_relation_nonunique",
+                "hj_mc_relation_fk_from_pk", "hj_mc_relation_pk_lshuffle", "hj_mc_relation_zipf"]
 
 
 class hj_config(C.Structure):
@@ -130,6 +131,10 @@ def load():
         "hj_generate_data": (C.c_int, [C.c_char_p, C.c_uint64, C.c_uint64, C.c_int, u64p]),
         "hj_mc_relation_pk": (None, [u64p, C.c_uint64, C.c_uint]),
         "hj_mc_relation_fk": (None, [u64p, C.c_uint64, C.c_uint64, C.c_uint]),
+        "hj_mc_relation_nonunique": (None, [u64p, C.c_uint64, C.c_uint64, C.c_uint, C.c_uint32]),
+        "hj_mc_relation_fk_from_pk": (None, [u64p, C.c_uint64, u64p, C.c_uint64, C.c_uint]),
+        "hj_mc_relation_pk_lshuffle": (None, [u64p, C.c_uint64, C.c_int, C.c_uint]),
+        "hj_mc_relation_zipf": (None, [u64p, C.c_uint64, C.c_uint64, C.c_double, C.c_uint]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)

@@ -23,4 +23,11 @@ int hj_generate_data(const char* dist, uint64_t size, uint64_t distinct_keys, in
 void hj_mc_relation_pk(uint64_t* out, uint64_t n, unsigned seed);
 // mc/src/generator.c:409-445: FK relation of m tuples over keys 1..maxid
 void hj_mc_relation_fk(uint64_t* out, uint64_t m, uint64_t maxid, unsigned seed);
+// mc's other workloads (mc/src/main.c:498-513 --non-unique / --full-range / --skew / --local-shuffle-range):
+// create_relation_nonunique (generator.c:493; keys in [0, maxid), + bias), create_relation_fk_from_pk (:448),
+// create_relation_pk_lshuffle (:263), create_relation_zipf (:522 -> genzipf.c gen_zipf)
+void hj_mc_relation_nonunique(uint64_t* out, uint64_t n, uint64_t maxid, unsigned seed, uint32_t bias);
+void hj_mc_relation_fk_from_pk(uint64_t* out, uint64_t m, const uint64_t* pk, uint64_t n, unsigned seed);
+void hj_mc_relation_pk_lshuffle(uint64_t* out, uint64_t n, int range, unsigned seed);
+void hj_mc_relation_zipf(uint64_t* out, uint64_t m, uint64_t maxid, double z, unsigned seed);
 }

@@ -10,6 +10,8 @@ import pytest
 
 from tests import oracle_lib
 
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
 GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "kats.json")
 
 
@@ -218,3 +220,49 @@ def test_reference_sortmerge_pins_the_comparator(oracle):
     j = ref.sort_merge(R, S)
     assert j["totalMatches"] == _ref_sortmerge_restated(R, S)
     assert j["totalMatches"] < oracle.true_join(R, S)[0] == n
+
+
+# ---- mc's skew / non-unique / full-range / local-shuffle generators: the ports are the reference's arrays ----
+def _mc_gen(*args):
+    """Keys the reference's own generator code produces (oracle/_ref/mc_gen = oracle/ref_gen.c around
+    mc/src/generator.c + genzipf.c compiled unmodified)."""
+    import subprocess
+    exe = os.path.join(ROOT, "oracle", "_ref", "mc_gen")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/mc_gen not built (needs /root/reference once)")
+    out = subprocess.run([exe] + [str(a) for a in args], capture_output=True, timeout=120)
+    assert out.returncode == 0
+    return np.frombuffer(out.stdout, dtype=np.int32).astype(np.int64)
+
+
+@pytest.mark.parametrize("case", [("pk", 10007, 12345), ("lshuffle", 10007, 16, 12345), ("lshuffle", 4096, 4096, 7),
+                                  ("fk", 23000, 5000, 54321), ("nonunique", 20011, 20011, 12345),
+                                  ("nonunique", 5003, 2147483647, 99), ("zipf", 30011, 4001, 0.5, 54321),
+                                  ("zipf", 30011, 4001, 1.25, 54321), ("zipf", 1000, 1, 1.0, 5),
+                                  ("fullrange_s", 9001, 3000, 12345, 54321)])
+def test_mc_generator_ports_equal_the_reference(hj, case):
+    want = _mc_gen(*case)
+    kind = case[0]
+    if kind == "pk":
+        got = hj.mc_relation_pk(case[1], case[2])
+    elif kind == "lshuffle":
+        got = hj.mc_relation_pk_lshuffle(case[1], case[2], case[3])
+    elif kind == "fk":
+        got = hj.mc_relation_fk(case[1], case[2], case[3])
+    elif kind == "nonunique":
+        got = hj.mc_relation_nonunique(case[1], case[2], case[3])
+        assert np.array_equal(hj.mc_relation_nonunique(case[1], case[2], case[3], bias=1), got + np.uint64(1))
+    elif kind == "zipf":
+        got = hj.mc_relation_zipf(case[1], case[2], case[3], case[4])
+        assert got.min() >= 1 and got.max() <= case[2]          # genzipf.c:39: 0 is not in the alphabet
+    else:
+        pk = hj.mc_relation_nonunique(case[2], 2147483647, case[3])
+        got = hj.mc_relation_fk_from_pk(case[1], pk, case[4])
+    assert got.dtype == np.uint64 and np.array_equal(got.astype(np.int64), want)
+
+
+def test_mc_nonunique_emits_key_zero(hj):
+    """RAND_RANGE(maxid) can emit 0, the empty-slot sentinel -- that is why the join paths
+    take these relations with bias=1."""
+    a = hj.mc_relation_nonunique(200000, 1000, 12345)
+    assert (a == 0).sum() > 0 and a.max() <= 999
