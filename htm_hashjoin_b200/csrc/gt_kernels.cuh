@@ -522,6 +522,10 @@ gt_probe_kernel(const u64* __restrict__ S, u64 m, const u64* __restrict__ table,
   u64 checksum = 0;
   u32 wmatches = 0, omatches = 0;  // per thread: < 2^32
   const u64 nchunks = (m + TILE - 1) / TILE;
+  __shared__ u64 s_q[TILE];  // S tuples of the tile that have to consult the overflow table
+  __shared__ u32 s_qn;
+  if (tid == 0) s_qn = 0;
+  __syncthreads();
 
   for (u64 c = blockIdx.x; c < nchunks; c += gridDim.x) {
     const u64 base = c * TILE + (u64)warp * (IPT * 32) + lane;
@@ -599,39 +603,42 @@ gt_probe_kernel(const u64* __restrict__ S, u64 m, const u64* __restrict__ table,
         }
       }
     }
-    // the window is full: tuples of this home slot may have overflowed.  The chains of all of a thread's
-    // tuples are walked together, one slot each per round (a walk is a chain of dependent L2 / DRAM loads).
-    if (ovf_count && full) {
+    // the window is full: tuples of this home slot may have overflowed.  Only ~15 % of the tuples of the
+    // reference's "uniform" input get here, and their chains differ in length: walked in place, a warp would
+    // run every round with 3-5 lanes busy (ncu: 54 % of the kernel's instructions at 2.5-5 threads each).
+    // The CTA queues them in shared memory instead and walks the queue with all lanes.
+    if (ovf_count) {  // (kernel-uniform)
       u32 act = 0;
-      u64 os[IPT];
 #pragma unroll
       for (int j = 0; j < IPT; j++) {
         if (full >> j & 1u) {
-          const u64 key = s[j] & key_mask;
-          const u64 home = key & mask;
-          if (__ldg(ovfmap + (home >> 5)) >> ((u32)home & 31u) & 1u) {
-            act |= 1u << j;
-            os[j] = ovf_hash(key, omask);
-          }
+          const u64 home = (s[j] & key_mask) & mask;
+          if (__ldg(ovfmap + (home >> 5)) >> ((u32)home & 31u) & 1u) act |= 1u << j;
         }
       }
-#pragma unroll 1
-      while (act) {
-        u64 o[IPT];
+      if (act) {
+        u32 pos = atomicAdd(&s_qn, (u32)__popc(act));
 #pragma unroll
         for (int j = 0; j < IPT; j++)
-          if (act >> j & 1u) o[j] = __ldg(ovf_table + os[j]);
-#pragma unroll
-        for (int j = 0; j < IPT; j++) {
-          if (act >> j & 1u) {
-            if (o[j] == 0ull) act &= ~(1u << j);
-            else {
-              if ((o[j] & key_mask) == (s[j] & key_mask)) { ++omatches; checksum += o[j] + s[j]; }
-              os[j] = (os[j] + 1) & omask;
-            }
-          }
+          if (act >> j & 1u) s_q[pos++] = s[j];
+      }
+      __syncthreads();
+      const u32 qn = s_qn;
+      for (u32 i = tid; i < qn; i += kGtThreads) {
+        const u64 sv = s_q[i];
+        const u64 key = sv & key_mask;
+        u64 os = ovf_hash(key, omask);
+#pragma unroll 1
+        while (true) {
+          const u64 o = __ldg(ovf_table + os);
+          if (o == 0ull) break;
+          if ((o & key_mask) == key) { ++omatches; checksum += o + sv; }
+          os = (os + 1) & omask;
         }
       }
+      __syncthreads();
+      if (tid == 0) s_qn = 0;
+      __syncthreads();
     }
   }
   u64 v[3] = {(u64)wmatches + omatches, checksum, (u64)wmatches};

@@ -818,8 +818,10 @@ int choose_radix(hj_handle* h, u64 n, bool has_s, bool pre1, bool pre1_known, bo
 
 // The per-partition shared-memory join over h->rb[0].out / h->rb[1].out (exact layout: offsets; histogram-free
 // layout: regions of capR / capS tuples whose fill levels are the scatter's cursors).
+// nsrc > 1: S was partitioned in nsrc separate chunks (hj_xchg): chunk c's partitions at rb[1].out + c * src_stride,
+// its fill levels at rb[1].cursors + c * off_stride; R_p's table is built once and probed with every chunk's S_p.
 int launch_partition_join(hj_handle* h, const RadixPlan& pl, u64 need, bool opt, u64 n, bool has_s, u64 m, u64 capR,
-                          u64 capS) {
+                          u64 capS, u32 nsrc = 1, u64 src_stride = 0, u64 off_stride = 0) {
   int rc;
   const u32 nparts = 1u << pl.bits;
   // 32-bit-key fast path first (returns at once if rx_hist saw wider keys), then the generic
@@ -870,12 +872,14 @@ int launch_partition_join(hj_handle* h, const RadixPlan& pl, u64 need, bool opt,
     u64 slice = 4 * (m >> pl.bits);
     if (slice < 32768) slice = 32768;
     if (env().join_slice) slice = env().join_slice;
+    if (nsrc > 1) slice = 1ull << 40;  // one task per partition: every source is probed by the CTA that built R_p
     slice &= ~1ull;
     const u64 max_tasks = (u64)nparts + m / slice + 1;
     if ((rc = ensure(h, h->tasks, max_tasks))) return rc;
     rx_tasks_kernel<<<1, 1024, 0, h->stream>>>(aoS, nparts, capS, slice, h->tasks.p, max_tasks, h->ctr);
     const u64* a_tasks = h->tasks.p;
-    void* args[] = {&aR, &aoR, &aS, &aoS, &a_np, &a_bits, &nbuckets, &a_ctr, &a_capR, &a_capS, &a_tasks, &slice};
+    void* args[] = {&aR, &aoR, &aS, &aoS, &a_np, &a_bits, &nbuckets, &a_ctr, &a_capR, &a_capS, &a_tasks, &slice,
+                    &nsrc, &src_stride, &off_stride};
     CK(cudaLaunchKernel(k, dim3(grid), dim3(threads), args, smem, h->stream));
     h->launches += 2;
   }
@@ -890,7 +894,8 @@ int launch_partition_join(hj_handle* h, const RadixPlan& pl, u64 need, bool opt,
     k<<<grid, kJoinThreads, smem, h->stream>>>(h->rb[0].out.p, opt ? h->rb[0].cursors.p : h->rb[0].offsets.p,
                                                has_s ? h->rb[1].out.p : nullptr,
                                                has_s ? (opt ? h->rb[1].cursors.p : h->rb[1].offsets.p) : nullptr, nparts,
-                                               pl.bits, pl.slots, h->cfg.key_mask, h->ctr, try32 ? 1 : 0, capR, capS);
+                                               pl.bits, pl.slots, h->cfg.key_mask, h->ctr, try32 ? 1 : 0, capR, capS,
+                                               nsrc, src_stride, off_stride);
     h->launches++;
     CK(cudaGetLastError());
   }
@@ -1890,6 +1895,7 @@ struct Xchg {
   cudaStream_t cs[kScMaxPeers];
   RadixPlan pl;
   u64 C2R = 0, C2S = 0, nR = 0, mS = 0;
+  u64 s_out_stride = 0;  // pass-2 output of S chunk c: rb[1].out + c * s_out_stride, fill levels rb[1].cursors + c * 2^bits
   cudaEvent_t ev_begin, ev_end;
 };
 
@@ -2025,6 +2031,10 @@ int hj_xchg_create(hj_handle* h, uint32_t n_ranks, uint32_t rank, uint64_t n_loc
   // pass 2 + join buffers for what arrives (expected: as much as was sent)
   if ((rc = ensure_rel(h, h->rb[0], x->nR, x->pl, true, true, G))) return fail(rc);
   if ((rc = ensure_rel(h, h->rb[1], x->mS, x->pl, true, true, G))) return fail(rc);
+  // every S chunk keeps its own pass-2 output and fill levels: ONE join at the end builds each R_p once
+  x->s_out_stride = ((1ull << x->pl.bits) * x->C2S + kScThreads * 32 + 2 + 1) & ~1ull;
+  if ((rc = ensure(h, h->rb[1].out, (u64)s_chunks * x->s_out_stride))) return fail(rc);
+  if ((rc = ensure(h, h->rb[1].cursors, (u64)s_chunks << x->pl.bits))) return fail(rc);
   {
     u64 slice = 4 * (x->mS >> x->pl.bits);
     if (slice < 32768) slice = 32768;
@@ -2117,10 +2127,12 @@ int xchg_pass2_stage(hj_handle* h, Xchg* x, u32 t) {
   const RadixPlan& pl = x->pl;
   const u32 nb = 1u << pl.bits, F1 = x->F1, F2 = 1u << pl.b2, nparent = x->G * F1;
   const u64 C2 = t == 0 ? x->C2R : x->C2S;
+  u64* const out = t == 0 ? rb.out.p : rb.out.p + (u64)(t - 1) * x->s_out_stride;
+  u64* const cursors = t == 0 ? rb.cursors.p : rb.cursors.p + ((u64)(t - 1) << pl.bits);
   const u32 ipt = sc_opt_ipt();
   const u32 tile = kScThreads * ipt;
   cudaEventRecord(st.ev[4], h->stream);
-  rx_opt_init_kernel<<<(nb + 255) / 256, 256, 0, h->stream>>>(rb.pcur.p, 0, 0, rb.cursors.p, nb, C2);
+  rx_opt_init_kernel<<<(nb + 255) / 256, 256, 0, h->stream>>>(rb.pcur.p, 0, 0, cursors, nb, C2);
   rx_xchg_parents_kernel<<<1, 1024, 0, h->stream>>>(x->window + st.fill_off, nparent, F1, st.cap, st.stride, tile,
                                                     rb.poff.p, rb.pend.p, rb.ptiles.p);
   h->launches += 2;
@@ -2133,8 +2145,8 @@ int xchg_pass2_stage(hj_handle* h, Xchg* x, u32 t) {
   memset(&d2, 0, sizeof(d2));
   d2.key_mask = h->cfg.key_mask; d2.mode = 0; d2.shift = pl.b1; d2.bits = pl.b2;
   ScOpt o{rb.pend.p, C2, (u64)nb * C2, h->ctr, 0, F1 - 1u, 0, 0};
-  k<<<grid, kScThreads, smem, h->stream>>>(x->window + st.recv_off, rb.out.p, d2, F2, nparent, rb.poff.p, rb.ptiles.p,
-                                           rb.cursors.p, nullptr, o);
+  k<<<grid, kScThreads, smem, h->stream>>>(x->window + st.recv_off, out, d2, F2, nparent, rb.poff.p, rb.ptiles.p,
+                                           cursors, nullptr, o);
   h->launches++;
   CK(cudaGetLastError());
   cudaEventRecord(st.ev[5], h->stream);
@@ -2176,9 +2188,12 @@ int hj_xchg_start(hj_handle* h, const uint64_t* R, const uint64_t* S, uint64_t e
     }
     if ((rc = xchg_wait_stage(h, x, c))) return rc;
     if ((rc = xchg_pass2_stage(h, x, c))) return rc;
-    if ((rc = launch_partition_join(h, x->pl, need, true, x->nR, true, x->mS, x->C2R, x->C2S))) return rc;
-    cudaEventRecord(x->st[c].ev[6], h->stream);
   }
+  // one join over all chunks: R_p's table is built once and probed with S_p of every chunk
+  if ((rc = launch_partition_join(h, x->pl, need, true, x->nR, true, x->mS, x->C2R, x->C2S, C, x->s_out_stride,
+                                  1ull << x->pl.bits)))
+    return rc;
+  cudaEventRecord(x->st[C].ev[6], h->stream);
   CK(cudaEventRecord(x->ev_end, h->stream));
   x->started = true;
   return HJ_OK;
@@ -2203,7 +2218,7 @@ int hj_xchg_finish(hj_handle* h, hj_result* res) {
       res->us_scatter1 += span(x->st[t].ev[0], x->st[t].ev[1]);
       res->us_reserved[0] += span(x->st[t].ev[2], x->st[t].ev[3]);  // waiting for the peers' copies
       res->us_scatter2 += span(x->st[t].ev[4], x->st[t].ev[5]);
-      if (t) res->us_join += span(x->st[t].ev[5], x->st[t].ev[6]);
+      if (t == x->nstages - 1) res->us_join += span(x->st[t].ev[5], x->st[t].ev[6]);
     }
     res->path_taken = HJ_PATH_RADIX;
     res->radix_bits = x->pl.bits;

@@ -234,7 +234,11 @@ template <int THREADS, int BATCH, int MINB, int W>
 __global__ void __launch_bounds__(THREADS, MINB)
 rx_join32_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const u64* __restrict__ Sp,
                  const u64* __restrict__ offS, u32 nparts, u32 radix_bits, u32 nbuckets, u64* __restrict__ ctr,
-                 u64 capR, u64 capS, const u64* __restrict__ tasks, u64 slice) {
+                 u64 capR, u64 capS, const u64* __restrict__ tasks, u64 slice, u32 nsrc, u64 src_stride,
+                 u64 off_stride) {
+  // nsrc > 1 (pipelined exchange): S arrived in nsrc chunks, each partitioned on its own -- source c's partitions
+  // live at Sp + c * src_stride with fill levels offS + c * off_stride.  R_p's table is built ONCE and probed
+  // with S_p of every source (a join is additive over disjoint parts of S); no S slicing then.
   static_assert(BATCH % 2 == 0, "BATCH tuples = BATCH/2 16-byte loads");
   static_assert(W == 2 || W == 4, "bucket of 2 or 4 keys");
   if (ctr[C_KEY_HI] != 0ull) return;  // keys wider than 32 bits: rx_join_kernel handles this join
@@ -267,13 +271,14 @@ rx_join32_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const
     // in rx_kernels.cuh): [p*cap, min(off[p], (p+1)*cap)) with off = the scatter's final cursors
     const u64 r0 = capR ? p * capR : offR[p];
     const u64 r1 = capR ? (offR[p] < r0 + capR ? offR[p] : r0 + capR) : offR[p + 1];
-    u64 s0 = capS ? p * capS : offS[p];
-    u64 s1 = capS ? (offS[p] < s0 + capS ? offS[p] : s0 + capS) : offS[p + 1];
-    s0 += k * slice;  // slice k of S_p (k == 0 and one slice: the whole partition)
-    if (s1 - s0 > slice) s1 = s0 + slice;
     const u64 nr = r1 - r0;
     if (k == 0) maxpart = nr > maxpart ? nr : maxpart;
-    if (nr == 0 || s1 <= s0) continue;
+    if (nr == 0) continue;
+    if (nsrc == 1) {  // nothing to probe with: skip the build too
+      const u64 q0 = (capS ? p * capS : offS[p]) + k * slice;
+      const u64 q1 = capS ? (offS[p] < p * capS + capS ? offS[p] : p * capS + capS) : offS[p + 1];
+      if (q1 <= q0) continue;
+    }
     if (nr > chunk_cap && k == 0) chunked++;
     // an R partition beyond the table's capacity is cut into EQUAL chunks (two chunks at load 0.6 probe
     // faster than one at 0.75 and one at 0.4: full buckets are what costs)
@@ -323,9 +328,17 @@ rx_join32_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const
 
       J32Acc acc;
       acc.key_sum = 0; acc.pay_sum = 0; acc.matches = 0;
+      for (u32 src = 0; src < nsrc; src++) {
+      const u64* __restrict__ Sp_ = Sp + (u64)src * src_stride;
+      const u64* __restrict__ offS_ = offS + (u64)src * off_stride;
+      u64 s0 = capS ? p * capS : offS_[p];
+      u64 s1 = capS ? (offS_[p] < s0 + capS ? offS_[p] : s0 + capS) : offS_[p + 1];
+      s0 += k * slice;  // slice k of S_p (k == 0 and one slice: the whole partition)
+      if (s1 > s0 && s1 - s0 > slice) s1 = s0 + slice;
+      if (s1 <= s0) continue;
       if (!unique) {
         for (u64 i = s0 + tid; i < s1; i += THREADS) {
-          const u64 sv = ld_stream(Sp + i);
+          const u64 sv = ld_stream(Sp_ + i);
           const u32 lo = (u32)sv, hi = (u32)(sv >> 32);
           const u64 r = j32_probe_multi<W>(tab.base, nbuckets, lo >> radix_bits);
           const u32 cnt = (u32)(r >> 32);
@@ -344,10 +357,10 @@ rx_join32_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const
         u64 A[BATCH], B[BATCH];
         auto load = [&](u64 (&v)[BATCH], u64 bi) {
           if (bi < nfull) {
-            const u64* src = Sp + i0 + bi * STEP + 2u * tid;
+            const u64* srcp = Sp_ + i0 + bi * STEP + 2u * tid;
 #pragma unroll
             for (int j = 0; j < BATCH / 2; j++) {
-              const ulonglong2 x = ld_stream_v2(src + 2u * j * THREADS);
+              const ulonglong2 x = ld_stream_v2(srcp + 2u * j * THREADS);
               v[2 * j] = x.x;
               v[2 * j + 1] = x.y;
             }
@@ -355,7 +368,7 @@ rx_join32_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const
 #pragma unroll
             for (int j = 0; j < BATCH; j++) {
               const u64 i = tail0 + (u64)j * THREADS + tid;
-              v[j] = i < s1 ? ld_stream(Sp + i) : 0ull;
+              v[j] = i < s1 ? ld_stream(Sp_ + i) : 0ull;
             }
           }
         };
@@ -370,7 +383,7 @@ rx_join32_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const
           }
         };
         if (tid == 0 && (s0 & 1ull)) {
-          u64 h[1] = {ld_stream(Sp + s0)};
+          u64 h[1] = {ld_stream(Sp_ + s0)};
           j32_probe_unique<W, 1, true>(tab, h, acc);
         }
         if (nb) {
@@ -386,6 +399,7 @@ rx_join32_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const
           }
         }
       }
+      }  // sources
       matches += acc.matches;  // < 2^32 per thread per chunk
       key_sum += acc.key_sum;
       pay_sum += acc.pay_sum;

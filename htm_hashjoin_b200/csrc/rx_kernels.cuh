@@ -694,7 +694,9 @@ template <int kJoinBatch, int MINB>
 __global__ void __launch_bounds__(kJoinThreads, MINB)
 rx_join_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const u64* __restrict__ Sp,
                const u64* __restrict__ offS, u32 nparts, u32 radix_bits, u32 slots, u64 key_mask,
-               u64* __restrict__ ctr, int narrow_keys_elsewhere, u64 capR, u64 capS) {
+               u64* __restrict__ ctr, int narrow_keys_elsewhere, u64 capR, u64 capS, u32 nsrc, u64 src_stride,
+               u64 off_stride) {
+  // nsrc > 1: S arrived in nsrc separately partitioned chunks (see rx_join32_kernel)
   // launched behind rx_join32_kernel: exactly one of the two does the work
   if (narrow_keys_elsewhere && ctr[C_KEY_HI] == 0ull) return;
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -720,9 +722,7 @@ rx_join_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const u
       for (u64 i = r0 + tid; i < r1; i += kJoinThreads) checksum += ((u32)Rp[i] & msk) >> radix_bits;
       continue;
     }
-    const u64 s0 = capS ? p * capS : offS[p];
-    const u64 s1 = capS ? (offS[p] < s0 + capS ? offS[p] : s0 + capS) : offS[p + 1];
-    if (nr == 0 || s1 == s0) continue;
+    if (nr == 0) continue;
     if (nr > chunk_cap) chunked++;
     for (u64 c0 = r0; c0 < r1; c0 += chunk_cap) {
       const u64 c1 = c0 + chunk_cap < r1 ? c0 + chunk_cap : r1;
@@ -747,13 +747,18 @@ rx_join_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const u
       __syncthreads();
       // probe: a batch of S loads in flight, then the home slots of the batch, then the walks
       u32 matches32 = 0;  // < 2^32 per thread per chunk
+      for (u32 src = 0; src < nsrc; src++) {
+      const u64* __restrict__ Sp_ = Sp + (u64)src * src_stride;
+      const u64* __restrict__ offS_ = offS + (u64)src * off_stride;
+      const u64 s0 = capS ? p * capS : offS_[p];
+      const u64 s1 = capS ? (offS_[p] < s0 + capS ? offS_[p] : s0 + capS) : offS_[p + 1];
       for (u64 b = s0; b < s1; b += (u64)kJoinThreads * kJoinBatch) {
         u64 sv[kJoinBatch], cur[kJoinBatch];
         u32 sl[kJoinBatch];
 #pragma unroll
         for (int j = 0; j < kJoinBatch; j++) {
           const u64 i = b + (u64)j * kJoinThreads + tid;
-          sv[j] = i < s1 ? ld_stream(Sp + i) : 0ull;
+          sv[j] = i < s1 ? ld_stream(Sp_ + i) : 0ull;
         }
 #pragma unroll
         for (int j = 0; j < kJoinBatch; j++) {
@@ -772,6 +777,7 @@ rx_join_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const u
           }
         }
       }
+      }  // sources
       matches += matches32;
     }
   }
