@@ -158,6 +158,7 @@ gt_build_kernel(const u64* __restrict__ R, SegMap sm, u64* __restrict__ table, u
 
     // Rounds: every pending tuple of the tile makes its next attempt.  AtomicHashBuild.hpp:46-60
     // with the claim bitmap standing in for the slot's old value.
+    bool first_round = true;
     while (__syncthreads_or(pend != 0)) {  // (also: everybody is done with s_want / s_old / s_min)
       for (u32 wi = tid; wi < nwords; wi += kGtThreads) s_want[wi] = 0u;
       __syncthreads();
@@ -172,12 +173,36 @@ gt_build_kernel(const u64* __restrict__ R, SegMap sm, u64* __restrict__ table, u
           }
       }
 #pragma unroll
-      for (int j = 0; j < IPT; j++)
-        if ((pend & ~farbits) >> j & 1u) {
-          const u32 cur = rel[j] + att[j];
-          const u32 bit = 1u << (cur & 31u);
-          if (atomicOr(&s_want[cur >> 5], bit) & bit) pre |= 1u << j;
+      for (int j = 0; j < IPT; j++) {
+        const bool inb = (pend & ~farbits) >> j & 1u;
+        const u32 cur = rel[j] + att[j];
+        const u32 bit = 1u << (cur & 31u);
+        bool asked = false;
+        if (first_round) {  // (CTA-uniform)
+          // A row of a sorted relation puts all 32 lanes on one or two bitmap words: 32 ATOMS on one address
+          // serialise 32-fold (ncu: 16 M bank conflicts in 20 M shared wavefronts, the pipe at 62 %).  When the
+          // row spans at most two words and asks for every bit once, the bits are OR-reduced with full-mask
+          // REDUX and set by one atomic per word.  (Groups with their own member masks were measured: 32
+          // different masks in one SHFL / REDUX serialise and cost more than they save.)
+          const u32 word = inb ? cur >> 5 : kGtFar;
+          const u32 wmin = __reduce_min_sync(0xffffffffu, word);
+          const u32 d = word - wmin;
+          if (wmin != kGtFar && __all_sync(0xffffffffu, !inb || d <= 1u)) {
+            const u32 or0 = __reduce_or_sync(0xffffffffu, inb && d == 0u ? bit : 0u);
+            const u32 or1 = __reduce_or_sync(0xffffffffu, inb && d == 1u ? bit : 0u);
+            if (__popc(or0) + __popc(or1) == __popc(__ballot_sync(0xffffffffu, inb))) {
+              u32 p = 0;
+              if (lane == 0 && or0) p = atomicOr(&s_want[wmin], or0);
+              if (lane == 1 && or1) p = atomicOr(&s_want[wmin + 1u], or1);
+              const u32 p0 = __shfl_sync(0xffffffffu, p, 0), p1 = __shfl_sync(0xffffffffu, p, 1);
+              if (inb && ((d ? p1 : p0) & bit)) pre |= 1u << j;
+              asked = true;
+            }
+          }
         }
+        if (inb && !asked && (atomicOr(&s_want[cur >> 5], bit) & bit)) pre |= 1u << j;
+      }
+      first_round = false;
       __syncthreads();
       // one global atomic per non-empty word of the band
       for (u32 wi = tid; wi < nwords; wi += kGtThreads) {

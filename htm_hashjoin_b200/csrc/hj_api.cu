@@ -47,6 +47,10 @@ struct Env {
   int sc_ipt, sm_variant, sm_mode, sm_ctas, j32_variant, join_variant, peer_ipt, peer_ctas;
   u64 l2_min_need, join_slice;
 };
+long long env_num(const char* k, long long dflt) {
+  const char* v = getenv(k);
+  return v ? atoll(v) : dflt;
+}
 Env read_env() {
     auto num = [](const char* k, long long dflt) { const char* v = getenv(k); return v ? atoll(v) : dflt; };
     Env x;
@@ -1893,6 +1897,11 @@ struct Xchg {
   u64 *cur = nullptr, *caps_dev = nullptr, *epoch_word = nullptr, *ones = nullptr;
   u64** dest_ptrs = nullptr;  // device [nstages][kScMaxPeers]: where the local scatter puts block `dest`
   cudaStream_t cs[kScMaxPeers];
+  // a block travels as `nsub` slices on nsub streams (one copy engine serves one stream at a time: with a single
+  // peer one stream would leave the other engines idle); the fill levels + flag follow on cs[p] after all slices
+  u32 nsub = 1;
+  cudaStream_t sub[kScMaxPeers][4];
+  cudaEvent_t sub_done[kScMaxPeers][4];
   RadixPlan pl;
   u64 C2R = 0, C2S = 0, nR = 0, mS = 0;
   u64 s_out_stride = 0;  // pass-2 output of S chunk c: rb[1].out + c * s_out_stride, fill levels rb[1].cursors + c * 2^bits
@@ -1931,8 +1940,13 @@ static u64 xchg_region_cap(u64 n_stage, u32 G, u32 F1) {
 void xchg_free(hj_handle* h) {
   Xchg* x = h->xc;
   if (!x) return;
-  for (u32 p = 0; p < x->G; p++)
+  for (u32 p = 0; p < x->G; p++) {
     if (x->cs[p]) { cudaStreamSynchronize(x->cs[p]); cudaStreamDestroy(x->cs[p]); }
+    for (u32 k = 0; k < 4; k++) {
+      if (x->sub[p][k]) { cudaStreamSynchronize(x->sub[p][k]); cudaStreamDestroy(x->sub[p][k]); }
+      if (x->sub_done[p][k]) cudaEventDestroy(x->sub_done[p][k]);
+    }
+  }
   for (u32 t = 0; t < x->nstages; t++) {
     if (x->st[t].send) cudaFree(x->st[t].send);
     if (x->st[t].scattered) cudaEventDestroy(x->st[t].scattered);
@@ -1973,6 +1987,8 @@ int hj_xchg_create(hj_handle* h, uint32_t n_ranks, uint32_t rank, uint64_t n_loc
   memset(x->peer_window, 0, sizeof(x->peer_window));
   memset(x->st, 0, sizeof(x->st));
   memset(x->cs, 0, sizeof(x->cs));
+  memset(x->sub, 0, sizeof(x->sub));
+  memset(x->sub_done, 0, sizeof(x->sub_done));
   x->ev_begin = x->ev_end = nullptr;
   h->xc = x;
   x->G = n_ranks; x->rank = rank; x->pl = ch.pl; x->b1 = ch.pl.b1; x->F1 = 1u << ch.pl.b1;
@@ -2025,8 +2041,18 @@ int hj_xchg_create(hj_handle* h, uint32_t n_ranks, uint32_t rank, uint64_t n_loc
     XCK(cudaMemcpy(x->caps_dev, caps, x->nstages * sizeof(u64), cudaMemcpyHostToDevice));
     XCK(cudaMemcpy(x->ones, ones, x->nstages * 4 * sizeof(u64), cudaMemcpyHostToDevice));
   }
-  for (u32 p = 0; p < G; p++)
-    if (p != rank) XCK(cudaStreamCreateWithFlags(&x->cs[p], cudaStreamNonBlocking));
+  {
+    const long long want = env_num("HJ_XCHG_SUBCOPIES", 0);
+    x->nsub = want > 0 ? (u32)(want > 4 ? 4 : want) : (G == 2 ? 4u : G == 4 ? 2u : 1u);
+  }
+  for (u32 p = 0; p < G; p++) {
+    if (p == rank) continue;
+    XCK(cudaStreamCreateWithFlags(&x->cs[p], cudaStreamNonBlocking));
+    for (u32 k = 1; k < x->nsub; k++) {  // slice 0 travels on cs[p] itself
+      XCK(cudaStreamCreateWithFlags(&x->sub[p][k], cudaStreamNonBlocking));
+      XCK(cudaEventCreateWithFlags(&x->sub_done[p][k], cudaEventDisableTiming));
+    }
+  }
 #undef XCK
   // pass 2 + join buffers for what arrives (expected: as much as was sent)
   if ((rc = ensure_rel(h, h->rb[0], x->nR, x->pl, true, true, G))) return fail(rc);
@@ -2100,8 +2126,22 @@ int xchg_scatter_stage(hj_handle* h, Xchg* x, u32 t, const u64* in) {
     cudaStream_t cs = x->cs[p];
     u64* pw = x->peer_window[p];
     CK(cudaStreamWaitEvent(cs, st.scattered, 0));
-    CK(cudaMemcpyAsync(pw + st.recv_off + (u64)x->rank * st.stride, st.send + (u64)p * st.stride,
-                       (u64)F1 * st.cap * sizeof(u64), cudaMemcpyDeviceToDevice, cs));
+    {
+      u64* const dst = pw + st.recv_off + (u64)x->rank * st.stride;
+      const u64* const src = st.send + (u64)p * st.stride;
+      const u64 total = (u64)F1 * st.cap;
+      const u64 per = ((total + x->nsub - 1) / x->nsub + 31) & ~31ull;  // 256-byte aligned slices
+      for (u32 k = 1; k < x->nsub; k++) {
+        const u64 b = (u64)k * per, e = b + per < total ? b + per : total;
+        if (b >= total) break;
+        CK(cudaStreamWaitEvent(x->sub[p][k], st.scattered, 0));
+        CK(cudaMemcpyAsync(dst + b, src + b, (e - b) * sizeof(u64), cudaMemcpyDeviceToDevice, x->sub[p][k]));
+        CK(cudaEventRecord(x->sub_done[p][k], x->sub[p][k]));
+      }
+      CK(cudaMemcpyAsync(dst, src, (per < total ? per : total) * sizeof(u64), cudaMemcpyDeviceToDevice, cs));
+      for (u32 k = 1; k < x->nsub; k++)
+        if ((u64)k * per < total) CK(cudaStreamWaitEvent(cs, x->sub_done[p][k], 0));
+    }
     CK(cudaMemcpyAsync(pw + st.fill_off + (u64)x->rank * F1, x->cur + (u64)t * gf + (u64)p * F1, F1 * sizeof(u64),
                        cudaMemcpyDeviceToDevice, cs));
     CK(cudaMemcpyAsync(pw + st.flag_off + x->rank, x->epoch_word, sizeof(u64), cudaMemcpyDeviceToDevice, cs));
@@ -2208,7 +2248,7 @@ int hj_xchg_finish(hj_handle* h, hj_result* res) {
   int rc;
   if ((rc = fetch_counters(h))) return rc;  // waits for the compute stream
   for (u32 p = 0; p < x->G; p++)
-    if (x->cs[p]) CK(cudaStreamSynchronize(x->cs[p]));  // the send buffers are free again
+    if (x->cs[p]) CK(cudaStreamSynchronize(x->cs[p]));  // (waits for the slices' streams too) the send buffers are free again
   if (res) {
     memset(res, 0, sizeof(*res));
     fill_common(h, res);
