@@ -385,9 +385,17 @@ def SortMerge(build, buildSize=None, probe=None, probeSize=None, numPartitions=6
 
 
 def PRO(relR, relS=None, nthreads=1, radix_bits=14, passes=2):
-    """mc PRO: returns the join cardinality, or with relS=None the reference's
-    build-only "Results" checksum (parallel_radix_join.c:231-283)."""
-    with HashJoin("radix", num_partitions=1 << radix_bits, passes=passes, key_mask=0xFFFFFFFF,
-                  enable_probe=relS is not None) as hj:
-        res = hj.join(relR, relS)
-        return int(res.matches if relS is not None else res.checksum)
+    """mc PRO (mc/src/parallel_radix_join.h:33-34) through the reference-named C++ entry point
+    (csrc/ref_entry.cpp: PRO): the join cardinality, or -- relS None or a dummy of at most 2 tuples, as
+    experiments/motivation.sh:11 passes -- the reference's build-only "Results" checksum
+    (parallel_radix_join.c:231-283).  NUM_RADIX_BITS / NUM_PASSES are hj_ref_set_radix()."""
+    pr, n = _ptr(relR)
+    ps, m = _ptr(relS)
+    lib.hj_ref_set_radix(int(radix_bits), int(passes))
+    try:
+        out = lib.hj_ref_pro(pr, n, ps, m, int(nthreads))
+    finally:
+        lib.hj_ref_set_radix(0, 0)
+    if out < 0 and lib.hj_ref_last_status() != HJ_OK:
+        raise HJError(lib.hj_ref_last_status(), "PRO")
+    return int(out)

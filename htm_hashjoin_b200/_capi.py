@@ -27,7 +27,7 @@ ABI_SYMBOLS = [
     "hj_xchg_create", "hj_xchg_connect", "hj_xchg_start", "hj_xchg_finish",
 ]
 # host-side mirror of the reference interface (csrc/ref_entry.hpp, csrc/datagen.hpp)
-HOST_SYMBOLS = ["hj_ref_run", "hj_ref_set_radix", "hj_ref_set_device", "hj_ref_last_status",
+HOST_SYMBOLS = ["hj_ref_pro", "hj_ref_run", "hj_ref_set_radix", "hj_ref_set_device", "hj_ref_last_status",
                 "hj_generate_data", "hj_mc_relation_pk", "hj_mc_relation_fk", "hj_mc_relation_nonunique",
                 "hj_mc_relation_fk_from_pk", "hj_mc_relation_pk_lshuffle", "hj_mc_relation_zipf"]
 
@@ -54,7 +54,8 @@ class hj_result(C.Structure):
         ("us_build", C.c_float), ("us_probe", C.c_float), ("us_hist", C.c_float), ("us_scan", C.c_float),
         ("us_scatter1", C.c_float), ("us_scatter2", C.c_float), ("us_join", C.c_float),
         ("us_reserved", C.c_float * 5),
-        ("hbm_bytes", C.c_uint64), ("max_partition", C.c_uint64), ("reserved", C.c_uint64 * 6),
+        ("hbm_bytes", C.c_uint64), ("max_partition", C.c_uint64), ("zero_keys", C.c_uint64),
+        ("reserved", C.c_uint64 * 5),
     ]
 
     def as_dict(self):
@@ -125,6 +126,7 @@ def load():
         "hj_sync": (C.c_int, [H]),
         "hj_ref_run": (C.c_int, [C.c_char_p, u64p, C.c_uint64, u64p, C.c_uint64, C.c_uint32, C.c_uint32,
                                  C.c_uint32, C.c_uint32, C.c_uint32, C.c_char_p, C.c_uint32]),
+        "hj_ref_pro": (C.c_int64, [u64p, C.c_uint32, u64p, C.c_uint32, C.c_int]),
         "hj_ref_set_radix": (None, [C.c_uint32, C.c_uint32]),
         "hj_ref_set_device": (None, [C.c_int]),
         "hj_ref_last_status": (C.c_int, []),

@@ -88,14 +88,17 @@ __global__ void __launch_bounds__(kGtThreads, 4)
 gt_build_kernel(const u64* __restrict__ R, SegMap sm, u64* __restrict__ table, u32* __restrict__ claim, u32 mask,
                 u32 hmask, u32 L, u64* __restrict__ ovf_list, u64* __restrict__ ctr) {
   constexpr int TILE = kGtThreads * IPT;
-  __shared__ u32 s_want[kGtBandWords];  // bits the tile asks for this round
+  __shared__ __align__(16) u32 s_req[kGtBandWords * 8];  // one byte per slot of the band: asked for this round
+  __shared__ u32 s_want[kGtBandWords];  // the same, packed: bits the tile asks for this round
   __shared__ u32 s_old[kGtBandWords];   // what the global word held before the tile's atomicOr
   __shared__ u32 s_min[kGtThreads / 32], s_max[kGtThreads / 32];
   const u32 tid = threadIdx.x, lane = lane_id();
   const u64 chunks_per_seg = (sm.seg_len + TILE - 1) / TILE;
   const u64 nchunks = chunks_per_seg * sm.nslices;
-  u32 retries = 0, steps = 0;
+  u32 retries = 0, steps = 0, zeros = 0;
   u64 sectors = 0, sampled = 0, span = 0, chunks = 0;
+  for (u32 i = tid; i < kGtBandWords * 8; i += kGtThreads) s_req[i] = 0u;  // (every commit scan re-zeroes what it read)
+  __syncthreads();
 
   for (u64 c = blockIdx.x; c < nchunks; c += gridDim.x) {
     const u64 slice = c / chunks_per_seg;
@@ -110,6 +113,7 @@ gt_build_kernel(const u64* __restrict__ R, SegMap sm, u64* __restrict__ table, u
     for (int j = 0; j < IPT; j++) {
       const u64 i = tbase + (u64)j * kGtThreads + tid;
       v[j] = i < seg_end ? ld_stream(R + i) : 0ull;
+      if (i < seg_end && v[j] == 0ull) ++zeros;
     }
 
     // the band: 32768 slots starting at the tile's lowest home slot (rounded down to a bitmap word)
@@ -158,10 +162,7 @@ gt_build_kernel(const u64* __restrict__ R, SegMap sm, u64* __restrict__ table, u
 
     // Rounds: every pending tuple of the tile makes its next attempt.  AtomicHashBuild.hpp:46-60
     // with the claim bitmap standing in for the slot's old value.
-    bool first_round = true;
     while (__syncthreads_or(pend != 0)) {  // (also: everybody is done with s_want / s_old / s_min)
-      for (u32 wi = tid; wi < nwords; wi += kGtThreads) s_want[wi] = 0u;
-      __syncthreads();
       u32 far_old[IPT];  // far tuples: what their own atomicOr returned
       u32 pre = 0;       // bit j: somebody in the tile asked for the same slot first
       if (pend & farbits) {  // all of a thread's far claims in flight together
@@ -172,42 +173,32 @@ gt_build_kernel(const u64* __restrict__ R, SegMap sm, u64* __restrict__ table, u
             far_old[j] = atomicOr(claim + (slot >> 5), 1u << (slot & 31u));
           }
       }
+      // One BYTE per slot in shared memory: the 32 lanes of a sorted row ask for 32 consecutive slots = 8
+      // different words (4 lanes each) instead of 32 bits of ONE word -- a 32-fold serialised ATOMS otherwise
+      // (ncu, bitmap image: 16 M bank conflicts in 20 M shared wavefronts, the pipe at 62 %).
 #pragma unroll
-      for (int j = 0; j < IPT; j++) {
-        const bool inb = (pend & ~farbits) >> j & 1u;
-        const u32 cur = rel[j] + att[j];
-        const u32 bit = 1u << (cur & 31u);
-        bool asked = false;
-        if (first_round) {  // (CTA-uniform)
-          // A row of a sorted relation puts all 32 lanes on one or two bitmap words: 32 ATOMS on one address
-          // serialise 32-fold (ncu: 16 M bank conflicts in 20 M shared wavefronts, the pipe at 62 %).  When the
-          // row spans at most two words and asks for every bit once, the bits are OR-reduced with full-mask
-          // REDUX and set by one atomic per word.  (Groups with their own member masks were measured: 32
-          // different masks in one SHFL / REDUX serialise and cost more than they save.)
-          const u32 word = inb ? cur >> 5 : kGtFar;
-          const u32 wmin = __reduce_min_sync(0xffffffffu, word);
-          const u32 d = word - wmin;
-          if (wmin != kGtFar && __all_sync(0xffffffffu, !inb || d <= 1u)) {
-            const u32 or0 = __reduce_or_sync(0xffffffffu, inb && d == 0u ? bit : 0u);
-            const u32 or1 = __reduce_or_sync(0xffffffffu, inb && d == 1u ? bit : 0u);
-            if (__popc(or0) + __popc(or1) == __popc(__ballot_sync(0xffffffffu, inb))) {
-              u32 p = 0;
-              if (lane == 0 && or0) p = atomicOr(&s_want[wmin], or0);
-              if (lane == 1 && or1) p = atomicOr(&s_want[wmin + 1u], or1);
-              const u32 p0 = __shfl_sync(0xffffffffu, p, 0), p1 = __shfl_sync(0xffffffffu, p, 1);
-              if (inb && ((d ? p1 : p0) & bit)) pre |= 1u << j;
-              asked = true;
-            }
-          }
+      for (int j = 0; j < IPT; j++)
+        if ((pend & ~farbits) >> j & 1u) {
+          const u32 cur = rel[j] + att[j];
+          const u32 sh = (cur & 3u) * 8u;
+          if (atomicOr(&s_req[cur >> 2], 1u << sh) >> sh & 1u) pre |= 1u << j;  // somebody in the tile asked first
         }
-        if (inb && !asked && (atomicOr(&s_want[cur >> 5], bit) & bit)) pre |= 1u << j;
-      }
-      first_round = false;
       __syncthreads();
-      // one global atomic per non-empty word of the band
+      // one global atomic per non-empty word of the band: 32 request bytes -> 32 bits (a byte is 0 or 1:
+      // x * 0x01020408 collects the four of a word in bits 24..27), and the bytes are zeroed for the next round
       for (u32 wi = tid; wi < nwords; wi += kGtThreads) {
-        const u32 want = s_want[wi];
-        if (want) s_old[wi] = atomicOr(gband + wi, want);
+        uint4* const rq = reinterpret_cast<uint4*>(s_req) + 2u * wi;
+        const uint4 a = rq[0], b = rq[1];
+        const u32 want = (a.x * 0x01020408u) >> 24 | ((a.y * 0x01020408u) >> 24) << 4 | ((a.z * 0x01020408u) >> 24) << 8 |
+                         ((a.w * 0x01020408u) >> 24) << 12 | ((b.x * 0x01020408u) >> 24) << 16 |
+                         ((b.y * 0x01020408u) >> 24) << 20 | ((b.z * 0x01020408u) >> 24) << 24 |
+                         ((b.w * 0x01020408u) >> 24) << 28;
+        s_want[wi] = want;
+        if (want) {
+          s_old[wi] = atomicOr(gband + wi, want);
+          rq[0] = make_uint4(0u, 0u, 0u, 0u);
+          rq[1] = make_uint4(0u, 0u, 0u, 0u);
+        }
       }
       __syncthreads();
 #pragma unroll
@@ -284,9 +275,9 @@ gt_build_kernel(const u64* __restrict__ R, SegMap sm, u64* __restrict__ table, u
       atomicAdd(ctr + C_CHUNKS, chunks);
     }
   } else {
-    u64 s[1] = {steps};
-    u64* const d[1] = {ctr + C_PROBE_STEPS};
-    block_sum_atomic<1, kGtThreads>(s, d);
+    u64 s[2] = {steps, zeros};
+    u64* const d[2] = {ctr + C_PROBE_STEPS, ctr + C_ZERO_KEYS};
+    block_sum_atomic<2, kGtThreads>(s, d);
   }
 }
 
@@ -301,7 +292,7 @@ gt_nocc_build_kernel(const u64* __restrict__ R, SegMap sm, u64* __restrict__ tab
   const u32 tid = threadIdx.x;
   const u64 chunks_per_seg = (sm.seg_len + TILE - 1) / TILE;
   const u64 nchunks = chunks_per_seg * sm.nslices;
-  u32 steps = 0;
+  u32 steps = 0, zeros = 0;
   for (u64 c = blockIdx.x; c < nchunks; c += gridDim.x) {
     const u64 slice = c / chunks_per_seg;
     const u64 w = c - slice * chunks_per_seg;
@@ -314,6 +305,7 @@ gt_nocc_build_kernel(const u64* __restrict__ R, SegMap sm, u64* __restrict__ tab
     for (int j = 0; j < IPT; j++) {
       const u64 i = base + (u64)j * kGtThreads + tid;
       v[j] = i < seg_end ? ld_stream(R + i) : 0ull;
+      if (i < seg_end && v[j] == 0ull) ++zeros;
     }
     u32 att[IPT], pend = 0, failed_bits = 0;
 #pragma unroll
@@ -350,9 +342,9 @@ gt_nocc_build_kernel(const u64* __restrict__ R, SegMap sm, u64* __restrict__ tab
         if (failed_bits >> j & 1u) ovf_list[dst++] = v[j];
     }
   }
-  u64 s[1] = {steps};
-  u64* const d[1] = {ctr + C_PROBE_STEPS};
-  block_sum_atomic<1, kGtThreads>(s, d);
+  u64 s[2] = {steps, zeros};
+  u64* const d[2] = {ctr + C_PROBE_STEPS, ctr + C_ZERO_KEYS};
+  block_sum_atomic<2, kGtThreads>(s, d);
 }
 
 // ---- overflow table ---------------------------------------------------------
@@ -508,7 +500,7 @@ gt_probe_home_kernel(const u64* __restrict__ S, u64 m, const u64* __restrict__ t
   constexpr int TILE = kGtThreads * IPT;
   const u32 tid = threadIdx.x;
   u64 checksum = 0;
-  u32 wmatches = 0;
+  u32 wmatches = 0, zeros = 0;
   const u64 nchunks = (m + TILE - 1) / TILE;
   for (u64 c = blockIdx.x; c < nchunks; c += gridDim.x) {
     const u64 base = c * TILE + tid;
@@ -517,6 +509,7 @@ gt_probe_home_kernel(const u64* __restrict__ S, u64 m, const u64* __restrict__ t
     for (int j = 0; j < IPT; j++) {
       const u64 i = base + (u64)j * kGtThreads;
       s[j] = i < m ? ld_stream(S + i) : 0ull;
+      if (i < m && s[j] == 0ull) ++zeros;
     }
 #pragma unroll
     for (int j = 0; j < IPT; j++) cur[j] = s[j] ? __ldg(table + ((s[j] & key_mask) & mask)) : 0ull;
@@ -524,9 +517,9 @@ gt_probe_home_kernel(const u64* __restrict__ S, u64 m, const u64* __restrict__ t
     for (int j = 0; j < IPT; j++)
       if (cur[j] != 0ull && (cur[j] & key_mask) == (s[j] & key_mask)) { ++wmatches; checksum += cur[j] + s[j]; }
   }
-  u64 v[3] = {(u64)wmatches, checksum, (u64)wmatches};
-  u64* const d[3] = {ctr + C_MATCHES, ctr + C_CHECKSUM, ctr + C_WINDOW_MATCHES};
-  block_sum_atomic<3, kGtThreads>(v, d);
+  u64 v[4] = {(u64)wmatches, checksum, (u64)wmatches, (u64)zeros};
+  u64* const d[4] = {ctr + C_MATCHES, ctr + C_CHECKSUM, ctr + C_WINDOW_MATCHES, ctr + C_ZERO_KEYS};
+  block_sum_atomic<4, kGtThreads>(v, d);
 }
 
 template <int IPT>
@@ -545,7 +538,7 @@ gt_probe_kernel(const u64* __restrict__ S, u64 m, const u64* __restrict__ table,
     omask = slots - 1;
   }
   u64 checksum = 0;
-  u32 wmatches = 0, omatches = 0;  // per thread: < 2^32
+  u32 wmatches = 0, omatches = 0, zeros = 0;  // per thread: < 2^32
   const u64 nchunks = (m + TILE - 1) / TILE;
   __shared__ u64 s_q[TILE];  // S tuples of the tile that have to consult the overflow table
   __shared__ u32 s_qn;
@@ -559,6 +552,7 @@ gt_probe_kernel(const u64* __restrict__ S, u64 m, const u64* __restrict__ table,
     for (int j = 0; j < IPT; j++) {
       const u64 i = base + (u64)j * 32;
       s[j] = i < m ? ld_stream(S + i) : 0ull;
+      if (i < m && s[j] == 0ull) ++zeros;
     }
     u32 full = 0;  // bit j: window exhausted without an empty slot
     // dense: homes of the warp = h0 .. h0 + IPT*32 - 1, no wrap-around, every tuple valid
@@ -666,9 +660,9 @@ gt_probe_kernel(const u64* __restrict__ S, u64 m, const u64* __restrict__ table,
       __syncthreads();
     }
   }
-  u64 v[3] = {(u64)wmatches + omatches, checksum, (u64)wmatches};
-  u64* const d[3] = {ctr + C_MATCHES, ctr + C_CHECKSUM, ctr + C_WINDOW_MATCHES};
-  block_sum_atomic<3, kGtThreads>(v, d);
+  u64 v[4] = {(u64)wmatches + omatches, checksum, (u64)wmatches, (u64)zeros};
+  u64* const d[4] = {ctr + C_MATCHES, ctr + C_CHECKSUM, ctr + C_WINDOW_MATCHES, ctr + C_ZERO_KEYS};
+  block_sum_atomic<4, kGtThreads>(v, d);
 }
 
 // ---- verification sums (AtomicHashBuild.hpp:90-119; untimed there and here) -----

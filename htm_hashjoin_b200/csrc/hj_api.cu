@@ -347,6 +347,7 @@ void fill_common(hj_handle* h, hj_result* r) {
   r->sampled = c[C_SAMPLED];
   r->sectors = c[C_SECTORS];
   r->max_partition = c[C_MAX_PART];
+  r->zero_keys = c[C_ZERO_KEYS];
   r->kernel_launches = h->launches;
   r->us_total = span_us(h, E_T0, E_END);
   r->us_h2d = span_us(h, E_CP0, h->ev_set[E_CPS] ? E_CPS : E_CPR);
@@ -2043,7 +2044,9 @@ int hj_xchg_create(hj_handle* h, uint32_t n_ranks, uint32_t rank, uint64_t n_loc
   }
   {
     const long long want = env_num("HJ_XCHG_SUBCOPIES", 0);
-    x->nsub = want > 0 ? (u32)(want > 4 ? 4 : want) : (G == 2 ? 4u : G == 4 ? 2u : 1u);
+    // measured at N=2 (profiles/r02_n2_xchg_subcopies.jsonl): 1 slice 13.85 ms, 2 slices 14.57, 4 slices 14.73 --
+    // one copy saturates what the concurrently running scatter / pass-2 kernels leave of HBM; default 1
+    x->nsub = want > 0 ? (u32)(want > 4 ? 4 : want) : 1u;
   }
   for (u32 p = 0; p < G; p++) {
     if (p == rank) continue;

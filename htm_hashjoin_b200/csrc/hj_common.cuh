@@ -32,6 +32,7 @@ enum Counter {
   C_NTASKS,          // join tasks = (partition, S slice) pairs built by rx_tasks_kernel (skew handling)
   C_MAT_TOTAL,       // pairs the materialising join will write (rx_joinmat.cuh, after the count pass)
   C_XCHG_TIMEOUT,    // a peer's stage flag did not arrive in time (pipelined exchange, rx_xchg_wait_kernel)
+  C_ZERO_KEYS,       // input tuples equal to 0 (the empty-slot sentinel): ignored by the join, reported here
   C_COUNT = 24
 };
 

@@ -223,7 +223,10 @@ int64_t PRO(relation_t* relR, relation_t* relS, int nthreads) {
   cfg.key_mask = 0xffffffffull;  // mc tuples: {int32 key, int32 payload}
   cfg.num_partitions = g_radix_bits ? (1u << g_radix_bits) : (1u << 14);  // NUM_RADIX_BITS default, prj_params.h:15
   cfg.passes = g_passes ? g_passes : 2;                                   // NUM_PASSES default, :20
-  const bool probe = relS && relS->tuples && relS->num_tuples;
+  // The reference's PRO never looks at S (parallel_radix_join.c:1305-1309 -> bucket_chaining_join :231-283 with the
+  // probe commented out) and its scripts pass a dummy one, --s-size=2 (experiments/motivation.sh:11), logging the
+  // build checksum.  A relS of at most 2 tuples is that dummy: build only, return the reference's "Results".
+  const bool probe = relS && relS->tuples && relS->num_tuples > 2;
   cfg.enable_probe = probe;
   hj_handle* h = nullptr;
   g_status = hj_create(&cfg, &h);
@@ -239,4 +242,11 @@ int64_t PRO(relation_t* relR, relation_t* relS, int nthreads) {
   hj_destroy(h);
   if (g_status) return -1;
   return (int64_t)(probe ? res.matches : res.checksum);
+}
+
+// C-callable form of PRO for bindings that cannot take C++ linkage (ctypes): tuples as in mc/src/types.h:31-46
+extern "C" int64_t hj_ref_pro(const void* r_tuples, uint32_t nr, const void* s_tuples, uint32_t ns, int nthreads) {
+  relation_t R{const_cast<tuple_t*>(static_cast<const tuple_t*>(r_tuples)), nr};
+  relation_t S{const_cast<tuple_t*>(static_cast<const tuple_t*>(s_tuples)), ns};
+  return PRO(&R, s_tuples ? &S : nullptr, nthreads);
 }

@@ -43,9 +43,9 @@ void SortMerge(uint64_t* build, uint32_t buildSize, uint64_t* probe, uint32_t pr
 // mc/src/types.h:31-46
 struct tuple_t { int32_t key; int32_t payload; };
 struct relation_t { tuple_t* tuples; uint32_t num_tuples; };
-// mc/src/parallel_radix_join.h:33-34.  relS == nullptr or num_tuples == 0:
-// partition + build only, returns the reference's "Results" checksum
-// (parallel_radix_join.c:256); otherwise the join cardinality.  nthreads is
+// mc/src/parallel_radix_join.h:33-34.  relS == nullptr or num_tuples <= 2 (the dummy S of
+// experiments/motivation.sh:11, --s-size=2): partition + build only, returns the reference's
+// "Results" checksum (parallel_radix_join.c:256); otherwise the join cardinality.  nthreads is
 // accepted and ignored.  Fan-out / passes: hj_ref_set_radix().
 int64_t PRO(relation_t* relR, relation_t* relS, int nthreads);
 
@@ -58,6 +58,7 @@ int hj_ref_last_status(void);
 // The generic form behind all of the above: 64-bit sizes, any algo
 // ("atomic","nocc","htm"/"adaptive","radix","sortmerge"), JSON line into json_out.
 // Returns the hj_* status.
+int64_t hj_ref_pro(const void* r_tuples, uint32_t nr, const void* s_tuples, uint32_t ns, int nthreads);
 int hj_ref_run(const char* algo, const uint64_t* relR, uint64_t rSize, const uint64_t* relS, uint64_t sSize,
                uint32_t transactionSize, uint32_t scaleOutput, uint32_t numPartitions, uint32_t probeLength,
                uint32_t passes, char* json_out, uint32_t cap);

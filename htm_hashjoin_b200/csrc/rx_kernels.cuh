@@ -57,6 +57,7 @@ rx_hist_kernel(const u64* __restrict__ in, u64 n, Digit dg, u32 nbins, u64* __re
   extern __shared__ u32 shist[];
   const u32 tid = threadIdx.x;
   u32 key_hi = 0;  // key bits above bit 31, ORed over every tuple: picks the join kernel (rx_join32.cuh)
+  u32 zeros = 0;   // tuples equal to 0 (the empty-slot sentinel) are ignored by the join: counted for the caller
   if (SMEM) {
     for (u32 i = tid; i < nbins; i += kHistThreads) shist[i] = 0;
     __syncthreads();
@@ -73,9 +74,11 @@ rx_hist_kernel(const u64* __restrict__ in, u64 n, Digit dg, u32 nbins, u64* __re
         ulonglong2 x = ld_stream_v2(in + i);
         v[2 * j] = x.x;
         v[2 * j + 1] = x.y;
+        zeros += (x.x == 0ull) + (x.y == 0ull);
       } else {
         v[2 * j] = i < n ? ld_stream(in + i) : 0ull;
         v[2 * j + 1] = 0ull;
+        zeros += i < n && v[2 * j] == 0ull;
       }
     }
 #pragma unroll
@@ -105,6 +108,8 @@ rx_hist_kernel(const u64* __restrict__ in, u64 n, Digit dg, u32 nbins, u64* __re
   }
   key_hi = __reduce_or_sync(0xffffffffu, key_hi);
   if (key_hi && lane_id() == 0) atomicOr(ctr + C_KEY_HI, (u64)key_hi);
+  zeros = __reduce_add_sync(0xffffffffu, zeros);
+  if (zeros && lane_id() == 0) atomicAdd(ctr + C_ZERO_KEYS, (u64)zeros);
 }
 
 // ---- scan ----------------------------------------------------------------------
@@ -285,7 +290,7 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
   __shared__ u64* s_peer[PEER ? kScMaxPeers : 1];
   if (PEER && threadIdx.x < dg.ndest) s_peer[threadIdx.x] = peer_out[threadIdx.x];
   __shared__ u64 s_pend[OPT ? kScParentCache + 1 : 1];
-  u32 key_hi = 0;
+  u32 key_hi = 0, zeros = 0;  // OPT == 1 (the pass that sees the input first, no rx_hist): key width, zero tuples
   constexpr int TILE = kScThreads * IPT;
   static_assert(TILE <= 65536, "rank is packed into 16 bits");
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -393,6 +398,8 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
         const u32 d = sc_digit<MODE>(dg, fmask, v[j]);
         dr[j] = (d << 16) | atomicAdd(hist + d, 1u);
         if (OPT == 1) key_hi |= (u32)(v[j] >> 32);
+      } else if (OPT == 1) {
+        zeros += 2u * ((j >> 1) * kScThreads + threadIdx.x) + (j & 1) < cnt;  // a real tuple, not tile padding
       }
     }
     // BULK: the previous tile's bulk copies have finished READING shared memory
@@ -530,6 +537,8 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
   if (OPT == 1) {
     key_hi = __reduce_or_sync(0xffffffffu, key_hi) & (u32)(dg.key_mask >> 32);
     if (key_hi && lane_id() == 0) atomicOr(opt.ctr + C_KEY_HI, (u64)key_hi);
+    zeros = __reduce_add_sync(0xffffffffu, zeros);
+    if (zeros && lane_id() == 0) atomicAdd(opt.ctr + C_ZERO_KEYS, (u64)zeros);
   }
 }
 

@@ -103,7 +103,9 @@ typedef struct hj_result {
   float us_reserved[5];    /* [0]: hj_xchg: device time spent waiting for the peers' copies */
   uint64_t hbm_bytes;      /* algorithmic HBM bytes of the path taken       */
   uint64_t max_partition;  /* largest R partition seen by the radix join                */
-  uint64_t reserved[6];
+  uint64_t zero_keys;      /* input tuples equal to 0 (R and S): 0 is the empty-slot sentinel, such tuples
+                              take no part in the join (mc --non-unique can emit them: bias keys by +1) */
+  uint64_t reserved[5];
 } hj_result;
 
 typedef struct hj_handle hj_handle;

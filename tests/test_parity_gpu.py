@@ -506,8 +506,12 @@ def test_region_exchange_logical_ranks(hj, oracle, skewed):
             slices = [rel[g * rel.size // G:(g + 1) * rel.size // G] for g in range(G)]
             cap = exchange.region_cap(slices[0].size, G, f1)
             trash = f1 * G * cap
-            bufs = [h.device_alloc((trash + 16384 + 2 + 2) * 8) for _ in range(G)]
+            total_elems = trash + 16384 + 2 + 2
+            bufs = [h.device_alloc(total_elems * 8) for _ in range(G)]
             guard = np.uint64(0xDEADBEEFDEADBEEF)
+            fill = np.full(total_elems, guard, dtype=np.uint64)
+            for b in bufs:
+                h.copy(b, fill.ctypes.data, fill.nbytes)
             finals = []
             for g in range(G):
                 d_sl = h.to_device(slices[g])
@@ -518,6 +522,23 @@ def test_region_exchange_logical_ranks(hj, oracle, skewed):
                 h.device_free(d_sl[0])
             final_all = torch.stack(finals)
             state[name] = (bufs, final_all, cap)
+            # nothing is written outside [region start, fill level) and the scratch zone: every other word of
+            # every destination buffer still holds the guard value
+            for d in range(G):
+                got = h.to_host(bufs[d], total_elems)
+                touched = np.zeros(total_elems, dtype=bool)
+                touched[trash:trash + 16384 + 2] = True                      # scratch zone (diverted claims)
+                for src in range(G):
+                    cur = final_all[src].cpu().numpy().reshape(G, f1)[d]     # rank src's cursors for dest d
+                    for low in range(f1):
+                        start = (low * G + src) * cap
+                        end = min(int(cur[low]), start + cap)
+                        assert end >= start
+                        touched[start:end] = True
+                assert (got[~touched] == guard).all(), f"{name}: a word outside regions/scratch of buffer {d} changed"
+                if not skewed:  # every claimed slot was filled with a tuple of the right owner and low bits
+                    vals = got[touched & (np.arange(total_elems) < trash)]
+                    assert (vals != guard).all()
         assert any_ovf == skewed
         if skewed:
             return

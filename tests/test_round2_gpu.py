@@ -223,3 +223,15 @@ def test_xchg_pipeline_logical_ranks(hj, oracle, G, chunks, skewed):
     finally:
         for h in hs:
             h.close()
+
+
+def test_pro_entry_point_with_the_reference_scripts_dummy_s(hj):
+    """experiments/motivation.sh:11 runs `--algo=PRO --s-size=2` and logs the build checksum: the reference's PRO
+    never looks at S.  The drop-in PRO treats an S of <= 2 tuples as that dummy (Results = sum idx, closed form
+    (n/2)(n/2^B - 1)) and joins a real S."""
+    n = 1 << 20
+    R = hj.mc_relation_pk(n)
+    dummy = hj.mc_relation_fk(2, n)
+    assert hj.PRO(R, dummy, nthreads=8) == hj.PRO(R, None) == 33030144 == (n // 2) * (n // (1 << 14) - 1)
+    S = hj.mc_relation_fk(4 * n, n)
+    assert hj.PRO(R, S, nthreads=8) == 4 * n
