@@ -826,7 +826,7 @@ int choose_radix(hj_handle* h, u64 n, bool has_s, bool pre1, bool pre1_known, bo
 // nsrc > 1: S was partitioned in nsrc separate chunks (hj_xchg): chunk c's partitions at rb[1].out + c * src_stride,
 // its fill levels at rb[1].cursors + c * off_stride; R_p's table is built once and probed with every chunk's S_p.
 int launch_partition_join(hj_handle* h, const RadixPlan& pl, u64 need, bool opt, u64 n, bool has_s, u64 m, u64 capR,
-                          u64 capS, u32 nsrc = 1, u64 src_stride = 0, u64 off_stride = 0) {
+                          u64 capS, u32 nsrc = 1, u64 src_stride = 0, u64 off_stride = 0, u32 src_first = 0) {
   int rc;
   const u32 nparts = 1u << pl.bits;
   // 32-bit-key fast path first (returns at once if rx_hist saw wider keys), then the generic
@@ -868,8 +868,9 @@ int launch_partition_join(hj_handle* h, const RadixPlan& pl, u64 need, bool opt,
     int grid = grid_for(h, k, threads, smem);
     if ((u32)grid > nparts) grid = (int)nparts;
     // histogram-free layout: the partitions' ends are the scatter's final cursors
-    const u64 *aR = h->rb[0].out.p, *aoR = opt ? h->rb[0].cursors.p : h->rb[0].offsets.p, *aS = h->rb[1].out.p,
-              *aoS = opt ? h->rb[1].cursors.p : h->rb[1].offsets.p;
+    const u64 *aR = h->rb[0].out.p, *aoR = opt ? h->rb[0].cursors.p : h->rb[0].offsets.p,
+              *aS = h->rb[1].out.p + (u64)src_first * src_stride,
+              *aoS = (opt ? h->rb[1].cursors.p : h->rb[1].offsets.p) + (u64)src_first * off_stride;
     u32 a_np = nparts, a_bits = pl.bits;
     u64* a_ctr = h->ctr;
     u64 a_capR = capR, a_capS = capS;
@@ -897,8 +898,9 @@ int launch_partition_join(hj_handle* h, const RadixPlan& pl, u64 need, bool opt,
     int grid = grid_for(h, (const void*)k, kJoinThreads, smem);
     if ((u32)grid > nparts) grid = (int)nparts;
     k<<<grid, kJoinThreads, smem, h->stream>>>(h->rb[0].out.p, opt ? h->rb[0].cursors.p : h->rb[0].offsets.p,
-                                               has_s ? h->rb[1].out.p : nullptr,
-                                               has_s ? (opt ? h->rb[1].cursors.p : h->rb[1].offsets.p) : nullptr, nparts,
+                                               has_s ? h->rb[1].out.p + (u64)src_first * src_stride : nullptr,
+                                               has_s ? (opt ? h->rb[1].cursors.p : h->rb[1].offsets.p) + (u64)src_first * off_stride
+                                                     : nullptr, nparts,
                                                pl.bits, pl.slots, h->cfg.key_mask, h->ctr, try32 ? 1 : 0, capR, capS,
                                                nsrc, src_stride, off_stride);
     h->launches++;
@@ -1883,6 +1885,7 @@ int hj_sync(hj_handle* h) {
 struct XStage {
   u64 n_local, cap, stride, recv_off, fill_off, flag_off;
   u64* send;
+  bool ev_joined;  // a join was launched right after this stage's pass 2 (ev[5] .. ev[6])
   cudaEvent_t scattered;
   cudaEvent_t ev[8];  // scatter0/1, wait0/1, pass2 0/1, join end, spare
 };
@@ -2217,26 +2220,49 @@ int hj_xchg_start(hj_handle* h, const uint64_t* R, const uint64_t* S, uint64_t e
                                                                             x->caps_dev, x->epoch_word, epoch);
   h->launches++;
   auto stage_in = [&](u32 t) { return t == 0 ? (const u64*)R : (const u64*)S + (u64)(t - 1) * x->mS; };
-  // one stage ahead: stage t+1 is scattered (and starts travelling) before stage t is waited for
-  if ((rc = xchg_scatter_stage(h, x, 0, stage_in(0)))) return rc;
-  if ((rc = xchg_scatter_stage(h, x, 1, stage_in(1)))) return rc;
+  // Every stage is scattered up front -- the copy engines then have work from the first scatter on and never
+  // wait for the SMs (scattering only one stage ahead left the link idle between stages: N=2, 4 chunks,
+  // 2.6 ms of waiting per step) -- then stage after stage is waited for and put through pass 2.  The chunks
+  // are joined in groups: a group's join builds every R_p once and probes it with S_p of all the group's
+  // chunks; with more than one group the join of the earlier chunks runs while the last ones still travel.
+  const u32 ahead = (u32)env_num("HJ_XCHG_AHEAD", 1000);
+  u32 scattered = 0;
+  auto scatter_upto = [&](u32 t_last) {
+    int r = HJ_OK;
+    while (scattered <= t_last && scattered < x->nstages && r == HJ_OK) {
+      r = xchg_scatter_stage(h, x, scattered, stage_in(scattered));
+      scattered++;
+    }
+    return r;
+  };
   const u64 per = (x->nR >> x->pl.bits) + 1;
   u64 need = per + 64;
   for (u64 r = 1; r * r < per * 64; r++) need = per + 64 + r;
+  u32 ngroups = (u32)env_num("HJ_XCHG_JOIN_GROUPS", x->G >= 4 ? 2 : 1);
+  if (ngroups < 1) ngroups = 1;
+  if (ngroups > C) ngroups = C;
+  const u32 gsize = (C + ngroups - 1) / ngroups;
+  u32 joined = 0;  // chunks already joined
+  if ((rc = scatter_upto(ahead))) return rc;
   for (u32 c = 1; c <= C; c++) {
-    if (c + 1 <= C && (rc = xchg_scatter_stage(h, x, c + 1, stage_in(c + 1)))) return rc;
+    if ((rc = scatter_upto(c + ahead))) return rc;
     if (c == 1) {
       if ((rc = xchg_wait_stage(h, x, 0))) return rc;
       if ((rc = xchg_pass2_stage(h, x, 0))) return rc;
     }
     if ((rc = xchg_wait_stage(h, x, c))) return rc;
     if ((rc = xchg_pass2_stage(h, x, c))) return rc;
+    if (c - joined == gsize || c == C) {
+      if ((rc = launch_partition_join(h, x->pl, need, true, x->nR, true, x->mS, x->C2R, x->C2S, c - joined,
+                                      x->s_out_stride, 1ull << x->pl.bits, joined)))
+        return rc;
+      cudaEventRecord(x->st[c].ev[6], h->stream);
+      x->st[c].ev_joined = true;
+      joined = c;
+    } else {
+      x->st[c].ev_joined = false;
+    }
   }
-  // one join over all chunks: R_p's table is built once and probed with S_p of every chunk
-  if ((rc = launch_partition_join(h, x->pl, need, true, x->nR, true, x->mS, x->C2R, x->C2S, C, x->s_out_stride,
-                                  1ull << x->pl.bits)))
-    return rc;
-  cudaEventRecord(x->st[C].ev[6], h->stream);
   CK(cudaEventRecord(x->ev_end, h->stream));
   x->started = true;
   return HJ_OK;
@@ -2261,7 +2287,7 @@ int hj_xchg_finish(hj_handle* h, hj_result* res) {
       res->us_scatter1 += span(x->st[t].ev[0], x->st[t].ev[1]);
       res->us_reserved[0] += span(x->st[t].ev[2], x->st[t].ev[3]);  // waiting for the peers' copies
       res->us_scatter2 += span(x->st[t].ev[4], x->st[t].ev[5]);
-      if (t == x->nstages - 1) res->us_join += span(x->st[t].ev[5], x->st[t].ev[6]);
+      if (t && x->st[t].ev_joined) res->us_join += span(x->st[t].ev[5], x->st[t].ev[6]);
     }
     res->path_taken = HJ_PATH_RADIX;
     res->radix_bits = x->pl.bits;
