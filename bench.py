@@ -59,6 +59,10 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-global-table", action="store_true", help="skip the global_table key (BASELINE configs[0]/[1])")
     ap.add_argument("--cpu-also-log-n", type=int, default=27, help="log2 |R| of the cpu_baseline.also runs (atomic / nocc / PRO)")
+    ap.add_argument("--cpu-curves", default="", help="write the reference's CPU W-sweep on this host to this file and exit")
+    ap.add_argument("--cpu-log-n", type=int, default=24)
+    ap.add_argument("--cpu-w-step", type=int, default=4)
+    ap.add_argument("--cpu-reps", type=int, default=3)
     return ap.parse_args()
 
 
@@ -225,6 +229,54 @@ def cpu_reference_extras(log_n=27, reps=5):
     except Exception as e:  # noqa: BLE001
         extra["atomic_error"] = str(e)[:120]
     return extra
+
+
+def cpu_w_sweep(args):
+    """--cpu-curves FILE: the reference's CPU paths over the shuffle window W on THIS host (the CPU side of
+    figs/perf.svg): AtomicHashBuild / NoCCHashBuild build+probe compiled unmodified (R = DataGen
+    local_shuffle W, S = sorted 1..n, main.cpp:93) and mc's NPO / PRO with --local-shuffle-range W, all host
+    threads, median of --cpu-reps runs.  One JSON line per (algo, W), experiments/plot_perf.py --cpu-measured reads it."""
+    import htm_hashjoin_b200 as hj
+    from tests.oracle_lib import Reference, mc_binary
+    n, cores = 1 << args.cpu_log_n, os.cpu_count() or 1
+    ref = Reference(probe=True)
+    exe = mc_binary(14, 2)
+    out = open(args.cpu_curves, "w")
+
+    def emit(o):
+        o.update({"rSize": n, "cores": cores, "cpu": host_desc(), "reps": args.cpu_reps})
+        out.write(json.dumps(o) + "\n")
+        out.flush()
+        print(json.dumps(o), flush=True)
+
+    S = hj.generate_data("sorted", n)
+    for lw in sorted(set(list(range(0, args.cpu_log_n + 1, args.cpu_w_step)) + [args.cpu_log_n])):
+        w = 1 << lw
+        if ref.available:
+            R = hj.generate_data("local_shuffle", n, n, w)
+            for algo in ("nocc", "atomic"):
+                ts = []
+                for _ in range(args.cpu_reps):
+                    j = ref.hash_build(algo, R, S, num_partitions=max(64, cores))
+                    assert j["totalMatches"] == n and j["inputSum"] == n * (n + 1) // 2
+                    ts.append(j["hashBuildTimeInMicroseconds"])
+                emit({"algo": f"{algo} (CPU, this host)", "dataDistr": "local_shuffle", "shuffleRange": w,
+                      "hashBuildTimeInMicroseconds": float(np.median(ts))})
+        if exe:
+            for algo, s_size in (("NPO", n), ("PRO", 2)):   # experiments/motivation.sh:11, npo_probe logs
+                ts = []
+                for _ in range(max(1, args.cpu_reps // 2)):
+                    o = subprocess.run([exe, f"--algo={algo}", f"--nthreads={cores}", f"--r-size={n}", f"--s-size={s_size}",
+                                        f"--local-shuffle-range={w}"], capture_output=True, text=True, timeout=900)
+                    lines = o.stdout.splitlines()
+                    for i, l in enumerate(lines):
+                        if l.startswith("TOTAL-TIME-USECS") and i + 1 < len(lines):
+                            ts.append(float(lines[i + 1].split()[0]))
+                name = "NPJ / NPO build+probe" if algo == "NPO" else "PRJ / PRO partition+build of R"
+                emit({"algo": f"{name} (CPU, this host)", "dataDistr": "local_shuffle", "shuffleRange": w,
+                      "hashBuildTimeInMicroseconds": float(np.median(ts))})
+    out.close()
+    return 0
 
 
 def run_reference(args):
@@ -842,6 +894,8 @@ def run_b200(args):
 
 def main():
     args = parse_args()
+    if args.cpu_curves:
+        return cpu_w_sweep(args)
     if args.impl == "reference":
         return run_reference(args)
     rc = run_b200(args)

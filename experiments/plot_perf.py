@@ -39,7 +39,18 @@ def load_cpu(path, family):
     return {k: [(x, us / 1000.0) for x, us in zip(xs, v)] for k, v in d.items() if not k.startswith("_") and k != "log2_W"}
 
 
-def svg(gpu, cpu, title, out):
+def load_measured_cpu(path):
+    """bench.py --cpu-curves: the reference's CPU code timed on the GPU box's own host cores."""
+    curves = {}
+    for l in open(path):
+        l = l.strip()
+        if l.startswith("{"):
+            o = json.loads(l)
+            curves.setdefault(o["algo"], []).append((math.log2(o["shuffleRange"]), o["hashBuildTimeInMicroseconds"] / 1000.0))
+    return {k: sorted(v) for k, v in curves.items()}
+
+
+def svg(gpu, cpu, title, out, note=""):
     W, H, L, R, T, B = 900, 560, 70, 270, 40, 55
     pts = [p for c in list(gpu.values()) + list(cpu.values()) for p in c]
     x0, x1 = 0.0, max(p[0] for p in pts)
@@ -77,7 +88,8 @@ def svg(gpu, cpu, title, out):
         o.append(f'<line x1="{W - R + 12}" y1="{ly}" x2="{W - R + 42}" y2="{ly}" stroke="{col}" stroke-width="2"{da}/>')
         o.append(f'<text x="{W - R + 48}" y="{ly + 4}">{name}</text>')
         ly += 20
-    o.append(f'<text x="{W - R + 12}" y="{ly + 8}" font-size="10">dashed: reference logs, 2016 CPU (published)</text>')
+    o.append(f'<text x="{W - R + 12}" y="{ly + 8}" font-size="10">dashed: CPU (reference code): published logs (2016),</text>')
+    o.append(f'<text x="{W - R + 12}" y="{ly + 20}" font-size="10">"this host" = timed on the GPU box {note}</text>')
     o.append("</svg>")
     os.makedirs(os.path.dirname(out), exist_ok=True)
     open(out, "w").write("\n".join(o) + "\n")
@@ -88,10 +100,17 @@ def main():
     ap.add_argument("--in", dest="inp", default=os.path.join(HERE, "results", "w_sweep.jsonl"))
     ap.add_argument("--out", default=os.path.join(HERE, "..", "figs", "perf.svg"))
     ap.add_argument("--family", default="build_probe", choices=["build_probe", "build_only"])
+    ap.add_argument("--cpu-measured", default="", help="bench.py --cpu-curves output: the reference's CPU code on this box")
     a = ap.parse_args()
     gpu = load_gpu(a.inp)
     cpu = load_cpu(os.path.join(HERE, "published_cpu.json"), a.family)
-    svg(gpu, cpu, "Hash join vs data locality: B200 library and the reference's CPU runs", a.out)
+    note = ""
+    if a.cpu_measured and os.path.exists(a.cpu_measured):
+        meas = load_measured_cpu(a.cpu_measured)
+        cpu.update(meas)
+        first = json.loads(open(a.cpu_measured).readline())
+        note = f"(|R| = {first.get('rSize')}, {first.get('cores')} cores)"
+    svg(gpu, cpu, "Hash join vs data locality: B200 library and the reference's CPU runs", a.out, note)
     print("wrote", os.path.normpath(a.out), {k: len(v) for k, v in gpu.items()})
 
 

@@ -267,9 +267,9 @@ gt_build_kernel(const u64* __restrict__ R, SegMap sm, u64* __restrict__ table, u
   }
 
   if (STATS) {
-    u64 s[4] = {retries, steps, sectors, sampled};
-    u64* const d[4] = {ctr + C_CAS_RETRIES, ctr + C_PROBE_STEPS, ctr + C_SECTORS, ctr + C_SAMPLED};
-    block_sum_atomic<4, kGtThreads>(s, d);
+    u64 s[5] = {retries, steps, sectors, sampled, zeros};
+    u64* const d[5] = {ctr + C_CAS_RETRIES, ctr + C_PROBE_STEPS, ctr + C_SECTORS, ctr + C_SAMPLED, ctr + C_ZERO_KEYS};
+    block_sum_atomic<5, kGtThreads>(s, d);
     if (tid == 0 && chunks) {
       atomicAdd(ctr + C_SPAN, span);
       atomicAdd(ctr + C_CHUNKS, chunks);

@@ -33,6 +33,7 @@ enum Counter {
   C_MAT_TOTAL,       // pairs the materialising join will write (rx_joinmat.cuh, after the count pass)
   C_XCHG_TIMEOUT,    // a peer's stage flag did not arrive in time (pipelined exchange, rx_xchg_wait_kernel)
   C_ZERO_KEYS,       // input tuples equal to 0 (the empty-slot sentinel): ignored by the join, reported here
+  C_PAY_HI,          // OR of the upper 32 bits of every tuple (0: no tuple carries a payload, rx_join32 skips them)
   C_COUNT = 24
 };
 

@@ -125,7 +125,9 @@ __device__ __noinline__ u64 j32_probe_walk(u32 base, u32 pay_delta, u32 a, u32 k
 
 // G tuples against a chunk whose keys are unique: all bucket loads first, then the
 // compares and payload loads, then the sums; stop at the first match.
-template <int W, int G, bool CHECK>
+// NOPAY: no tuple of either relation carries a payload (ctr[C_PAY_HI] == 0): the payload array is never read --
+// the random LDS.32 per match was 4.6 of the ~10 shared-memory wavefronts a probe cost (ncu, round 1).
+template <int W, int G, bool CHECK, bool NOPAY>
 __device__ __forceinline__ void j32_probe_unique(const J32Tab& t, const u64* __restrict__ s, J32Acc& acc) {
   u32 a[G], kk[G][W];
 #pragma unroll
@@ -141,13 +143,13 @@ __device__ __forceinline__ void j32_probe_unique(const J32Tab& t, const u64* __r
     const bool found = j32_match<W>(kk[g], k, off);
     if (CHECK && s[g] == 0ull) continue;
     if (found) {
-      acc.pay_sum += lds_u32(a[g] + t.pay_delta + off) + hi;
+      if (!NOPAY) acc.pay_sum += lds_u32(a[g] + t.pay_delta + off) + hi;
       acc.key_sum += lo;
       acc.matches += 1;
     } else if (kk[g][W - 1] != kJ32Empty) {
       const u64 r = j32_probe_walk<W>(t.base, t.pay_delta, a[g], k);
       if (r) {
-        acc.pay_sum += (u32)r + hi;
+        if (!NOPAY) acc.pay_sum += (u32)r + hi;
         acc.key_sum += lo;
         acc.matches += 1;
       }
@@ -242,6 +244,7 @@ rx_join32_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const
   static_assert(BATCH % 2 == 0, "BATCH tuples = BATCH/2 16-byte loads");
   static_assert(W == 2 || W == 4, "bucket of 2 or 4 keys");
   if (ctr[C_KEY_HI] != 0ull) return;  // keys wider than 32 bits: rx_join_kernel handles this join
+  const bool nopay = ctr[C_PAY_HI] == 0ull;  // (kernel-uniform) nobody carries a payload: the payload array stays untouched
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __shared__ u32 s_dup;
   J32Tab tab;
@@ -319,7 +322,7 @@ rx_join32_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const
               if (a == tab_end) a = tab.base;
             }
           }
-          sts_u32(a + tab.pay_delta + 4u * i, (u32)(rv[j] >> 32));
+          if (!nopay) sts_u32(a + tab.pay_delta + 4u * i, (u32)(rv[j] >> 32));
         }
         if (dup) s_dup = 1;
       }
@@ -344,7 +347,7 @@ rx_join32_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const
           const u32 cnt = (u32)(r >> 32);
           acc.matches += cnt;
           acc.key_sum += (u64)cnt * lo;
-          acc.pay_sum += (u32)r + cnt * hi;
+          if (!nopay) acc.pay_sum += (u32)r + cnt * hi;  // (the payload array is uninitialised otherwise)
         }
       } else {
         // ---- probe: batches of 16-byte loads from the first even index, two register batches
@@ -375,16 +378,25 @@ rx_join32_kernel(const u64* __restrict__ Rp, const u64* __restrict__ offR, const
         auto process = [&](u64 (&v)[BATCH], u64 bi) {
           constexpr int G = BATCH < 4 ? BATCH : (BATCH % 4 == 0 ? 4 : 2);  // bucket loads in flight per thread
           if (bi < nfull) {
+            if (nopay) {
 #pragma unroll
-            for (int g = 0; g < BATCH; g += G) j32_probe_unique<W, G, false>(tab, v + g, acc);
+              for (int g = 0; g < BATCH; g += G) j32_probe_unique<W, G, false, true>(tab, v + g, acc);
+            } else {
+#pragma unroll
+              for (int g = 0; g < BATCH; g += G) j32_probe_unique<W, G, false, false>(tab, v + g, acc);
+            }
+          } else if (nopay) {
+#pragma unroll
+            for (int g = 0; g < BATCH; g += G) j32_probe_unique<W, G, true, true>(tab, v + g, acc);
           } else {
 #pragma unroll
-            for (int g = 0; g < BATCH; g += G) j32_probe_unique<W, G, true>(tab, v + g, acc);
+            for (int g = 0; g < BATCH; g += G) j32_probe_unique<W, G, true, false>(tab, v + g, acc);
           }
         };
         if (tid == 0 && (s0 & 1ull)) {
           u64 h[1] = {ld_stream(Sp_ + s0)};
-          j32_probe_unique<W, 1, true>(tab, h, acc);
+          if (nopay) j32_probe_unique<W, 1, true, true>(tab, h, acc);
+          else j32_probe_unique<W, 1, true, false>(tab, h, acc);
         }
         if (nb) {
           u64 bi = 0;

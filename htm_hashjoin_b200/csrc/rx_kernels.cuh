@@ -58,6 +58,7 @@ rx_hist_kernel(const u64* __restrict__ in, u64 n, Digit dg, u32 nbins, u64* __re
   const u32 tid = threadIdx.x;
   u32 key_hi = 0;  // key bits above bit 31, ORed over every tuple: picks the join kernel (rx_join32.cuh)
   u32 zeros = 0;   // tuples equal to 0 (the empty-slot sentinel) are ignored by the join: counted for the caller
+  u32 pay_hi = 0;  // upper halves ORed, unmasked: 0 = nobody carries a payload (rx_join32 then never touches them)
   if (SMEM) {
     for (u32 i = tid; i < nbins; i += kHistThreads) shist[i] = 0;
     __syncthreads();
@@ -85,6 +86,7 @@ rx_hist_kernel(const u64* __restrict__ in, u64 n, Digit dg, u32 nbins, u64* __re
     for (int j = 0; j < kHistIPT; j++) {
       const bool valid = v[j] != 0ull;
       key_hi |= (u32)((v[j] & dg.key_mask) >> 32);
+      pay_hi |= (u32)(v[j] >> 32);
       const u32 d = valid ? digit_of(dg, v[j]) : 0xffffffffu;
       // sorted input on high bits puts a whole warp in one bin: add once
       const u32 d0 = __shfl_sync(0xffffffffu, d, 0);
@@ -108,6 +110,8 @@ rx_hist_kernel(const u64* __restrict__ in, u64 n, Digit dg, u32 nbins, u64* __re
   }
   key_hi = __reduce_or_sync(0xffffffffu, key_hi);
   if (key_hi && lane_id() == 0) atomicOr(ctr + C_KEY_HI, (u64)key_hi);
+  pay_hi = __reduce_or_sync(0xffffffffu, pay_hi);
+  if (pay_hi && lane_id() == 0) atomicOr(ctr + C_PAY_HI, (u64)pay_hi);
   zeros = __reduce_add_sync(0xffffffffu, zeros);
   if (zeros && lane_id() == 0) atomicAdd(ctr + C_ZERO_KEYS, (u64)zeros);
 }
@@ -535,7 +539,9 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
   }
   if (BULK) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
   if (OPT == 1) {
-    key_hi = __reduce_or_sync(0xffffffffu, key_hi) & (u32)(dg.key_mask >> 32);
+    key_hi = __reduce_or_sync(0xffffffffu, key_hi);  // (raw upper halves so far)
+    if (key_hi && lane_id() == 0) atomicOr(opt.ctr + C_PAY_HI, (u64)key_hi);
+    key_hi &= (u32)(dg.key_mask >> 32);
     if (key_hi && lane_id() == 0) atomicOr(opt.ctr + C_KEY_HI, (u64)key_hi);
     zeros = __reduce_add_sync(0xffffffffu, zeros);
     if (zeros && lane_id() == 0) atomicAdd(opt.ctr + C_ZERO_KEYS, (u64)zeros);

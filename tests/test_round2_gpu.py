@@ -178,7 +178,7 @@ def test_pass1_bits_out_of_range_is_einval(hj):
 
 
 # ---- pipelined exchange over the copy engines (hj_xchg_*) with logical ranks on one GPU ----------
-@pytest.mark.parametrize("G,chunks,skewed", [(2, 1, False), (2, 3, False), (4, 2, False), (2, 2, True)])
+@pytest.mark.parametrize("G,chunks,skewed", [(2, 1, False), (2, 3, False), (4, 2, False), (2, 2, True), (4, 4, "mc")])
 def test_xchg_pipeline_logical_ranks(hj, oracle, G, chunks, skewed):
     """G logical ranks = G handles on one device; the 'peer windows' are local pointers, the copies are
     device-to-device on the same GPU -- the protocol (stages, flags, fill levels, pass 2 over (source, low)
@@ -189,7 +189,9 @@ def test_xchg_pipeline_logical_ranks(hj, oracle, G, chunks, skewed):
     R = hj.generate_data("shuffle", n)
     S = np.concatenate([hj.generate_data("shuffle", n), hj.mc_relation_fk(n, n) & np.uint64(0xFFFFFFFF),
                         hj.generate_data("shuffle", n)])
-    if skewed:
+    if skewed == "mc":   # mc --non-unique: duplicate keys on both sides, spread evenly over the key range
+        R, S, skewed = hj.mc_relation_nonunique(n, n, 12345, bias=1), hj.mc_relation_nonunique(m, n, 54321, bias=1), False
+    elif skewed:
         S = S.copy()
         S[: m // 4] = 12345
     want = oracle.true_join(R, S)
@@ -235,3 +237,72 @@ def test_pro_entry_point_with_the_reference_scripts_dummy_s(hj):
     assert hj.PRO(R, dummy, nthreads=8) == hj.PRO(R, None) == 33030144 == (n // 2) * (n // (1 << 14) - 1)
     S = hj.mc_relation_fk(4 * n, n)
     assert hj.PRO(R, S, nthreads=8) == 4 * n
+
+
+# ---- mc's own skew / non-unique / full-range workloads, generated by the bit-identical ports ----
+@pytest.mark.parametrize("algo", ["atomic", "radix", "adaptive", "sortmerge"])
+@pytest.mark.parametrize("workload", ["skew0.5", "skew1.0", "skew1.5", "non_unique", "full_range", "lshuffle"])
+def test_mc_workloads_join_equals_oracle(hj, oracle, algo, workload):
+    """mc --skew z / --non-unique / --full-range / --local-shuffle-range (mc/src/main.c:362-411), inputs from
+    csrc/datagen.cpp's ports of generator.c / genzipf.c (pinned on the reference's code in test_oracle_cpu.py)."""
+    n, m = 1 << 17, 1 << 19
+    if workload.startswith("skew"):
+        R, S = hj.mc_relation_pk(n), hj.mc_relation_zipf(m, n, float(workload[4:]))
+    elif workload == "non_unique":      # keys in [0, n) + 1: no tuple carries the empty-slot sentinel
+        R, S = hj.mc_relation_nonunique(n, n, 12345, bias=1), hj.mc_relation_nonunique(m, n, 54321, bias=1)
+    elif workload == "full_range":      # 31-bit keys, S = copies of R shuffled
+        R = hj.mc_relation_nonunique(n, 2147483647, 12345, bias=1)
+        S = hj.mc_relation_fk_from_pk(m, R, 54321)
+    else:
+        R, S = hj.mc_relation_pk_lshuffle(n, 64), hj.mc_relation_fk(m, n)
+    want = oracle.true_join(R, S, 0xFFFFFFFF)
+    assert want[0] >= m if workload != "non_unique" else want[0] > 0
+    with hj.HashJoin(algo, key_mask=0xFFFFFFFF) as h:
+        res = h.join(R, S)
+        assert (res.matches, res.checksum) == want
+        assert res.zero_keys == 0
+
+
+@pytest.mark.parametrize("algo,kw", [("atomic", {}), ("nocc", {}), ("radix", {}), ("radix", dict(num_partitions=64, passes=1)),
+                                     ("sortmerge", {})])
+def test_zero_keys_are_reported_not_silently_dropped(hj, oracle, algo, kw):
+    """mc --non-unique as the reference generates it: RAND_RANGE(maxid) emits key 0 (generator.c:20,231-238), the
+    empty-slot sentinel.  Such tuples take no part in the join -- and the result says how many there were."""
+    n, m = 100003, 300007
+    R, S = hj.mc_relation_nonunique(n, 5000, 12345), hj.mc_relation_nonunique(m, 5000, 54321)
+    zr, zs = int((R == 0).sum()), int((S == 0).sum())
+    assert zr > 0 and zs > 0
+    want = oracle.true_join(R[R != 0], S[S != 0], 0xFFFFFFFF)
+    with hj.HashJoin(algo, key_mask=0xFFFFFFFF, **kw) as h:
+        res = h.join(R, S)
+        if algo != "nocc":   # nocc races by design on duplicate keys
+            assert (res.matches, res.checksum) == want
+        assert res.zero_keys == zr + zs
+
+
+def test_experiment_harness_w_sweep(hj, tmp_path):
+    """experiments/w_sweep.py (the reference's probe.sh / motivation.sh sweep against this library)
+    at 2^20 for four shuffle windows: every point verified against the closed-form result, the adaptive path on
+    the global table for small windows, and the figure writer takes its output."""
+    import json
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = tmp_path / "w.jsonl"
+    subprocess.run([sys.executable, os.path.join(root, "experiments", "w_sweep.py"), "--log-n", "20", "--w-step", "7",
+                    "--reps", "2", "--out", str(out)], check=True, capture_output=True, timeout=600)
+    rows = [json.loads(l) for l in open(out)]
+    assert len(rows) == 4 * 4   # W = 2^0, 2^7, 2^14, 2^20 x nocc, atomic, radix, adaptive
+    n = 1 << 20
+    for r in rows:
+        assert r["verified"] is True and r["totalMatches"] == n and r["hashBuildTimeInMicroseconds"] > 0
+    by = {(r["algo"], r["shuffleRange"]): r for r in rows}
+    assert by[("adaptive", 1)]["pathTaken"] == "global" and by[("atomic", 1)]["pathTaken"] == "global"
+    assert by[("radix", 1 << 20)]["pathTaken"] == "radix"
+    # locality is measured: the contention signal grows with the window
+    assert by[("adaptive", 1 << 20)]["firstRoundFailureFraction"] > by[("adaptive", 1)]["firstRoundFailureFraction"]
+    svg = tmp_path / "perf.svg"
+    subprocess.run([sys.executable, os.path.join(root, "experiments", "plot_perf.py"), "--in", str(out), "--out", str(svg)],
+                   check=True, capture_output=True)
+    assert svg.read_text().startswith("<svg")
