@@ -112,7 +112,7 @@ class HashJoin:
 
     def __init__(self, algo="atomic", device=0, probe_length=4, scale_output=2, num_partitions=0, passes=0,
                  transaction_size=16, enable_probe=True, sample_rounds=5, key_mask=0, adaptive_threshold=0.0,
-                 pass1_bits=0):
+                 pass1_bits=0, tuple_bytes=8):
         cfg = hj_config()
         lib.hj_config_default(C.byref(cfg))
         cfg.algo = ALGOS[algo] if isinstance(algo, str) else int(algo)
@@ -127,6 +127,8 @@ class HashJoin:
         cfg.key_mask = key_mask if key_mask else 0xFFFFFFFFFFFFFFFF
         cfg.adaptive_threshold = adaptive_threshold
         cfg.pass1_bits = pass1_bits
+        cfg.tuple_bytes = tuple_bytes
+        self.words = 2 if tuple_bytes == 16 else 1   # 8-byte words per tuple
         self.cfg = cfg
         self._h = C.c_void_p()
         rc = lib.hj_create(C.byref(cfg), C.byref(self._h))
@@ -163,20 +165,21 @@ class HashJoin:
     def build(self, R):
         p, n = _ptr(R)
         res = hj_result()
-        self._check(lib.hj_build(self._h, p, n, C.byref(res)), "hj_build")
+        self._check(lib.hj_build(self._h, p, n // self.words, C.byref(res)), "hj_build")
         return res
 
     def probe(self, S):
         p, m = _ptr(S)
         res = hj_result()
-        self._check(lib.hj_probe(self._h, p, m, C.byref(res)), "hj_probe")
+        self._check(lib.hj_probe(self._h, p, m // self.words, C.byref(res)), "hj_probe")
         return res
 
     def join(self, R, S=None):
+        """R, S: uint64 arrays (tuple_bytes=16: 2 words per tuple, e.g. shape (n, 2)), tensors or (pointer, words)."""
         pr, n = _ptr(R)
         ps, m = _ptr(S)
         res = hj_result()
-        self._check(lib.hj_join(self._h, pr, n, ps, m, C.byref(res)), "hj_join")
+        self._check(lib.hj_join(self._h, pr, n // self.words, ps, m // self.words, C.byref(res)), "hj_join")
         return res
 
     def join_materialize(self, R, S, d_out=None, capacity=0):
@@ -204,7 +207,7 @@ class HashJoin:
     def checksums(self, R=None):
         p, n = _ptr(R)
         res = hj_result()
-        self._check(lib.hj_checksums(self._h, p, n, C.byref(res)), "hj_checksums")
+        self._check(lib.hj_checksums(self._h, p, n // self.words, C.byref(res)), "hj_checksums")
         return res
 
     def radix_partition(self, d_in, n, shift, bits, d_out, d_offsets):

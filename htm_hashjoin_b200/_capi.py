@@ -38,7 +38,7 @@ class hj_config(C.Structure):
         ("probe_length", C.c_uint32), ("scale_output", C.c_uint32), ("num_partitions", C.c_uint32),
         ("passes", C.c_uint32), ("transaction_size", C.c_uint32), ("enable_probe", C.c_uint32),
         ("sample_rounds", C.c_uint32), ("key_mask", C.c_uint64), ("adaptive_threshold", C.c_double),
-        ("pass1_bits", C.c_uint64), ("reserved", C.c_uint64 * 3),
+        ("pass1_bits", C.c_uint64), ("tuple_bytes", C.c_uint64), ("reserved", C.c_uint64 * 2),
     ]
 
 

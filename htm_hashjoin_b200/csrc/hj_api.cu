@@ -22,6 +22,7 @@
 #include "rx_joinl2.cuh"
 #include "rx_joinmat.cuh"
 #include "rx_sortmerge.cuh"
+#include "rx_wide.cuh"
 
 using namespace hj;
 
@@ -670,7 +671,7 @@ int radix_partition_rel(hj_handle* h, const u64* in, u64 n, RelBufs& rb, const R
   // Single pass: f2 = nb makes parent 0 span every bin.
   rx_scan_kernel<<<1, kScanThreads, 0, h->stream>>>(rb.ghist.p, nb, rb.offsets.p, rb.cursors.p,
                                                     pl.passes == 2 ? F2 : nb, rb.poff.p, rb.pcur.p, rb.ptiles.p,
-                                                    rb.one.p, tile, max_bin);
+                                                    rb.one.p, tile, max_bin, n);
   h->launches++;
   CK(cudaGetLastError());
   if (evb >= 0) mark(h, evb + 2);
@@ -1159,6 +1160,207 @@ int run_global_join(hj_handle* h, const u64* dR, u64 n, const u64* dS, u64 m, bo
 
 }  // namespace
 
+// ---- 16-byte tuples (cfg.tuple_bytes == 16; mc's KEY_8B tuple, mc/src/types.h:22-37) -----------------------
+namespace {
+
+bool wide(const hj_handle* h) { return h->cfg.tuple_bytes == 16; }
+
+// partition a relation of n 16-byte tuples by pl (exact layout): rb.out = partitions, rb.offsets = 2^bits + 1 offsets
+int wide_partition_rel(hj_handle* h, const tup16* in, u64 n, RelBufs& rb, const RadixPlan& pl, int evb) {
+  const u32 nb = 1u << pl.bits, F1 = 1u << pl.b1, F2 = 1u << pl.b2;
+  constexpr u32 tile = kWScThreads * kWScIPT;
+  Digit full;
+  memset(&full, 0, sizeof(full));
+  full.key_mask = h->cfg.key_mask;
+  if (pl.passes == 2) { full.mode = 1; full.b1 = pl.b1; full.b2 = pl.b2; }
+  else { full.mode = 0; full.shift = 0; full.bits = pl.bits; }
+  if (evb >= 0) mark(h, evb);
+  CK(cudaMemsetAsync(rb.ghist.p, 0, nb * sizeof(u64), h->stream));
+  {
+    const size_t smem = (size_t)nb * 4;
+    CK(cudaFuncSetAttribute(w_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int grid = grid_for(h, (const void*)w_hist_kernel, kWHistThreads, smem);
+    const u64 tiles = (n + (u64)kWHistThreads * kWHistIPT - 1) / ((u64)kWHistThreads * kWHistIPT);
+    if ((u64)grid > tiles) grid = (int)(tiles ? tiles : 1);
+    w_hist_kernel<<<grid, kWHistThreads, smem, h->stream>>>(in, n, full, nb, rb.ghist.p, h->ctr);
+    h->launches++;
+  }
+  if (evb >= 0) mark(h, evb + 1);
+  rx_scan_kernel<<<1, kScanThreads, 0, h->stream>>>(rb.ghist.p, nb, rb.offsets.p, rb.cursors.p, pl.passes == 2 ? F2 : nb,
+                                                    rb.poff.p, rb.pcur.p, rb.ptiles.p, rb.one.p, tile, h->ctr + C_MAX_PART, n);
+  h->launches++;
+  CK(cudaGetLastError());
+  if (evb >= 0) mark(h, evb + 2);
+  auto scatter = [&](const tup16* src, tup16* dst, const Digit& dg, u32 F, u32 nparent, const u64* poff, const u64* ptiles,
+                     u64* cursors, u64 max_tiles) {
+    const size_t smem = (size_t)tile * 16 + (size_t)F * 16;
+    if (cudaFuncSetAttribute(w_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return HJ_ECUDA;
+    int grid = grid_for(h, (const void*)w_scatter_kernel, kWScThreads, smem);
+    if ((u64)grid > max_tiles) grid = (int)(max_tiles ? max_tiles : 1);
+    w_scatter_kernel<<<grid, kWScThreads, smem, h->stream>>>(src, dst, dg, F, nparent, poff, ptiles, cursors);
+    h->launches++;
+    return cudaGetLastError() == cudaSuccess ? HJ_OK : HJ_ECUDA;
+  };
+  const u64 max_tiles = (n + tile - 1) / tile;
+  tup16* out = reinterpret_cast<tup16*>(rb.out.p);
+  tup16* tmp = reinterpret_cast<tup16*>(rb.tmp.p);
+  int rc;
+  if (pl.passes == 1) {
+    if ((rc = scatter(in, out, full, nb, 1, rb.poff.p, rb.ptiles.p, rb.cursors.p, max_tiles))) return rc;
+    if (evb >= 0) { mark(h, evb + 3); mark(h, evb + 4); }
+  } else {
+    Digit d1, d2;
+    memset(&d1, 0, sizeof(d1));
+    d1.key_mask = h->cfg.key_mask; d1.mode = 0; d1.shift = 0; d1.bits = pl.b1;
+    d2 = d1; d2.shift = pl.b1; d2.bits = pl.b2;
+    if ((rc = scatter(in, tmp, d1, F1, 1, rb.one.p, rb.one.p + 2, rb.pcur.p, max_tiles))) return rc;
+    if (evb >= 0) mark(h, evb + 3);
+    if ((rc = scatter(tmp, out, d2, F2, F1, rb.poff.p, rb.ptiles.p, rb.cursors.p, max_tiles + F1))) return rc;
+    if (evb >= 0) mark(h, evb + 4);
+  }
+  return HJ_OK;
+}
+
+int run_wide_radix_join(hj_handle* h, const u64* dR, u64 n, bool pendR, const u64* dS, u64 m, bool pendS, hj_result* res) {
+  if (!dS) {
+    snprintf(h->err, sizeof(h->err), "16-byte tuples: the radix join needs both relations");
+    return HJ_EINVAL;
+  }
+  RadixPlan pl;
+  int rc;
+  h->built = false;
+  if ((rc = plan_radix(h, n, &pl, 4096))) return rc;  // R partitions of <= 4096 tuples: one chunk of an 8192-slot table
+  if (pl.passes == 1 && pl.bits > kMaxBitsPerPass) return HJ_EINVAL;
+  if ((rc = ensure_rel(h, h->rb[0], 2 * n, pl))) return rc;
+  if ((rc = ensure_rel(h, h->rb[1], 2 * m, pl))) return rc;
+  CK(cudaMemsetAsync(h->ctr, 0, C_COUNT * sizeof(u64), h->stream));
+  if ((rc = wait_staged(h, E_CPR, pendR))) return rc;
+  if ((rc = wide_partition_rel(h, reinterpret_cast<const tup16*>(dR), n, h->rb[0], pl, E_RX))) return rc;
+  if ((rc = wait_staged(h, E_CPS, pendS))) return rc;
+  if ((rc = wide_partition_rel(h, reinterpret_cast<const tup16*>(dS), m, h->rb[1], pl, E_RX + 5))) return rc;
+  mark(h, E_JOIN0);
+  {
+    const u32 nparts = 1u << pl.bits;
+    u64 per = (n >> pl.bits) + 1;
+    u32 slots = 1024;
+    while (slots < 8192 && slots < 4 * per) slots <<= 1;
+    const size_t smem = (size_t)slots * 16;
+    CK(cudaFuncSetAttribute(w_join_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int grid = grid_for(h, (const void*)w_join_kernel, kWJoinThreads, smem);
+    if ((u32)grid > nparts) grid = (int)nparts;
+    w_join_kernel<<<grid, kWJoinThreads, smem, h->stream>>>(reinterpret_cast<const tup16*>(h->rb[0].out.p), h->rb[0].offsets.p,
+                                                            reinterpret_cast<const tup16*>(h->rb[1].out.p), h->rb[1].offsets.p,
+                                                            nparts, pl.bits, slots, h->cfg.key_mask, h->ctr);
+    h->launches++;
+    CK(cudaGetLastError());
+  }
+  mark(h, E_JOIN);
+  mark(h, E_END);
+  if ((rc = fetch_counters(h))) return rc;
+  if (res) {
+    fill_common(h, res);
+    res->path_taken = HJ_PATH_RADIX;
+    res->radix_bits = pl.bits;
+    res->passes = pl.passes;
+    res->hbm_bytes = 16ull * (3 * pl.passes + 1) * (n + m);  // per pass: histogram read (exact layout) + read + write; join read
+  }
+  return HJ_OK;
+}
+
+int wide_prepare_table(hj_handle* h, u64 n) {
+  u32 scale = h->cfg.scale_output ? h->cfg.scale_output : 2;
+  u64 slots = pow2_ceil_u64(n * scale < 128 ? 128 : n * scale);
+  if (slots > (1ull << 32)) return HJ_EINVAL;
+  int rc;
+  if ((rc = ensure(h, h->table, 2 * slots))) return rc;
+  if ((rc = ensure(h, h->ovf_table, 2 * slots))) return rc;
+  if ((rc = ensure(h, h->ovf_list, 2 * (n ? n : 1)))) return rc;
+  if ((rc = ensure(h, h->claim, slots / 64))) return rc;
+  if (slots != h->slots) h->built = false;
+  h->slots = slots;
+  h->mask = slots - 1;
+  return HJ_OK;
+}
+
+int wide_build(hj_handle* h, const u64* dR, u64 n) {
+  int rc;
+  if ((rc = zero_async(h, h->table.p, 2 * h->slots))) return rc;
+  CK(cudaMemsetAsync(h->claim.p, 0, h->slots / 8, h->stream));
+  mark(h, E_CLEAR);
+  const u64 chunks = (n + kGtThreads * kWGtIPT - 1) / (kGtThreads * kWGtIPT);
+  int grid = grid_for(h, (const void*)gw_build_kernel, kGtThreads, 0);
+  if ((u64)grid > chunks) grid = (int)(chunks ? chunks : 1);
+  gw_build_kernel<<<grid, kGtThreads, 0, h->stream>>>(reinterpret_cast<const tup16*>(dR), n, reinterpret_cast<tup16*>(h->table.p),
+                                                      reinterpret_cast<u32*>(h->claim.p), (u32)h->mask, h->cfg.key_mask,
+                                                      h->cfg.probe_length, reinterpret_cast<tup16*>(h->ovf_list.p), h->ctr);
+  gw_ovf_clear_kernel<<<h->sm_count * 8, 256, 0, h->stream>>>(reinterpret_cast<tup16*>(h->ovf_table.p), h->ctr, h->ovf_table.cap / 2);
+  gw_ovf_insert_kernel<<<h->sm_count * 8, 256, 0, h->stream>>>(reinterpret_cast<const tup16*>(h->ovf_list.p),
+                                                               reinterpret_cast<tup16*>(h->ovf_table.p), h->ctr, h->cfg.key_mask,
+                                                               h->ovf_table.cap / 2);
+  h->launches += 3;
+  CK(cudaGetLastError());
+  mark(h, E_BUILD);
+  h->built = true;
+  return HJ_OK;
+}
+
+int wide_probe(hj_handle* h, const u64* dS, u64 m) {
+  mark(h, E_PROBE0);
+  if (m) {
+    int grid = grid_for(h, (const void*)gw_probe_kernel, kGtThreads, 0);
+    gw_probe_kernel<<<grid, kGtThreads, 0, h->stream>>>(reinterpret_cast<const tup16*>(dS), m, reinterpret_cast<const tup16*>(h->table.p),
+                                                        (u32)h->mask, h->cfg.key_mask, h->cfg.probe_length,
+                                                        reinterpret_cast<const tup16*>(h->ovf_table.p), h->ovf_table.cap / 2, h->ctr);
+    h->launches++;
+    CK(cudaGetLastError());
+  }
+  mark(h, E_PROBE);
+  return HJ_OK;
+}
+
+// hj_join / hj_build / hj_probe on 16-byte tuples
+int wide_join(hj_handle* h, const u64* R, u64 n, const u64* S, u64 m, hj_result* res, bool build, bool probe) {
+  int rc;
+  const u64 *dR = nullptr, *dS = nullptr;
+  bool pendR = false, pendS = false;
+  const int algo = h->cfg.algo;
+  if (algo != HJ_ALGO_RADIX && algo != HJ_ALGO_ATOMIC) {
+    snprintf(h->err, sizeof(h->err), "16-byte tuples: HJ_ALGO_RADIX and HJ_ALGO_ATOMIC only");
+    return HJ_EINVAL;
+  }
+  mark(h, E_T0);
+  mark(h, E_CP0, h->copy_stream);
+  if (build && (rc = stage(h, R, 2 * n, h->stageR, &dR, E_CPR, &pendR))) return rc;
+  if (probe && (rc = stage(h, S, 2 * m, h->stageS, &dS, E_CPS, &pendS))) return rc;
+  if (algo == HJ_ALGO_RADIX) {
+    if (!build || !probe) return HJ_ESTATE;
+    return run_wide_radix_join(h, dR, n, pendR, dS, m, pendS, res);
+  }
+  if (build) {
+    if ((rc = wide_prepare_table(h, n))) return rc;
+    CK(cudaMemsetAsync(h->ctr, 0, C_COUNT * sizeof(u64), h->stream));
+    if ((rc = wait_staged(h, E_CPR, pendR))) return rc;
+    if ((rc = wide_build(h, dR, n))) return rc;
+  } else {
+    if (!h->built) return HJ_ESTATE;
+    if ((rc = clear_probe_counters(h))) return rc;
+  }
+  if (probe) {
+    if ((rc = wait_staged(h, E_CPS, pendS))) return rc;
+    if ((rc = wide_probe(h, dS, m))) return rc;
+  }
+  mark(h, E_END);
+  if ((rc = fetch_counters(h))) return rc;
+  if (res) {
+    fill_common(h, res);
+    res->path_taken = HJ_PATH_GLOBAL;
+    res->hbm_bytes = 32ull * (build ? n : 0) + 32ull * (probe ? m : 0);  // 16 B read + 16 B slot per tuple
+  }
+  return HJ_OK;
+}
+
+}  // namespace
+
 void xchg_free(hj_handle* h);  // defined with the pipelined exchange at the end of this file
 
 // ===========================================================================
@@ -1212,6 +1414,8 @@ int hj_create(const hj_config* cfg, hj_handle** out) {
   if (!cfg || !out || cfg->struct_size != sizeof(hj_config)) return HJ_EINVAL;
   if (cfg->algo < HJ_ALGO_ATOMIC || cfg->algo > HJ_ALGO_SORTMERGE) return HJ_EINVAL;
   if (cfg->probe_length == 0 || cfg->probe_length > 1024) return HJ_EINVAL;
+  if (cfg->tuple_bytes != 0 && cfg->tuple_bytes != 8 && cfg->tuple_bytes != 16) return HJ_EINVAL;
+  if (cfg->tuple_bytes == 16 && cfg->algo != HJ_ALGO_RADIX && cfg->algo != HJ_ALGO_ATOMIC) return HJ_EINVAL;
   int ndev = hj_device_count();
   if (ndev <= 0 || cfg->device < 0 || cfg->device >= ndev) return HJ_ECUDA;
   hj_handle* h = new (std::nothrow) hj_handle();
@@ -1307,6 +1511,7 @@ int hj_build(hj_handle* h, const uint64_t* R, uint64_t n, hj_result* res) {
   CK(cudaSetDevice(h->device));
   if (res) memset(res, 0, sizeof(*res));
   reset_events(h);
+  if (wide(h)) return wide_join(h, (const u64*)R, n, nullptr, 0, res, true, false);
   int rc;
   if ((rc = prepare_table(h, n))) return rc;
   mark(h, E_T0);
@@ -1327,6 +1532,7 @@ int hj_probe(hj_handle* h, const uint64_t* S, uint64_t m, hj_result* res) {
   CK(cudaSetDevice(h->device));
   if (res) memset(res, 0, sizeof(*res));
   reset_events(h);
+  if (wide(h)) return wide_join(h, nullptr, 0, (const u64*)S, m, res, false, true);
   int rc;
   const u64* dS = nullptr;
   bool pendS = false;
@@ -1387,6 +1593,7 @@ int hj_join(hj_handle* h, const uint64_t* R, uint64_t n, const uint64_t* S, uint
   CK(cudaSetDevice(h->device));
   if (res) memset(res, 0, sizeof(*res));
   reset_events(h);
+  if (wide(h)) return wide_join(h, (const u64*)R, n, (const u64*)S, m, res, true, S != nullptr);
   int rc;
   const int algo = h->cfg.algo;
   const u64 *dR = nullptr, *dS = nullptr;
@@ -1527,15 +1734,17 @@ int hj_checksums(hj_handle* h, const uint64_t* R, uint64_t n, hj_result* res) {
   const u64* dR = nullptr;
   if (R && n) {
     bool pend = false;
-    if ((rc = stage(h, (const u64*)R, n, h->stageR, &dR, E_CPR, &pend, false))) return rc;
+    if ((rc = stage(h, (const u64*)R, (wide(h) ? 2 : 1) * n, h->stageR, &dR, E_CPR, &pend, wide(h)))) return rc;
     if ((rc = wait_staged(h, E_CPR, pend))) return rc;
   }
   CK(cudaMemsetAsync(h->ctr + C_SUM0, 0, 3 * sizeof(u64), h->stream));
   int grid = h->sm_count * 8;
-  if (dR) sum_u64_kernel<<<grid, 256, 0, h->stream>>>(dR, n, h->ctr + C_SUM0);
+  const u64 words = wide(h) ? 2 : 1;  // 16-byte tuples: sums of key + payload words
+  if (dR) sum_u64_kernel<<<grid, 256, 0, h->stream>>>(dR, words * n, h->ctr + C_SUM0);
   if (h->built) {
-    sum_u64_kernel<<<grid, 256, 0, h->stream>>>(h->table.p, h->slots, h->ctr + C_SUM1);
-    sum_ovf_kernel<<<grid, 256, 0, h->stream>>>(h->ovf_list.p, h->ctr, h->ctr + C_SUM2);
+    sum_u64_kernel<<<grid, 256, 0, h->stream>>>(h->table.p, words * h->slots, h->ctr + C_SUM1);
+    if (wide(h)) sum_ovf16_kernel<<<grid, 256, 0, h->stream>>>(reinterpret_cast<const tup16*>(h->ovf_list.p), h->ctr, h->ctr + C_SUM2);
+    else sum_ovf_kernel<<<grid, 256, 0, h->stream>>>(h->ovf_list.p, h->ctr, h->ctr + C_SUM2);
   }
   CK(cudaGetLastError());
   if ((rc = fetch_counters(h))) return rc;
@@ -1568,7 +1777,7 @@ int hj_radix_partition(hj_handle* h, const uint64_t* in, uint64_t n, uint32_t sh
   CK(cudaMemsetAsync(rb.ghist.p, 0, F * sizeof(u64), h->stream));
   if ((rc = launch_hist(h, (const u64*)in, n, dg, F, rb.ghist.p))) return rc;
   rx_scan_kernel<<<1, kScanThreads, 0, h->stream>>>(rb.ghist.p, F, (u64*)offsets, rb.cursors.p, F, rb.poff.p,
-                                                    rb.pcur.p, rb.ptiles.p, rb.one.p, tile, nullptr);
+                                                    rb.pcur.p, rb.ptiles.p, rb.one.p, tile, nullptr, n);
   CK(cudaGetLastError());
   if ((rc = launch_scatter_t<kExactIPT>(h, (const u64*)in, (u64*)out, dg, F, 1, rb.poff.p, rb.ptiles.p, rb.cursors.p,
                                 (n + tile - 1) / tile)))
@@ -1599,7 +1808,7 @@ int hj_exchange_partition(hj_handle* h, const uint64_t* in, uint64_t n, uint32_t
   CK(cudaMemsetAsync(rb.ghist.p, 0, F * sizeof(u64), h->stream));
   if ((rc = launch_hist(h, (const u64*)in, n, dg, F, rb.ghist.p))) return rc;
   rx_scan_kernel<<<1, kScanThreads, 0, h->stream>>>(rb.ghist.p, F, (u64*)offsets, rb.cursors.p, F, rb.poff.p,
-                                                    rb.pcur.p, rb.ptiles.p, rb.one.p, tile, nullptr);
+                                                    rb.pcur.p, rb.ptiles.p, rb.one.p, tile, nullptr, n);
   CK(cudaGetLastError());
   if ((rc = launch_scatter_t<kExactIPT>(h, (const u64*)in, (u64*)out, dg, F, 1, rb.poff.p, rb.ptiles.p, rb.cursors.p,
                                 (n + tile - 1) / tile)))

@@ -127,7 +127,9 @@ constexpr int kScanThreads = 1024;
 __global__ void __launch_bounds__(kScanThreads)
 rx_scan_kernel(const u64* __restrict__ ghist, u32 nbins, u64* __restrict__ offsets, u64* __restrict__ cursors,
                u32 f2, u64* __restrict__ parent_off, u64* __restrict__ parent_cursor, u64* __restrict__ parent_tiles,
-               u64* __restrict__ one, u32 tile, u64* __restrict__ max_bin) {
+               u64* __restrict__ one, u32 tile, u64* __restrict__ max_bin, u64 n_input) {
+  // n_input: tuples in the relation the first pass READS.  It can exceed the histogram's total: tuples equal to 0
+  // (the empty-slot sentinel) are counted nowhere, but the pass that reads the raw input must still walk over them.
   __shared__ u64 wsum[kScanThreads / 32];
   __shared__ u64 carry_s;
   const u32 tid = threadIdx.x;
@@ -170,7 +172,7 @@ rx_scan_kernel(const u64* __restrict__ ghist, u32 nbins, u64* __restrict__ offse
   if (tid == 0) {
     offsets[nbins] = carry_s;
     if (one) {  // one-parent view of the whole relation: offsets {0, n}, tiles {0, ceil(n/tile)}
-      one[0] = 0; one[1] = carry_s; one[2] = 0; one[3] = (carry_s + tile - 1) / tile;
+      one[0] = 0; one[1] = n_input; one[2] = 0; one[3] = (n_input + tile - 1) / tile;
     }
   }
   if (max_bin) {
@@ -186,7 +188,8 @@ rx_scan_kernel(const u64* __restrict__ ghist, u32 nbins, u64* __restrict__ offse
   if (parent_off) {
     const u32 nparent = nbins / f2;
     for (u32 p = tid; p <= nparent; p += kScanThreads) {
-      const u64 o = offsets[p * f2];  // p == nparent reads offsets[nbins]
+      u64 o = offsets[p * f2];  // p == nparent reads offsets[nbins]
+      if (nparent == 1 && p == 1) o = n_input;  // single pass: the one parent is the raw input
       parent_off[p] = o;
       if (p < nparent) parent_cursor[p] = o;
     }

@@ -74,7 +74,12 @@ typedef struct hj_config {
   uint64_t pass1_bits;       /* 2-pass plans: radix bits of pass 1; 0 = floor(bits/2) as
                                 prj_params.h:76-78.  The fused multi-GPU exchange uses a
                                 smaller pass 1 so that G << pass1_bits stays ~128 bins    */
-  uint64_t reserved[3];
+  uint64_t tuple_bytes;      /* 0 / 8: one 8-byte word per tuple (default).  16: mc's KEY_8B tuple
+                                (mc/src/types.h:22-37) = {uint64_t key; uint64_t payload}: R / S point to
+                                2 words per tuple, sizes still count tuples; key = word 0 & key_mask, key 0 =
+                                empty; checksum = sum over pairs of all four words.  HJ_ALGO_RADIX and
+                                HJ_ALGO_ATOMIC through hj_join / hj_build / hj_probe / hj_checksums only */
+  uint64_t reserved[2];
 } hj_config;
 
 /* Per-call outcome.  The first block mirrors the JSON the reference prints

@@ -247,6 +247,38 @@ void orc_true_join(const uint64_t *R, uint64_t n, const uint64_t *S, uint64_t m,
   if (checksum) *checksum = sum;
 }
 
+/* The same join on mc's KEY_8B tuple, {int64 key; int64 payload} (mc/src/types.h:22-37): true equi-join
+ * count (no_partitioning_join.c:270-310 counts `matches++` per equal key) and the checksum extended to the
+ * four words of a pair.  T = n tuples of two words {key, payload}. */
+void orc_true_join16(const uint64_t *R, uint64_t n, const uint64_t *S, uint64_t m,
+                     uint64_t key_mask, uint64_t *matches, uint64_t *checksum) {
+  kv_t *r = (kv_t *)malloc((n ? n : 1) * sizeof(kv_t));
+  kv_t *s = (kv_t *)malloc((m ? m : 1) * sizeof(kv_t));
+  uint64_t nr = 0, ns = 0;
+  for (uint64_t i = 0; i < n; i++)
+    if (R[2 * i] & key_mask) { r[nr].key = R[2 * i] & key_mask; r[nr].val = R[2 * i] + R[2 * i + 1]; nr++; }
+  for (uint64_t i = 0; i < m; i++)
+    if (S[2 * i] & key_mask) { s[ns].key = S[2 * i] & key_mask; s[ns].val = S[2 * i] + S[2 * i + 1]; ns++; }
+  qsort(r, nr, sizeof(kv_t), kv_cmp);
+  qsort(s, ns, sizeof(kv_t), kv_cmp);
+  uint64_t i = 0, j = 0, cnt = 0, sum = 0;
+  while (i < nr && j < ns) {
+    if (r[i].key < s[j].key) i++;
+    else if (r[i].key > s[j].key) j++;
+    else {
+      uint64_t k = r[i].key, cr = 0, cs = 0, sr = 0, ss = 0;
+      while (i < nr && r[i].key == k) { cr++; sr += r[i].val; i++; }
+      while (j < ns && s[j].key == k) { cs++; ss += s[j].val; j++; }
+      cnt += cr * cs;
+      sum += sr * cs + ss * cr;
+    }
+  }
+  free(r);
+  free(s);
+  if (matches) *matches = cnt;
+  if (checksum) *checksum = sum;
+}
+
 /* ------------------------------------------------------------------------ */
 /* radix path: mc/src/parallel_radix_join.c                                  */
 /* ------------------------------------------------------------------------ */

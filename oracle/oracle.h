@@ -72,6 +72,9 @@ int orc_gt_build_probe_serial(const uint64_t *R, uint64_t n,
 void orc_true_join(const uint64_t *R, uint64_t n, const uint64_t *S,
                    uint64_t m, uint64_t key_mask, uint64_t *matches,
                    uint64_t *checksum);
+/* KEY_8B tuples (mc/src/types.h:22-37): R, S = n, m tuples of two words {key, payload}; key 0 = no tuple */
+void orc_true_join16(const uint64_t *R, uint64_t n, const uint64_t *S, uint64_t m,
+                     uint64_t key_mask, uint64_t *matches, uint64_t *checksum);
 
 /* ---- radix path ---------------------------------------------------------- */
 

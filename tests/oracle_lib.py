@@ -36,6 +36,8 @@ class Oracle:
         L.orc_gt_build_probe_serial.argtypes = [vp, u64, vp, u64, C.c_uint32, C.c_uint32, C.c_uint32, C.c_int,
                                                 C.POINTER(orc_gt_result)]
         L.orc_true_join.argtypes = [vp, u64, vp, u64, u64, C.POINTER(u64), C.POINTER(u64)]
+        if hasattr(L, "orc_true_join16"):
+            L.orc_true_join16.argtypes = [vp, u64, vp, u64, u64, C.POINTER(u64), C.POINTER(u64)]
         L.orc_radix_partition.argtypes = [vp, u64, C.c_uint32, C.c_uint32, vp, vp]
         L.orc_pro_checksum.restype = u64
         L.orc_pro_checksum.argtypes = [vp, u64, C.c_uint32]
@@ -127,6 +129,18 @@ class Oracle:
         out = np.empty(count, dtype=np.uint64)
         self.lib.orc_feistel_gen(kind, first, count, domain, seed, _p(out))
         return out
+
+
+def _true_join16(self, R, S, key_mask=0xFFFFFFFFFFFFFFFF):
+    """KEY_8B tuples: R, S uint64 arrays of shape (n, 2) = {key, payload}."""
+    R = np.ascontiguousarray(R, dtype=np.uint64).reshape(-1, 2)
+    S = np.ascontiguousarray(S, dtype=np.uint64).reshape(-1, 2)
+    mt, ck = C.c_uint64(0), C.c_uint64(0)
+    self.lib.orc_true_join16(_p(R), R.shape[0], _p(S), S.shape[0], key_mask, C.byref(mt), C.byref(ck))
+    return mt.value, ck.value
+
+
+Oracle.true_join16 = _true_join16
 
 
 class Reference:

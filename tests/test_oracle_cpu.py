@@ -266,3 +266,31 @@ def test_mc_nonunique_emits_key_zero(hj):
     take these relations with bias=1."""
     a = hj.mc_relation_nonunique(200000, 1000, 12345)
     assert (a == 0).sum() > 0 and a.max() <= 999
+
+
+def test_oracle_join16_is_pinned_on_the_reference_key8b_build(oracle, hj):
+    """16-byte tuples: mc compiled with -DKEY_8B (mc/src/types.h:22-37) runs NPO on its own PK / FK relations
+    (same generator code, so the keys are csrc/datagen.cpp's); its match count is orc_true_join16's."""
+    import subprocess
+    exe = os.path.join(ROOT, "oracle", "_ref", "mc_key8b")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/mc_key8b not built")
+    n, m = 100000, 350000
+    out = subprocess.run([exe, "--algo=NPO", "--nthreads=4", f"--r-size={n}", f"--s-size={m}"], capture_output=True,
+                         text=True, timeout=300)
+    ref_matches = int([l for l in out.stdout.splitlines() if "Results =" in l][0].split("=")[1].split(".")[0])
+    rng = np.random.default_rng(1)
+    R = np.stack([hj.mc_relation_pk(n), rng.integers(0, 1 << 62, n, dtype=np.uint64)], axis=1)
+    S = np.stack([hj.mc_relation_fk(m, n), rng.integers(0, 1 << 62, m, dtype=np.uint64)], axis=1)
+    matches, checksum = oracle.true_join16(R, S)
+    assert matches == ref_matches == m
+    # every S tuple meets the R tuple with its key: checksum = sum of all S words + the R words of the partners
+    pay_r = np.zeros(n + 1, dtype=np.uint64)
+    pay_r[R[:, 0]] = R[:, 1]
+    want = (int(S.sum(dtype=np.uint64)) + int(S[:, 0].sum(dtype=np.uint64)) + int(pay_r[S[:, 0]].sum(dtype=np.uint64))) % (1 << 64)
+    assert checksum == want
+    # duplicates on both sides, zero keys ignored, key mask honoured
+    Rd = np.array([[5, 1], [5, 2], [7, 3], [0, 9], [(1 << 40) | 5, 4]], dtype=np.uint64)
+    Sd = np.array([[5, 10], [5, 20], [7, 30], [0, 1], [8, 1]], dtype=np.uint64)
+    assert oracle.true_join16(Rd, Sd) == (5, (2 * (5 + 10 + 5 + 20) + 2 * (5 + 1 + 5 + 2) + (7 + 3 + 7 + 30)))
+    assert oracle.true_join16(Rd, Sd, 0xFFFFFFFF)[0] == 7

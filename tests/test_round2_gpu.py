@@ -306,3 +306,49 @@ def test_experiment_harness_w_sweep(hj, tmp_path):
     subprocess.run([sys.executable, os.path.join(root, "experiments", "plot_perf.py"), "--in", str(out), "--out", str(svg)],
                    check=True, capture_output=True)
     assert svg.read_text().startswith("<svg")
+
+
+# ---- 16-byte tuples (mc's KEY_8B, mc/src/types.h:22-37) ---------------------------------------------
+def _wide(keys, seed):
+    rng = np.random.default_rng(seed)
+    return np.ascontiguousarray(np.stack([keys.astype(np.uint64), rng.integers(0, 1 << 63, keys.size, dtype=np.uint64)], axis=1))
+
+
+@pytest.mark.parametrize("algo,kw", [("radix", {}), ("radix", dict(num_partitions=1 << 9, passes=1)),
+                                     ("radix", dict(num_partitions=1 << 12, passes=2)), ("atomic", {})])
+@pytest.mark.parametrize("case", ["pk_fk", "duplicates", "wide_keys", "zeros"])
+def test_wide_tuples_join_equals_oracle(hj, oracle, algo, kw, case):
+    n, m = (1 << 16) + 3, (3 << 16) + 5
+    if case == "pk_fk":
+        R, S = _wide(hj.mc_relation_pk(n), 1), _wide(hj.mc_relation_fk(m, n), 2)
+    elif case == "duplicates":
+        R, S = _wide(hj.generate_data("uniform", n, 1 << 13, 16), 3), _wide(hj.generate_data("uniform", m, 1 << 13, 16), 4)
+    elif case == "wide_keys":   # keys above 2^32 (and above the table mask): the whole 64-bit key is compared
+        k = hj.mc_relation_pk(n) * np.uint64(0x100000001)
+        R, S = _wide(k, 5), _wide(np.concatenate([k, k[: m - n] + np.uint64(1 << 40)]), 6)
+    else:
+        R, S = _wide(hj.mc_relation_nonunique(n, 4096, 12345), 7), _wide(hj.mc_relation_nonunique(m, 4096, 54321), 8)
+    want = oracle.true_join16(R, S)
+    assert want[0] > 0
+    with hj.HashJoin(algo, tuple_bytes=16, **kw) as h:
+        res = h.join(R, S)
+        assert (res.matches, res.checksum) == want
+        assert res.zero_keys == int((R[:, 0] == 0).sum() + (S[:, 0] == 0).sum())
+        dR, dS = h.to_device(R.reshape(-1)), h.to_device(S.reshape(-1))   # device-resident inputs
+        res2 = h.join(dR, dS)
+        assert (res2.matches, res2.checksum) == want and res2.us_h2d == 0.0
+        if algo == "atomic":
+            sums = h.checksums(R)
+            assert sums.input_sum == int(R.sum(dtype=np.uint64))
+            zero_sum = int(R[R[:, 0] == 0].sum(dtype=np.uint64))     # tuples with key 0 are in neither table
+            assert (sums.table_sum + sums.overflow_sum + zero_sum) % (1 << 64) == sums.input_sum
+            h.build(R)
+            p = h.probe(S)
+            assert (p.matches, p.checksum) == want
+        h.device_free(dR[0]); h.device_free(dS[0])
+
+
+def test_wide_tuples_refuse_what_is_not_built(hj):
+    with pytest.raises(hj.HJError) as e:
+        hj.HashJoin("adaptive", tuple_bytes=16)
+    assert e.value.code == hj.HJ_EINVAL
