@@ -113,7 +113,6 @@ gt_build_kernel(const u64* __restrict__ R, SegMap sm, u64* __restrict__ table, u
     for (int j = 0; j < IPT; j++) {
       const u64 i = tbase + (u64)j * kGtThreads + tid;
       v[j] = i < seg_end ? ld_stream(R + i) : 0ull;
-      if (i < seg_end && v[j] == 0ull) ++zeros;
     }
 
     // the band: 32768 slots starting at the tile's lowest home slot (rounded down to a bitmap word)
@@ -157,6 +156,8 @@ gt_build_kernel(const u64* __restrict__ R, SegMap sm, u64* __restrict__ table, u
         const u32 r = hm - base;
         if ((u64)r + L + 32 < kGtBand && (u64)hm + L + 32 <= mask) rel[j] = r;
         else farbits |= 1u << j;
+      } else if (tbase + (u64)j * kGtThreads + tid < seg_end) {
+        ++zeros;  // a tuple equal to 0, the empty-slot sentinel: not inserted, reported (hj_result.zero_keys)
       }
     }
 
@@ -305,13 +306,13 @@ gt_nocc_build_kernel(const u64* __restrict__ R, SegMap sm, u64* __restrict__ tab
     for (int j = 0; j < IPT; j++) {
       const u64 i = base + (u64)j * kGtThreads + tid;
       v[j] = i < seg_end ? ld_stream(R + i) : 0ull;
-      if (i < seg_end && v[j] == 0ull) ++zeros;
     }
     u32 att[IPT], pend = 0, failed_bits = 0;
 #pragma unroll
     for (int j = 0; j < IPT; j++) {
       att[j] = 0;
       if (v[j]) pend |= 1u << j;
+      else if (base + (u64)j * kGtThreads + tid < seg_end) ++zeros;
     }
 #pragma unroll 1
     while (pend) {
@@ -509,13 +510,14 @@ gt_probe_home_kernel(const u64* __restrict__ S, u64 m, const u64* __restrict__ t
     for (int j = 0; j < IPT; j++) {
       const u64 i = base + (u64)j * kGtThreads;
       s[j] = i < m ? ld_stream(S + i) : 0ull;
-      if (i < m && s[j] == 0ull) ++zeros;
     }
 #pragma unroll
     for (int j = 0; j < IPT; j++) cur[j] = s[j] ? __ldg(table + ((s[j] & key_mask) & mask)) : 0ull;
 #pragma unroll
-    for (int j = 0; j < IPT; j++)
+    for (int j = 0; j < IPT; j++) {
       if (cur[j] != 0ull && (cur[j] & key_mask) == (s[j] & key_mask)) { ++wmatches; checksum += cur[j] + s[j]; }
+      if (s[j] == 0ull && base + (u64)j * kGtThreads < m) ++zeros;  // (after the loads: nothing waits in between)
+    }
   }
   u64 v[4] = {(u64)wmatches, checksum, (u64)wmatches, (u64)zeros};
   u64* const d[4] = {ctr + C_MATCHES, ctr + C_CHECKSUM, ctr + C_WINDOW_MATCHES, ctr + C_ZERO_KEYS};
@@ -552,8 +554,10 @@ gt_probe_kernel(const u64* __restrict__ S, u64 m, const u64* __restrict__ table,
     for (int j = 0; j < IPT; j++) {
       const u64 i = base + (u64)j * 32;
       s[j] = i < m ? ld_stream(S + i) : 0ull;
-      if (i < m && s[j] == 0ull) ++zeros;
     }
+#pragma unroll
+    for (int j = 0; j < IPT; j++)
+      if (s[j] == 0ull && base + (u64)j * 32 < m) ++zeros;
     u32 full = 0;  // bit j: window exhausted without an empty slot
     // dense: homes of the warp = h0 .. h0 + IPT*32 - 1, no wrap-around, every tuple valid
     const u64 h0 = __shfl_sync(0xffffffffu, (s[0] & key_mask) & mask, 0);

@@ -297,7 +297,7 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
   __shared__ u64* s_peer[PEER ? kScMaxPeers : 1];
   if (PEER && threadIdx.x < dg.ndest) s_peer[threadIdx.x] = peer_out[threadIdx.x];
   __shared__ u64 s_pend[OPT ? kScParentCache + 1 : 1];
-  u32 key_hi = 0, zeros = 0;  // OPT == 1 (the pass that sees the input first, no rx_hist): key width, zero tuples
+  u32 key_hi = 0;  // OPT == 1 (the pass that sees the input first, no rx_hist): key width (and zero tuples, below)
   constexpr int TILE = kScThreads * IPT;
   static_assert(TILE <= 65536, "rank is packed into 16 bits");
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -405,8 +405,6 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
         const u32 d = sc_digit<MODE>(dg, fmask, v[j]);
         dr[j] = (d << 16) | atomicAdd(hist + d, 1u);
         if (OPT == 1) key_hi |= (u32)(v[j] >> 32);
-      } else if (OPT == 1) {
-        zeros += 2u * ((j >> 1) * kScThreads + threadIdx.x) + (j & 1) < cnt;  // a real tuple, not tile padding
       }
     }
     // BULK: the previous tile's bulk copies have finished READING shared memory
@@ -470,6 +468,9 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
           }
           if (BULK) rcnt[b] = c;
           run += c;
+          // tuples equal to 0 (the empty-slot sentinel) were not ranked: what the tile's histogram lacks of its
+          // length is their number (reported, hj_result.zero_keys; no per-thread counter: registers are full)
+          if (OPT == 1 && b == F - 1 && run != cnt) atomicAdd(opt.ctr + C_ZERO_KEYS, (u64)(cnt - run));
         }
       }
     }
@@ -546,8 +547,6 @@ rx_scatter_kernel(const u64* __restrict__ in, u64* __restrict__ out, Digit dg, u
     if (key_hi && lane_id() == 0) atomicOr(opt.ctr + C_PAY_HI, (u64)key_hi);
     key_hi &= (u32)(dg.key_mask >> 32);
     if (key_hi && lane_id() == 0) atomicOr(opt.ctr + C_KEY_HI, (u64)key_hi);
-    zeros = __reduce_add_sync(0xffffffffu, zeros);
-    if (zeros && lane_id() == 0) atomicAdd(opt.ctr + C_ZERO_KEYS, (u64)zeros);
   }
 }
 
