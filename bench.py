@@ -50,7 +50,7 @@ def parse_args():
                          "counts first); nccl = partition + NCCL all-to-all")
     ap.add_argument("--chunks", type=int, default=0,
                     help="split S into this many chunks so the exchange of chunk c+1 overlaps pass 2 + join of chunk c "
-                         "(a join is additive over disjoint parts of S); 0 = 4 for xchg, 1 otherwise")
+                         "(a join is additive over disjoint parts of S); 0 = 8 for xchg, 1 otherwise")
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
                     help="weak: every GPU holds 2^log-r x 2^log-s; strong: those are the GLOBAL sizes, split over the GPUs "
                          "(BASELINE configs[4]: --scaling strong --log-r 30 --log-s 33)")
@@ -379,7 +379,7 @@ class Rank:
             self.n, self.m = self.n // G, self.m // G
         self.domain = G * self.n
         if args.chunks == 0:
-            args.chunks = 4 if (G > 1 and args.exchange == "xchg") else 1
+            args.chunks = 8 if (G > 1 and args.exchange == "xchg") else 1
         self.xchg = G > 1 and args.exchange == "xchg"
         self.h = hj.HashJoin(args.algo, device=self.local, num_partitions=(1 << args.radix_bits) if args.radix_bits else 0,
                              passes=args.passes)

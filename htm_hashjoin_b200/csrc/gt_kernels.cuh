@@ -511,15 +511,31 @@ gt_probe_home_kernel(const u64* __restrict__ S, u64 m, const u64* __restrict__ t
       const u64 i = base + (u64)j * kGtThreads;
       s[j] = i < m ? ld_stream(S + i) : 0ull;
     }
+    // Two batches of IPT loads in flight, S then the home slots.  ptxas otherwise interleaves them pairwise to save
+    // registers (2-3 loads in flight: 337 -> 430 us at 2^27); a data dependency it cannot see through makes every
+    // table address depend on ALL S loads and every compare on ALL table loads (`none` is 0 at run time: the table
+    // has at most 2^32 slots).  The slot of key 0 is slot 0, so the table load needs no predicate, and a padding
+    // lane (s = 0) can never match: a stored tuple has a non-zero key.
+    const u64 none = 0ull - (mask >> 63);
+    u64 dep = 0;
 #pragma unroll
-    for (int j = 0; j < IPT; j++) cur[j] = s[j] ? __ldg(table + ((s[j] & key_mask) & mask)) : 0ull;
+    for (int j = 0; j < IPT; j++) dep |= s[j];
+    dep &= none;
+#pragma unroll
+    for (int j = 0; j < IPT; j++) cur[j] = __ldg(table + (((s[j] & key_mask) & mask) | dep));
+    dep = 0;
+#pragma unroll
+    for (int j = 0; j < IPT; j++) dep |= cur[j];
+    dep &= none;
 #pragma unroll
     for (int j = 0; j < IPT; j++) {
-      if (cur[j] != 0ull && (cur[j] & key_mask) == (s[j] & key_mask)) { ++wmatches; checksum += cur[j] + s[j]; }
-      if (s[j] == 0ull && base + (u64)j * kGtThreads < m) ++zeros;  // (after the loads: nothing waits in between)
+      const u64 t = cur[j] | dep;
+      if (t != 0ull && (t & key_mask) == (s[j] & key_mask)) { ++wmatches; checksum += t + s[j]; }
+      zeros += s[j] == 0ull;  // padding lanes included: taken out again below
     }
   }
-  u64 v[4] = {(u64)wmatches, checksum, (u64)wmatches, (u64)zeros};
+  if (blockIdx.x == 0 && tid == 0) zeros -= (u32)(nchunks * TILE - m);  // (mod 2^32: the block sum below is mod 2^64)
+  u64 v[4] = {(u64)wmatches, checksum, (u64)wmatches, (u64)(long long)(int)zeros};  // (sign-extended: may be negative here)
   u64* const d[4] = {ctr + C_MATCHES, ctr + C_CHECKSUM, ctr + C_WINDOW_MATCHES, ctr + C_ZERO_KEYS};
   block_sum_atomic<4, kGtThreads>(v, d);
 }

@@ -2103,6 +2103,7 @@ constexpr u64 kXScratch = (u64)kScThreads * 32 + 2;  // diverted claims of one s
 struct Xchg {
   u32 G = 0, rank = 0, b1 = 0, F1 = 0, nstages = 0, domain_bits = 0;
   bool connected = false, started = false;
+  bool pow2_domain = false;  // keys lie in [1, 2^domain_bits] (caller's promise, hj_xchg_create): the shift form applies
   u64 window_elems = 0, epoch = 0;
   u64* window = nullptr;
   u64* peer_window[kScMaxPeers];
@@ -2130,7 +2131,7 @@ static void xchg_preload_kernels() {
   const void* ks[] = {
       (const void*)rx_xchg_init_kernel, (const void*)rx_xchg_wait_kernel, (const void*)rx_xchg_parents_kernel,
       (const void*)rx_opt_init_kernel, (const void*)rx_tasks_kernel,
-      (const void*)rx_scatter_kernel<16, 2, true, 1, true>,
+      (const void*)rx_scatter_kernel<16, 2, true, 1, true>, (const void*)rx_scatter_kernel<16, 3, true, 1, true>,
       (const void*)sc_opt_kernel<8>(1, true), (const void*)sc_opt_kernel<8>(1, false),
       (const void*)sc_opt_kernel<16>(1, true), (const void*)sc_opt_kernel<16>(1, false),
       (const void*)sc_opt_kernel<32>(1, true), (const void*)sc_opt_kernel<32>(1, false),
@@ -2206,6 +2207,7 @@ int hj_xchg_create(hj_handle* h, uint32_t n_ranks, uint32_t rank, uint64_t n_loc
   h->xc = x;
   x->G = n_ranks; x->rank = rank; x->pl = ch.pl; x->b1 = ch.pl.b1; x->F1 = 1u << ch.pl.b1;
   x->nstages = 1 + s_chunks; x->domain_bits = domain_bits;
+  x->pow2_domain = true;  // dest = ((key-1) * G) >> domain_bits == (key-1) >> (domain_bits - log2 G) for G = 2^k
   x->nR = n_local; x->mS = m_local / s_chunks;
   x->C2R = opt_region_cap(x->nR, ch.pl.bits);
   x->C2S = opt_region_cap(x->mS, ch.pl.bits);
@@ -2318,7 +2320,13 @@ int xchg_scatter_stage(hj_handle* h, Xchg* x, u32 t, const u64* in) {
   dg.key_mask = h->cfg.key_mask; dg.mode = 3; dg.ndest = G; dg.domain_bits = x->domain_bits; dg.b1 = x->b1;
   constexpr int IPT = 16;  // 8192-tuple tiles, two CTAs per SM: the HBM-speed shape of the local passes
   const u32 tile = kScThreads * IPT;
-  auto k = rx_scatter_kernel<IPT, 2, true, 1, true>;
+  // 32-bit keys and a power-of-two domain: the shift form of the owner function (sc_digit<3>)
+  u32 lg = 0;
+  while ((1u << lg) < G) lg++;
+  const bool fast = (h->cfg.key_mask & 0xffffffffull) == 0xffffffffull && x->domain_bits >= lg && x->domain_bits <= 32 &&
+                    x->pow2_domain;
+  if (fast) dg.shift = x->domain_bits - lg;
+  auto k = fast ? rx_scatter_kernel<IPT, 3, true, 1, true> : rx_scatter_kernel<IPT, 2, true, 1, true>;
   const size_t smem = (size_t)tile * 8 + (size_t)F * 16 + sc_bulk_extra(F);
   CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int grid = grid_for(h, (const void*)k, kScThreads, smem);
@@ -2447,7 +2455,9 @@ int hj_xchg_start(hj_handle* h, const uint64_t* R, const uint64_t* S, uint64_t e
   const u64 per = (x->nR >> x->pl.bits) + 1;
   u64 need = per + 64;
   for (u64 r = 1; r * r < per * 64; r++) need = per + 64 + r;
-  u32 ngroups = (u32)env_num("HJ_XCHG_JOIN_GROUPS", x->G >= 4 ? 2 : 1);
+  // measured at N=2 (profiles/r02_n2_xchg_order_groups.jsonl): 1 group 13.6 ms (2.2 ms waiting for the last chunks
+  // before the one join), 2 groups 12.8 ms (0.1-0.8 ms waiting; the second build of the R tables costs 0.75 ms)
+  u32 ngroups = (u32)env_num("HJ_XCHG_JOIN_GROUPS", 2);
   if (ngroups < 1) ngroups = 1;
   if (ngroups > C) ngroups = C;
   const u32 gsize = (C + ngroups - 1) / ngroups;

@@ -215,9 +215,16 @@ constexpr int kScParentCache = 256;  // parents whose offset/tile tables are cac
 
 // MODE: compile-time digit function (0 = one radix pass on bits [shift, shift+bits),
 // which must lie below bit 32; 2 = generic digit_of, used for the G-way range split).
+// 3 = exchange digit for 32-bit keys, a power-of-two number of ranks and a key domain of 2^domain_bits:
+//     (min(G-1, (key-1) >> shift) << b1) | (key & (2^b1 - 1)) with shift = domain_bits - log2 G (host) -- digit_of's
+//     mode 3 without the 64-bit multiply (the local scatter of the pipelined exchange).
 template <int MODE>
 __device__ __forceinline__ u32 sc_digit(const Digit& dg, u32 fmask, u64 v) {
   if (MODE == 0) return (u32)(v >> dg.shift) & fmask;
+  if (MODE == 3) {
+    const u32 k = (u32)v;
+    return (min((k - 1u) >> dg.shift, dg.ndest - 1u) << dg.b1) | (k & ((1u << dg.b1) - 1u));
+  }
   return digit_of(dg, v);
 }
 
