@@ -2344,8 +2344,12 @@ int xchg_scatter_stage(hj_handle* h, Xchg* x, u32 t, const u64* in) {
   // own block: written in place by the scatter; its fill levels go next to the others'
   CK(cudaMemcpyAsync(x->window + st.fill_off + (u64)x->rank * F1, x->cur + (u64)t * gf + (u64)x->rank * F1,
                      F1 * sizeof(u64), cudaMemcpyDeviceToDevice, h->stream));
-  for (u32 p = 0; p < G; p++) {
-    if (p == x->rank) continue;
+  // Peers in ring order, rank+1 first: the copy engines take the streams' copies roughly in the order they were
+  // enqueued, and if every rank started with peer 0 all of them would write into ONE GPU at a time (N=8, peers in
+  // index order: 175 GB/s per GPU, 35 ms of a 48 ms step spent waiting; profiles/r02_bench_n8_xchg_v1*.json).
+  const bool ring = env_num("HJ_XCHG_RING", 1) != 0;
+  for (u32 k = 1; k < G; k++) {
+    const u32 p = ring ? (x->rank + k) % G : (k <= x->rank ? k - 1 : k);
     cudaStream_t cs = x->cs[p];
     u64* pw = x->peer_window[p];
     CK(cudaStreamWaitEvent(cs, st.scattered, 0));
