@@ -2120,6 +2120,12 @@ struct Xchg {
   u64 C2R = 0, C2S = 0, nR = 0, mS = 0;
   u64 s_out_stride = 0;  // pass-2 output of S chunk c: rb[1].out + c * s_out_stride, fill levels rb[1].cursors + c * 2^bits
   cudaEvent_t ev_begin, ev_end;
+  // HJ_XCHG_TRACE=1: a timeline of the step (copies per stage and peer, compute-stream phases) on stderr
+  bool one_stream = true, peer_copy = false;
+  cudaStream_t cs_all = nullptr;
+  int peer_dev[kScMaxPeers];
+  bool trace = false;
+  cudaEvent_t cev[kXMaxStages][kScMaxPeers][2];
 };
 
 // CUDA loads kernels lazily, at their first launch, and that load synchronises with running kernels: a step
@@ -2154,8 +2160,9 @@ static u64 xchg_region_cap(u64 n_stage, u32 G, u32 F1) {
 void xchg_free(hj_handle* h) {
   Xchg* x = h->xc;
   if (!x) return;
+  if (x->cs_all) { cudaStreamSynchronize(x->cs_all); cudaStreamDestroy(x->cs_all); }
   for (u32 p = 0; p < x->G; p++) {
-    if (x->cs[p]) { cudaStreamSynchronize(x->cs[p]); cudaStreamDestroy(x->cs[p]); }
+    if (x->cs[p] && x->cs[p] != x->cs_all) { cudaStreamSynchronize(x->cs[p]); cudaStreamDestroy(x->cs[p]); }
     for (u32 k = 0; k < 4; k++) {
       if (x->sub[p][k]) { cudaStreamSynchronize(x->sub[p][k]); cudaStreamDestroy(x->sub[p][k]); }
       if (x->sub_done[p][k]) cudaEventDestroy(x->sub_done[p][k]);
@@ -2166,6 +2173,9 @@ void xchg_free(hj_handle* h) {
     if (x->st[t].scattered) cudaEventDestroy(x->st[t].scattered);
     for (cudaEvent_t e : x->st[t].ev)
       if (e) cudaEventDestroy(e);
+    for (u32 p = 0; p < x->G; p++)
+      for (cudaEvent_t e : x->cev[t][p])
+        if (e) cudaEventDestroy(e);
   }
   void* bufs[] = {x->window, x->cur, x->caps_dev, x->epoch_word, x->ones, x->dest_ptrs};
   for (void* b : bufs)
@@ -2203,6 +2213,8 @@ int hj_xchg_create(hj_handle* h, uint32_t n_ranks, uint32_t rank, uint64_t n_loc
   memset(x->cs, 0, sizeof(x->cs));
   memset(x->sub, 0, sizeof(x->sub));
   memset(x->sub_done, 0, sizeof(x->sub_done));
+  memset(x->cev, 0, sizeof(x->cev));
+  x->trace = env_num("HJ_XCHG_TRACE", 0) != 0;
   x->ev_begin = x->ev_end = nullptr;
   h->xc = x;
   x->G = n_ranks; x->rank = rank; x->pl = ch.pl; x->b1 = ch.pl.b1; x->F1 = 1u << ch.pl.b1;
@@ -2262,9 +2274,22 @@ int hj_xchg_create(hj_handle* h, uint32_t n_ranks, uint32_t rank, uint64_t n_loc
     // one copy saturates what the concurrently running scatter / pass-2 kernels leave of HBM; default 1
     x->nsub = want > 0 ? (u32)(want > 4 ? 4 : want) : 1u;
   }
+  if (x->trace)
+    for (u32 t = 0; t < x->nstages; t++)
+      for (u32 p = 0; p < G; p++)
+        for (cudaEvent_t& e : x->cev[t][p]) XCK(cudaEventCreate(&e));
+  // One copy stream for all peers (default): the copy engines serve ONE of a GPU's streams until it has nothing
+  // ready and only then the next (HJ_XCHG_TRACE at N=4, per-peer streams: the first S chunk was complete after
+  // 11.8 ms although it was scattered after 1.6 ms, because the stream of peer r+1 shipped ITS blocks of every stage
+  // first); a single stream keeps the copies in stage order, ring order inside a stage.  HJ_XCHG_PEER_STREAMS=1: one
+  // stream per peer.
+  x->one_stream = env_num("HJ_XCHG_PEER_STREAMS", 0) == 0;
+  if (x->one_stream) XCK(cudaStreamCreateWithFlags(&x->cs_all, cudaStreamNonBlocking));
+  x->peer_copy = env_num("HJ_XCHG_PEERCOPY", 0) != 0;
   for (u32 p = 0; p < G; p++) {
     if (p == rank) continue;
-    XCK(cudaStreamCreateWithFlags(&x->cs[p], cudaStreamNonBlocking));
+    if (x->one_stream) x->cs[p] = x->cs_all;
+    else XCK(cudaStreamCreateWithFlags(&x->cs[p], cudaStreamNonBlocking));
     for (u32 k = 1; k < x->nsub; k++) {  // slice 0 travels on cs[p] itself
       XCK(cudaStreamCreateWithFlags(&x->sub[p][k], cudaStreamNonBlocking));
       XCK(cudaEventCreateWithFlags(&x->sub_done[p][k], cudaEventDisableTiming));
@@ -2297,6 +2322,9 @@ int hj_xchg_connect(hj_handle* h, void* const* peer_windows) {
   for (u32 p = 0; p < x->G; p++) {
     x->peer_window[p] = p == x->rank ? x->window : (u64*)peer_windows[p];
     if (!x->peer_window[p] || ((uintptr_t)x->peer_window[p] & 15)) return HJ_EINVAL;
+    cudaPointerAttributes pa;
+    x->peer_dev[p] = cudaPointerGetAttributes(&pa, x->peer_window[p]) == cudaSuccess ? pa.device : -1;
+    cudaGetLastError();
   }
   for (u32 t = 0; t < x->nstages; t++)
     for (u32 d = 0; d < x->G; d++)  // the own block is written in place, the others into the send buffer
@@ -2353,6 +2381,7 @@ int xchg_scatter_stage(hj_handle* h, Xchg* x, u32 t, const u64* in) {
     cudaStream_t cs = x->cs[p];
     u64* pw = x->peer_window[p];
     CK(cudaStreamWaitEvent(cs, st.scattered, 0));
+    if (x->trace) cudaEventRecord(x->cev[t][p][0], cs);
     {
       u64* const dst = pw + st.recv_off + (u64)x->rank * st.stride;
       const u64* const src = st.send + (u64)p * st.stride;
@@ -2365,13 +2394,17 @@ int xchg_scatter_stage(hj_handle* h, Xchg* x, u32 t, const u64* in) {
         CK(cudaMemcpyAsync(dst + b, src + b, (e - b) * sizeof(u64), cudaMemcpyDeviceToDevice, x->sub[p][k]));
         CK(cudaEventRecord(x->sub_done[p][k], x->sub[p][k]));
       }
-      CK(cudaMemcpyAsync(dst, src, (per < total ? per : total) * sizeof(u64), cudaMemcpyDeviceToDevice, cs));
+      if (x->peer_copy && x->peer_dev[p] >= 0 && x->peer_dev[p] != h->device)
+        CK(cudaMemcpyPeerAsync(dst, x->peer_dev[p], src, h->device, (per < total ? per : total) * sizeof(u64), cs));
+      else
+        CK(cudaMemcpyAsync(dst, src, (per < total ? per : total) * sizeof(u64), cudaMemcpyDeviceToDevice, cs));
       for (u32 k = 1; k < x->nsub; k++)
         if ((u64)k * per < total) CK(cudaStreamWaitEvent(cs, x->sub_done[p][k], 0));
     }
     CK(cudaMemcpyAsync(pw + st.fill_off + (u64)x->rank * F1, x->cur + (u64)t * gf + (u64)p * F1, F1 * sizeof(u64),
                        cudaMemcpyDeviceToDevice, cs));
     CK(cudaMemcpyAsync(pw + st.flag_off + x->rank, x->epoch_word, sizeof(u64), cudaMemcpyDeviceToDevice, cs));
+    if (x->trace) cudaEventRecord(x->cev[t][p][1], cs);
   }
   return HJ_OK;
 }
@@ -2516,6 +2549,23 @@ int hj_xchg_finish(hj_handle* h, hj_result* res) {
     res->radix_bits = x->pl.bits;
     res->passes = 2;
     res->hbm_bytes = 40ull * (x->nR + x->mS * (x->nstages - 1));  // 8*(2P+1) per tuple, P = 2
+  }
+  if (x->trace) {
+    auto at = [&](cudaEvent_t e) { float ms = 0.f; return cudaEventElapsedTime(&ms, x->ev_begin, e) == cudaSuccess ? ms : -1.f; };
+    for (u32 t = 0; t < x->nstages; t++) {
+      const XStage& st = x->st[t];
+      char line[1024];
+      int n = snprintf(line, sizeof(line), "[xchg r%u e%llu] stage %u: scatter %.2f-%.2f wait %.2f-%.2f pass2 %.2f-%.2f join-end %.2f | copies",
+                       x->rank, (unsigned long long)x->epoch, t, at(st.ev[0]), at(st.ev[1]), at(st.ev[2]), at(st.ev[3]),
+                       at(st.ev[4]), at(st.ev[5]), t && st.ev_joined ? at(st.ev[6]) : -1.f);
+      for (u32 k = 1; k < x->G && n < 900; k++) {
+        const u32 p = (x->rank + k) % x->G;
+        n += snprintf(line + n, sizeof(line) - n, " ->%u(d%d) %.2f-%.2f", p, x->peer_dev[p], at(x->cev[t][p][0]), at(x->cev[t][p][1]));
+      }
+      snprintf(line + n, sizeof(line) - n, "\n");
+      fputs(line, stderr);
+    }
+    fprintf(stderr, "[xchg r%u] end %.2f\n", x->rank, at(x->ev_end));
   }
   if (h->h_ctr[C_XCHG_TIMEOUT]) {
     snprintf(h->err, sizeof(h->err), "hj_xchg: a peer's stage did not arrive within 10 s (epoch %llu)", x->epoch);
