@@ -329,6 +329,21 @@ class HashJoin:
         self._check(lib.hj_sync(self._h), "hj_sync")
 
 
+NOALLOC_MAX_R = 1 << 16  # HJ_NOALLOC_MAX_R (include/hj_b200.h)
+
+
+def join_noalloc(d_R, n, d_S, m, d_out, probe_length=4, device=0, stream=0):
+    """hj_join_noalloc: the global-table join on the library's static device scratch -- no handle, no allocation,
+    no host synchronisation.  d_R, d_S, d_out: raw device pointers; d_out receives {matches, checksum} once
+    `stream` (a cudaStream_t value, 0 = default stream) reaches that point.  Raises HJError (HJ_EINVAL) when
+    n > NOALLOC_MAX_R."""
+    err = C.create_string_buffer(256)
+    rc = lib.hj_join_noalloc(int(device), int(stream) or None, int(d_R), int(n), int(d_S) if d_S else None, int(m),
+                             int(probe_length), int(d_out), err, 256)
+    if rc != HJ_OK:
+        raise HJError(rc, "hj_join_noalloc", err.value.decode())
+
+
 def pinned_empty(n):
     """uint64 numpy array over pinned host memory (hj_host_alloc)."""
     p = C.c_void_p()

@@ -24,7 +24,7 @@ ABI_SYMBOLS = [
     "hj_radix_plan", "hj_ipc_export", "hj_ipc_open", "hj_ipc_close", "hj_peer_hist", "hj_peer_scatter",
     "hj_join_pass1", "hj_join_materialize", "hj_peer_scatter_async",
     "hj_peer_scatter_regions", "hj_join_regions", "hj_reserve_staging", "hj_alloc_count",
-    "hj_xchg_create", "hj_xchg_connect", "hj_xchg_start", "hj_xchg_finish",
+    "hj_xchg_create", "hj_xchg_connect", "hj_xchg_start", "hj_xchg_finish", "hj_join_noalloc",
 ]
 # host-side mirror of the reference interface (csrc/ref_entry.hpp, csrc/datagen.hpp)
 HOST_SYMBOLS = ["hj_ref_pro", "hj_ref_run", "hj_ref_set_radix", "hj_ref_set_device", "hj_ref_last_status",
@@ -116,6 +116,8 @@ def load():
         "hj_xchg_connect": (C.c_int, [H, C.POINTER(C.c_uint64)]),
         "hj_xchg_start": (C.c_int, [H, u64p, u64p, C.c_uint64]),
         "hj_xchg_finish": (C.c_int, [H, C.POINTER(hj_result)]),
+        "hj_join_noalloc": (C.c_int, [C.c_int, vp, u64p, C.c_uint64, u64p, C.c_uint64, C.c_uint32, u64p, C.c_char_p,
+                                      C.c_uint32]),
         "hj_generate": (C.c_int, [H, C.c_int, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, u64p]),
         "hj_device_alloc": (C.c_int, [H, C.c_uint64, C.POINTER(vp)]),
         "hj_device_free": (C.c_int, [H, vp]),

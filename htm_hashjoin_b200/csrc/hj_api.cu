@@ -9,10 +9,12 @@
 // There is deliberately no CPU path in this file: without a device every entry
 // point fails with HJ_ECUDA.
 #include <cuda_runtime.h>
+#include <stdarg.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
+#include <mutex>
 #include <new>
 
 #include "../../include/hj_b200.h"
@@ -2580,3 +2582,130 @@ int hj_xchg_finish(hj_handle* h, hj_result* res) {
 }
 
 }  // extern "C"
+
+// ===========================================================================
+// hj_join_noalloc: the global-table join with every byte of scratch in a static device array
+// ===========================================================================
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (CUDA-graph capture, tight serving loops, harnesses that forbid it).  The global-table kernels of
+// gt_kernels.cuh -- build, overflow insert, probe -- run here on a table, claim bitmap, overflow table / list /
+// map and counters carved out of ONE file-scope __device__ array instead of the handle's cudaMalloc'ed buffers.
+// The array costs kNaWords * 8 bytes (2.53 MiB) on every GPU that loads the library, until the process exits.
+// The name g_na_scratch is a host-side stand-in in host code, not a device address: the address the kernels get
+// comes from cudaGetSymbolAddress, once per device, with that device current.
+// Every call shares the array and finds the last call's contents in it: the counters, the table and the claim
+// bitmap are cleared at the start of each call (the overflow table and map by gt_ovf_clear_kernel when something
+// overflowed).  Calls that overlap on one GPU (two streams, two threads) race on it.
+namespace {
+
+constexpr u64 kNaMaxR = HJ_NOALLOC_MAX_R;      // tuples of R
+constexpr u64 kNaSlotsMax = 2 * kNaMaxR;       // scaleOutput 2 (the reference's default, main.cpp:80)
+constexpr u64 kNaCtrOff = 0;                   // C_COUNT counters, padded to 32 words (256 bytes)
+constexpr u64 kNaTableOff = 32;
+constexpr u64 kNaOvfTableOff = kNaTableOff + kNaSlotsMax;
+constexpr u64 kNaOvfListOff = kNaOvfTableOff + kNaSlotsMax;
+constexpr u64 kNaClaimOff = kNaOvfListOff + kNaMaxR;
+constexpr u64 kNaOvfMapOff = kNaClaimOff + kNaSlotsMax / 64;
+constexpr u64 kNaWords = kNaOvfMapOff + kNaSlotsMax / 64;
+static_assert(C_COUNT <= 32, "counter block of the no-alloc scratch");
+static_assert(C_CHECKSUM == C_MATCHES + 1, "hj_join_noalloc copies {matches, checksum} as one 16-byte block");
+
+static __device__ __align__(256) unsigned long long g_na_scratch[kNaWords];
+
+constexpr int kNaMaxDevices = 64;
+struct NaDevice {
+  u64* base = nullptr;  // device address of g_na_scratch on this device
+  int sm_count = 0;
+};
+NaDevice g_na_dev[kNaMaxDevices];
+std::mutex g_na_mutex;
+
+int na_fail(char* err, uint32_t cap, int code, const char* fmt, ...) {
+  if (err && cap) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(err, cap, fmt, ap);
+    va_end(ap);
+  }
+  return code;
+}
+
+}  // namespace
+
+extern "C" int hj_join_noalloc(int device, void* stream, const uint64_t* R, uint64_t n, const uint64_t* S, uint64_t m,
+                               uint32_t probe_length, uint64_t* out, char* err, uint32_t err_cap) {
+  if (err && err_cap) err[0] = 0;
+  if (device < 0 || device >= kNaMaxDevices) return na_fail(err, err_cap, HJ_EINVAL, "hj_join_noalloc: device %d out of range", device);
+  if (!R || !n || !out || (m && !S)) return na_fail(err, err_cap, HJ_EINVAL, "hj_join_noalloc: null input or output, or |R| = 0");
+  if (n > kNaMaxR)
+    return na_fail(err, err_cap, HJ_EINVAL,
+                   "hj_join_noalloc: |R| = %llu exceeds HJ_NOALLOC_MAX_R = %llu (the static scratch holds a table of %llu "
+                   "slots); use hj_join on a handle for larger builds",
+                   (unsigned long long)n, (unsigned long long)kNaMaxR, (unsigned long long)kNaSlotsMax);
+  if (probe_length == 0) probe_length = 4;  // main.cpp:81
+#define NCK(call)                                                                                          \
+  do {                                                                                                     \
+    cudaError_t e_ = (call);                                                                               \
+    if (e_ != cudaSuccess)                                                                                 \
+      return na_fail(err, err_cap, HJ_ECUDA, "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
+  } while (0)
+  NCK(cudaSetDevice(device));
+  if (!is_device_ptr(R) || (m && !is_device_ptr(S)) || !is_device_ptr(out))
+    return na_fail(err, err_cap, HJ_EINVAL, "hj_join_noalloc: R, S and out must be device pointers");
+  NaDevice nd;
+  {
+    std::lock_guard<std::mutex> lock(g_na_mutex);
+    NaDevice& d = g_na_dev[device];
+    if (!d.base) {  // set-up, once per device, with that device current
+      void* p = nullptr;
+      NCK(cudaGetSymbolAddress(&p, g_na_scratch));
+      int sms = 0;
+      NCK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+      d.sm_count = sms > 0 ? sms : 148;
+      d.base = static_cast<u64*>(p);
+    }
+    nd = d;
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  u64* const ctr = nd.base + kNaCtrOff;
+  u64* const table = nd.base + kNaTableOff;
+  u64* const ovf_table = nd.base + kNaOvfTableOff;
+  u64* const ovf_list = nd.base + kNaOvfListOff;
+  u32* const claim = reinterpret_cast<u32*>(nd.base + kNaClaimOff);
+  u32* const ovfmap = reinterpret_cast<u32*>(nd.base + kNaOvfMapOff);
+  const u64 slots = pow2_ceil_u64(n * 2 < 128 ? 128 : n * 2);  // prepare_table's geometry at scaleOutput 2
+  const u64 mask = slots - 1, key_mask = ~0ull;                 // hj_config_default: all 64 bits are the key
+  // what must start at zero: counters, table, claim bitmap
+  NCK(cudaMemsetAsync(ctr, 0, 32 * sizeof(u64), st));
+  NCK(cudaMemsetAsync(table, 0, slots * sizeof(u64), st));
+  NCK(cudaMemsetAsync(claim, 0, slots / 8, st));
+  {
+    constexpr int IPT = 2;
+    const u64 chunks = (n + kGtThreads * IPT - 1) / (kGtThreads * IPT);
+    u64 grid = (u64)nd.sm_count * 4;
+    if (grid > chunks) grid = chunks;
+    gt_build_kernel<IPT, false><<<(int)grid, kGtThreads, 0, st>>>(reinterpret_cast<const u64*>(R), whole(n), table, claim, (u32)mask,
+                                                                  (u32)(key_mask & mask), probe_length, ovf_list, ctr);
+  }
+  gt_ovf_clear_kernel<<<nd.sm_count * 2, 256, 0, st>>>(ovf_table, ovfmap, slots / 32, ctr, slots);
+  gt_ovf_insert_kernel<<<nd.sm_count * 2, 256, 0, st>>>(ovf_list, ovf_table, ovfmap, ctr, mask, key_mask, slots);
+  if (m) {
+    {
+      constexpr int HIPT = 8;
+      const u64 chunks = (m + kGtThreads * HIPT - 1) / (kGtThreads * HIPT);
+      u64 grid = (u64)nd.sm_count * 4;
+      if (grid > chunks) grid = chunks;
+      gt_probe_home_kernel<HIPT><<<(int)grid, kGtThreads, 0, st>>>(reinterpret_cast<const u64*>(S), m, table, mask, key_mask, ctr);
+    }
+    constexpr int IPT = 4;
+    const u64 chunks = (m + kGtThreads * IPT - 1) / (kGtThreads * IPT);
+    u64 grid = (u64)nd.sm_count * 3;
+    if (grid > chunks) grid = chunks;
+    gt_probe_kernel<IPT><<<(int)grid, kGtThreads, 0, st>>>(reinterpret_cast<const u64*>(S), m, table, mask, key_mask, probe_length,
+                                                           ovf_table, slots, ovfmap, ctr);
+  }
+  NCK(cudaGetLastError());
+  NCK(cudaMemcpyAsync(out, ctr + C_MATCHES, 2 * sizeof(u64), cudaMemcpyDeviceToDevice, st));
+#undef NCK
+  return HJ_OK;
+}

@@ -278,6 +278,27 @@ int hj_xchg_finish(hj_handle *h, hj_result *res);
 int hj_generate(hj_handle *h, int kind, uint64_t first, uint64_t count,
                 uint64_t domain, uint64_t seed, uint64_t *out);
 
+/* ---- a join that allocates nothing ---------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).
+ * The global-table join (the atomic build + probe of hj_join on an HJ_ALGO_ATOMIC handle with the default
+ * configuration: scaleOutput 2, all 64 bits of a tuple are the key) with its table, claim bitmap, overflow
+ * structures and counters in a static __device__ array of the library: 2.53 MiB that every GPU which loads the
+ * library holds until the process exits.  No cudaMalloc / cudaFree / allocating routine is called, no handle is
+ * needed, nothing synchronises with the host: the work is enqueued on `stream` (a cudaStream_t; NULL = the default
+ * stream) and out[0] = matches, out[1] = checksum are valid once the stream reaches that point.
+ *   R, S, out   device pointers (8-byte aligned); |R| = n in [1, HJ_NOALLOC_MAX_R], |S| = m (any size, 0 allowed)
+ *   probe_length   as --probeLength (0 = the default, 4)
+ *   err, err_cap   optional buffer for the message of a failure
+ * n > HJ_NOALLOC_MAX_R is rejected with HJ_EINVAL.  Every call on a GPU shares the one array and finds the last
+ * call's contents in it; each call clears what it needs at its start.  Calls that overlap on the same GPU (two
+ * streams, two threads) race on the array: serialise them.  The first call on a device looks the array's address
+ * up (cudaGetSymbolAddress) and is therefore not capturable; later calls only launch kernels, memsets and a
+ * 16-byte device-to-device copy. */
+#define HJ_NOALLOC_MAX_R (1u << 16)
+int hj_join_noalloc(int device, void *stream, const uint64_t *R, uint64_t n, const uint64_t *S, uint64_t m,
+                    uint32_t probe_length, uint64_t *out, char *err, uint32_t err_cap);
+
 /* ---- memory helpers so a C host needs no CUDA headers ------------------------ */
 int hj_device_alloc(hj_handle *h, uint64_t bytes, void **out);
 int hj_device_free(hj_handle *h, void *p);
