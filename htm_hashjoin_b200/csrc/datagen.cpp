@@ -97,7 +97,7 @@ extern "C" void hj_mc_relation_fk(uint64_t* out, uint64_t m, uint64_t maxid, uns
 
 // ---- mc's remaining generators: --non-unique, --full-range, --skew, --local-shuffle-range ------
 // Same libc calls in the same order as mc/src/generator.c / genzipf.c, so the arrays are the reference's arrays
-// (checked against the reference's own code in tests/test_oracle_cpu.py via oracle/_ref/mc_gen).
+// (checked against the reference's own code in tests/test_oracle_cpu.py via a binary built from the reference sources).
 
 #include <math.h>
 
