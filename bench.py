@@ -379,7 +379,9 @@ class Rank:
             self.n, self.m = self.n // G, self.m // G
         self.domain = G * self.n
         if args.chunks == 0:
-            args.chunks = 8 if (G > 1 and args.exchange == "xchg") else 1
+            # measured (profiles/r02_n2_xchg_order_groups.jsonl, r02_n4_pg_c*.json): N=2 8 chunks 12.8 ms vs 13.6 with 4;
+            # N=4 4 chunks 13.5 ms vs 13.9 with 8 (more, smaller copies: more per-copy gaps and token waits)
+            args.chunks = (8 if G == 2 else 4) if (G > 1 and args.exchange == "xchg") else 1
         self.xchg = G > 1 and args.exchange == "xchg"
         self.h = hj.HashJoin(args.algo, device=self.local, num_partitions=(1 << args.radix_bits) if args.radix_bits else 0,
                              passes=args.passes)
@@ -421,8 +423,34 @@ class Rank:
             dom_bits = self.exchange.domain_bits_for(self.domain)
             win, self.window_bytes = self.h.xchg_create(G, self.rank, self.n, self.m, self.chunks, dom_bits)
             handles = self.exchange.exchange_ipc_handles(self.h.ipc_export(win))
-            self.h.xchg_connect([win if g == self.rank else self.h.ipc_open(handles[g]) for g in range(G)])
+            peers = [win if g == self.rank else self.h.ipc_open(handles[g]) for g in range(G)]
+            self.h.xchg_connect(peers)
             self.epoch = 0
+            if os.environ.get("HJ_BENCH_COPYPROBE"):
+                # diagnostic: what the copy engines give THIS process (torch + NCCL initialised, the exchange's own
+                # window mapping) for plain ring-ordered block copies in lock step, no compute beside them
+                import torch.distributed as dist
+                blk = 512 << 20
+                fresh_src = self.h.device_alloc(G * blk)
+                fresh_win = self.h.device_alloc(G * blk)
+                hs2 = self.exchange.exchange_ipc_handles(self.h.ipc_export(fresh_win))
+                peers2 = [fresh_win if g == self.rank else self.h.ipc_open(hs2[g]) for g in range(G)]
+                variants = [("window<-dS", peers, self.dS.data_ptr()), ("window<-fresh", peers, fresh_src),
+                            ("fresh<-dS", peers2, self.dS.data_ptr()), ("fresh<-fresh", peers2, fresh_src)]
+                print(f"[copyprobe r{self.rank}] mod 2MiB: window {win % (2 << 20)} dS {self.dS.data_ptr() % (2 << 20)} "
+                      f"peer windows {[q % (2 << 20) for q in peers]} window_bytes {self.window_bytes}", file=sys.stderr, flush=True)
+                for name, pw, src in variants:
+                    torch.cuda.synchronize()
+                    dist.barrier()
+                    t0 = time.perf_counter()
+                    for _ in range(4):
+                        for k in range(1, G):
+                            p = (self.rank + k) % G
+                            self.h.copy(pw[p] + self.rank * blk, src + p * blk, blk)
+                    dt = time.perf_counter() - t0
+                    print(f"[copyprobe r{self.rank}] {name}: {4 * (G - 1) * blk / dt / 1e9:.1f} GB/s "
+                          f"({dt * 1e3 / (4 * (G - 1)):.3f} ms per 512 MiB block)", file=sys.stderr, flush=True)
+                    dist.barrier()
         elif self.fused:
             # exchange == radix pass 1: every rank stores straight into the owners' pass-1 buffers
             # (CUDA IPC over NVLink).  The fan-out is fixed so all ranks agree on b1.

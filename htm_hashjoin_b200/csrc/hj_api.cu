@@ -8,6 +8,7 @@
 //
 // There is deliberately no CPU path in this file: without a device every entry
 // point fails with HJ_ECUDA.
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdarg.h>
 #include <stdio.h>
@@ -125,13 +126,22 @@ namespace {
     }                                                                                              \
   } while (0)
 
+// cudaMalloc backs an allocation whose SIZE is not a multiple of 2 MiB with small pages throughout: a copy-engine
+// write into such a buffer over NVLink runs at 530 GB/s instead of 760 (tools/py_copy_probe.py,
+// profiles/r02_py_copy_probe.jsonl: a 9.78 GB window, 12 800 bytes past a 2 MiB multiple).  Every large allocation
+// is therefore rounded up to whole 2 MiB pages.
+inline u64 page_round_bytes(u64 bytes) {
+  constexpr u64 kPage = 2ull << 20;
+  return bytes >= kPage / 2 ? (bytes + kPage - 1) & ~(kPage - 1) : bytes;
+}
+
 int ensure(hj_handle* h, DevBuf& b, u64 elems) {
   if (b.cap >= elems) return HJ_OK;
   if (&b == &h->table) h->built = false;  // the old table goes away with its contents
   if (b.p) CK(cudaFree(b.p));
   b.p = nullptr;
   b.cap = 0;
-  CK(cudaMalloc(&b.p, elems * sizeof(u64)));
+  CK(cudaMalloc(&b.p, page_round_bytes(elems * sizeof(u64))));
   h->allocs++;
   b.cap = elems;
   return HJ_OK;
@@ -2024,7 +2034,7 @@ int hj_generate(hj_handle* h, int kind, uint64_t first, uint64_t count, uint64_t
 int hj_device_alloc(hj_handle* h, uint64_t bytes, void** out) {
   if (!h || !out) return HJ_EINVAL;
   CK(cudaSetDevice(h->device));
-  CK(cudaMalloc(out, bytes ? bytes : 8));
+  CK(cudaMalloc(out, bytes ? page_round_bytes(bytes) : 8));
   return HJ_OK;
 }
 int hj_device_free(hj_handle* h, void* p) {
@@ -2093,14 +2103,30 @@ int hj_sync(hj_handle* h) {
 //     counter read-back ever synchronises with the host.
 // Contract: all ranks call hj_xchg_start with the same, strictly increasing epoch, and nobody starts epoch
 // e+1 before every rank finished epoch e (the all-reduce of the result is that barrier).
+typedef CUresult (*StreamWaitValue64)(CUstream, CUdeviceptr, cuuint64_t, unsigned int);
+static StreamWaitValue64 stream_wait_value() {
+  static StreamWaitValue64 fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    if (cudaGetDriverEntryPoint("cuStreamWaitValue64", &p, cudaEnableDefault, &qr) != cudaSuccess ||
+        qr != cudaDriverEntryPointSuccess) {
+      cudaGetLastError();
+      p = nullptr;
+    }
+    return (StreamWaitValue64)p;
+  }();
+  return fn;
+}
+
 struct XStage {
-  u64 n_local, cap, stride, recv_off, fill_off, flag_off;
+  u64 n_local, cap, stride, recv_off, fill_off, flag_off, tok_off;
   u64* send;
   bool ev_joined;  // a join was launched right after this stage's pass 2 (ev[5] .. ev[6])
   cudaEvent_t scattered;
   cudaEvent_t ev[8];  // scatter0/1, wait0/1, pass2 0/1, join end, spare
 };
 constexpr u32 kXMaxStages = 17;
+constexpr u64 kXPage = (2ull << 20) / sizeof(u64);  // 2 MiB in tuples
 constexpr u64 kXScratch = (u64)kScThreads * 32 + 2;  // diverted claims of one scatter tile (+ alignment)
 struct Xchg {
   u32 G = 0, rank = 0, b1 = 0, F1 = 0, nstages = 0, domain_bits = 0;
@@ -2124,6 +2150,13 @@ struct Xchg {
   cudaEvent_t ev_begin, ev_end;
   // HJ_XCHG_TRACE=1: a timeline of the step (copies per stage and peer, compute-stream phases) on stderr
   bool one_stream = true, peer_copy = false;
+  // Ring kept in lock step (one_stream && G > 2): before this rank's copy stream ships round k+1 of a stage (target
+  // rank+k+1) it waits -- cuStreamWaitValue64, no SM involved -- for a token from its successor rank+1, the previous
+  // sender to that target, saying that its round k is done.  Without it the ranks drift apart, two of them write into
+  // one GPU while another receives nothing, and a block takes 1.0-1.15 ms instead of 0.75 (tools/ce_probe_ipc.cu:
+  // 715 GB/s in step, 475-550 GB/s with the ranks 0.4 ms apart, 600-620 GB/s with tokens, the skew included).
+  bool tokens = false;
+  u64 tok_first = 0, tok_words = 0;  // the token area of the window
   cudaStream_t cs_all = nullptr;
   int peer_dev[kScMaxPeers];
   bool trace = false;
@@ -2162,6 +2195,9 @@ static u64 xchg_region_cap(u64 n_stage, u32 G, u32 F1) {
 void xchg_free(hj_handle* h) {
   Xchg* x = h->xc;
   if (!x) return;
+  if (x->tokens && x->window) {  // release token waits still pending (a step that was started and never finished)
+    cudaMemset(x->window + x->tok_first, 0xFF, x->tok_words * sizeof(u64));
+  }
   if (x->cs_all) { cudaStreamSynchronize(x->cs_all); cudaStreamDestroy(x->cs_all); }
   for (u32 p = 0; p < x->G; p++) {
     if (x->cs[p] && x->cs[p] != x->cs_all) { cudaStreamSynchronize(x->cs[p]); cudaStreamDestroy(x->cs[p]); }
@@ -2232,22 +2268,28 @@ int hj_xchg_create(hj_handle* h, uint32_t n_ranks, uint32_t rank, uint64_t n_loc
     XStage& st = x->st[t];
     st.n_local = t == 0 ? n_local : x->mS;
     st.cap = xchg_region_cap(st.n_local, G, F1);
-    st.stride = ((u64)F1 * st.cap + kXScratch + 31) & ~31ull;
+    // Blocks start on 2 MiB boundaries on both sides and travel as whole 2 MiB pages: the copy engines move a block
+    // that is only 256-byte aligned at 475-540 GB/s, a page-aligned one at 720-740 GB/s (tools/ce_probe_ipc.cu with
+    // PROBE_BLOCK_BYTES, profiles/r02_ce_probe_ipc_align.jsonl)
+    st.stride = ((u64)F1 * st.cap + kXScratch + kXPage - 1) & ~(kXPage - 1);
     st.recv_off = off;
     off += (u64)G * st.stride;
   }
   for (u32 t = 0; t < x->nstages; t++) { x->st[t].fill_off = off; off += (gf + 31) & ~31u; }
   for (u32 t = 0; t < x->nstages; t++) { x->st[t].flag_off = off; off += 32; }
+  x->tok_first = off;
+  for (u32 t = 0; t < x->nstages; t++) { x->st[t].tok_off = off; off += 32; }
+  x->tok_words = off - x->tok_first;
   x->window_elems = off;
   auto fail = [&](int code) { xchg_free(h); return code; };
 #define XCK(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { \
     snprintf(h->err, sizeof(h->err), "%s:%d %s: %s", __FILE__, __LINE__, #call, cudaGetErrorString(e_)); \
     return fail(e_ == cudaErrorMemoryAllocation ? HJ_ENOMEM : HJ_ECUDA); } } while (0)
-  XCK(cudaMalloc(&x->window, off * sizeof(u64)));
+  XCK(cudaMalloc(&x->window, page_round_bytes(off * sizeof(u64))));
   h->allocs++;
   XCK(cudaMemset(x->window + x->st[0].fill_off, 0, (off - x->st[0].fill_off) * sizeof(u64)));  // fills + flags
   for (u32 t = 0; t < x->nstages; t++) {
-    XCK(cudaMalloc(&x->st[t].send, (u64)G * x->st[t].stride * sizeof(u64)));
+    XCK(cudaMalloc(&x->st[t].send, page_round_bytes((u64)G * x->st[t].stride * sizeof(u64))));
     h->allocs++;
     XCK(cudaEventCreateWithFlags(&x->st[t].scattered, cudaEventDisableTiming));
     for (cudaEvent_t& e : x->st[t].ev) XCK(cudaEventCreate(&e));
@@ -2288,6 +2330,8 @@ int hj_xchg_create(hj_handle* h, uint32_t n_ranks, uint32_t rank, uint64_t n_loc
   x->one_stream = env_num("HJ_XCHG_PEER_STREAMS", 0) == 0;
   if (x->one_stream) XCK(cudaStreamCreateWithFlags(&x->cs_all, cudaStreamNonBlocking));
   x->peer_copy = env_num("HJ_XCHG_PEERCOPY", 0) != 0;
+  x->tokens = x->one_stream && G > 2 && env_num("HJ_XCHG_RING", 1) != 0 && env_num("HJ_XCHG_TOKENS", 1) != 0 &&
+              stream_wait_value() != nullptr;
   for (u32 p = 0; p < G; p++) {
     if (p == rank) continue;
     if (x->one_stream) x->cs[p] = x->cs_all;
@@ -2383,11 +2427,19 @@ int xchg_scatter_stage(hj_handle* h, Xchg* x, u32 t, const u64* in) {
     cudaStream_t cs = x->cs[p];
     u64* pw = x->peer_window[p];
     CK(cudaStreamWaitEvent(cs, st.scattered, 0));
+    if (x->tokens && k >= 2) {  // the successor's round k-1 went to the same target: let it finish first
+      const CUresult cr = stream_wait_value()((CUstream)cs, (CUdeviceptr)(x->window + st.tok_off + (k - 1)), x->epoch,
+                                              CU_STREAM_WAIT_VALUE_GEQ);
+      if (cr != CUDA_SUCCESS) {
+        snprintf(h->err, sizeof(h->err), "hj_xchg: cuStreamWaitValue64 failed (%d)", (int)cr);
+        return HJ_ECUDA;
+      }
+    }
     if (x->trace) cudaEventRecord(x->cev[t][p][0], cs);
     {
       u64* const dst = pw + st.recv_off + (u64)x->rank * st.stride;
       const u64* const src = st.send + (u64)p * st.stride;
-      const u64 total = (u64)F1 * st.cap;
+      const u64 total = ((u64)F1 * st.cap + kXPage - 1) & ~(kXPage - 1);  // whole pages (<= stride: the tail is scratch)
       const u64 per = ((total + x->nsub - 1) / x->nsub + 31) & ~31ull;  // 256-byte aligned slices
       for (u32 k = 1; k < x->nsub; k++) {
         const u64 b = (u64)k * per, e = b + per < total ? b + per : total;
@@ -2403,6 +2455,9 @@ int xchg_scatter_stage(hj_handle* h, Xchg* x, u32 t, const u64* in) {
       for (u32 k = 1; k < x->nsub; k++)
         if ((u64)k * per < total) CK(cudaStreamWaitEvent(cs, x->sub_done[p][k], 0));
     }
+    if (x->tokens && k + 2 <= G)  // round k done: the predecessor's round k+1 has the target to itself
+      CK(cudaMemcpyAsync(x->peer_window[(x->rank + G - 1) % G] + st.tok_off + k, x->epoch_word, sizeof(u64),
+                         cudaMemcpyDeviceToDevice, cs));
     CK(cudaMemcpyAsync(pw + st.fill_off + (u64)x->rank * F1, x->cur + (u64)t * gf + (u64)p * F1, F1 * sizeof(u64),
                        cudaMemcpyDeviceToDevice, cs));
     CK(cudaMemcpyAsync(pw + st.flag_off + x->rank, x->epoch_word, sizeof(u64), cudaMemcpyDeviceToDevice, cs));
@@ -2534,6 +2589,10 @@ int hj_xchg_finish(hj_handle* h, hj_result* res) {
   x->started = false;
   int rc;
   if ((rc = fetch_counters(h))) return rc;  // waits for the compute stream
+  if (h->h_ctr[C_XCHG_TIMEOUT] && x->tokens) {  // a peer is gone: nothing may keep this rank's copy stream waiting
+    CK(cudaMemsetAsync(x->window + x->tok_first, 0xFF, x->tok_words * sizeof(u64), h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+  }
   for (u32 p = 0; p < x->G; p++)
     if (x->cs[p]) CK(cudaStreamSynchronize(x->cs[p]));  // (waits for the slices' streams too) the send buffers are free again
   if (res) {
