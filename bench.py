@@ -379,9 +379,9 @@ class Rank:
             self.n, self.m = self.n // G, self.m // G
         self.domain = G * self.n
         if args.chunks == 0:
-            # measured (profiles/r02_n2_xchg_order_groups.jsonl, r02_n4_pg_c*.json): N=2 8 chunks 12.8 ms vs 13.6 with 4;
-            # N=4 4 chunks 13.5 ms vs 13.9 with 8 (more, smaller copies: more per-copy gaps and token waits)
-            args.chunks = (8 if G == 2 else 4) if (G > 1 and args.exchange == "xchg") else 1
+            # measured with the page-aligned window (profiles/r02_n2_pg_c*.json, r02_n4_pg_c*.json): N=2 4 chunks
+            # 12.0 ms vs 12.7 with 8; N=4 13.5 vs 13.9 (more, smaller copies: more per-copy gaps and token waits)
+            args.chunks = 4 if (G > 1 and args.exchange == "xchg") else 1
         self.xchg = G > 1 and args.exchange == "xchg"
         self.h = hj.HashJoin(args.algo, device=self.local, num_partitions=(1 << args.radix_bits) if args.radix_bits else 0,
                              passes=args.passes)
@@ -747,7 +747,11 @@ class Rank:
 
 # ncu --set full, profiles/r02_ncu_global_*: DRAM bytes per tuple of the two kernels (read + write) -- filled from the
 # committed captures; None = not captured for that input
-GT_TRAFFIC = {}
+GT_TRAFFIC = {
+    # profiles/r02_ncu_global_n27_raw.csv, sorted 2^27: gt_build_kernel 1.091 GB read + 1.035 GB written (0.670 ms under
+    # ncu), gt_probe_home_kernel 2.148 GB read + 0.004 GB written (0.306 ms = 7.0 TB/s): no re-reads on either side
+    "c2_atomic_sorted_2^27": 4277000000,
+}
 
 
 def global_table_lines(rk, reps=5, warm=2):

@@ -2551,7 +2551,10 @@ int hj_xchg_start(hj_handle* h, const uint64_t* R, const uint64_t* S, uint64_t e
   for (u64 r = 1; r * r < per * 64; r++) need = per + 64 + r;
   // measured at N=2 (profiles/r02_n2_xchg_order_groups.jsonl): 1 group 13.6 ms (2.2 ms waiting for the last chunks
   // before the one join), 2 groups 12.8 ms (0.1-0.8 ms waiting; the second build of the R tables costs 0.75 ms)
-  u32 ngroups = (u32)env_num("HJ_XCHG_JOIN_GROUPS", 2);
+  // With the page-aligned window (copies at 740 GB/s) N=2 never waits for the link: one join, every R table built
+  // once (profiles/r02_n2_pg_*.json: 4 chunks, 1 group 11.5 ms, 2 groups 12.0 ms).  From N=4 on the last chunks
+  // arrive late enough that joining the first half meanwhile pays.
+  u32 ngroups = (u32)env_num("HJ_XCHG_JOIN_GROUPS", x->G <= 2 ? 1 : 2);
   if (ngroups < 1) ngroups = 1;
   if (ngroups > C) ngroups = C;
   const u32 gsize = (C + ngroups - 1) / ngroups;
