@@ -2554,7 +2554,10 @@ int hj_xchg_start(hj_handle* h, const uint64_t* R, const uint64_t* S, uint64_t e
   // With the page-aligned window (copies at 740 GB/s) N=2 never waits for the link: one join, every R table built
   // once (profiles/r02_n2_pg_*.json: 4 chunks, 1 group 11.5 ms, 2 groups 12.0 ms).  From N=4 on the last chunks
   // arrive late enough that joining the first half meanwhile pays.
-  u32 ngroups = (u32)env_num("HJ_XCHG_JOIN_GROUPS", x->G <= 2 ? 1 : 2);
+  // At N=8 the link is the longer pole (7/8 of the tuples leave): every chunk is joined as it arrives, the extra
+  // builds of the R tables run while the next chunk travels and only one chunk's join is left after the last copy
+  // (profiles/r02_n8_pg_c4*.json: 4 groups 15.0 ms, 2 groups 16.1 ms; at N=4 the same trade loses, r02_n4_pg_c8_g4).
+  u32 ngroups = (u32)env_num("HJ_XCHG_JOIN_GROUPS", x->G <= 2 ? 1 : x->G <= 4 ? 2 : (long long)C);
   if (ngroups < 1) ngroups = 1;
   if (ngroups > C) ngroups = C;
   const u32 gsize = (C + ngroups - 1) / ngroups;
