@@ -10,6 +10,7 @@
 // point fails with HJ_ECUDA.
 #include <cuda.h>
 #include <cuda_runtime.h>
+#include <math.h>
 #include <stdarg.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -389,17 +390,21 @@ double contention_of(hj_handle* h) {
   return locality + retry;
 }
 
-// Default switch point.  The span signal says how far apart the slots of one CTA chunk lie; what that
-// costs depends on how much of the table the 126 MB L2 holds anyway: a table of up to ~2x L2 (|R| = 2^24)
-// stays cheaper than the radix join until the input is fully shuffled (threshold 0.25), while at
-// |R| = 2^27 (2 GiB table) the radix join wins from W = 2^11 on, where the signal is only 3e-4
-// (experiments/results/w_sweep*.jsonl).  Between the two the threshold falls with the cube of
-// 2*L2 / table bytes -- fitted to those two sizes, checked at 2^25 and 2^26.
+// Default switch point.  The span signal says how far apart the slots of one CTA chunk lie; what that costs depends on
+// how much of the table the 126 MB L2 holds anyway.  Fitted to the crossovers of the round-2 build (R = local_shuffle W,
+// experiments/results/w_sweep_n24.jsonl, w_sweep_n26.jsonl, w_sweep_n27.jsonl), with r = 2 L2 / table bytes:
+//   |R| = 2^24 (r = 0.94): the bitmap-claimed table wins up to W = 2^15 (signal 0.004), ties at 2^16 (0.008);
+//   |R| = 2^26 (r = 0.23): wins up to 2^14 (0.002), loses from 2^16 (0.008);
+//   |R| = 2^27 (r = 0.12): ties from 2^12 to 2^14 (0.0005 .. 0.002), loses from 2^15 (0.004).
+// Threshold 0.0068 r^0.55 (0.0066 / 0.0031 / 0.0021 at those sizes).  A table that fits L2 whole (r >= 2) keeps the
+// old 0.25 -- only a span of a quarter of L2 sends it to the radix join -- with a log-linear blend in between.
 double default_threshold(const hj_handle* h) {
   const double table_bytes = 8.0 * (double)h->slots;
-  double r = 2.0 * (double)h->l2_bytes / (table_bytes > 0 ? table_bytes : 1.0);
-  if (r > 1.0) r = 1.0;
-  return 0.25 * r * r * r;
+  const double r = 2.0 * (double)h->l2_bytes / (table_bytes > 0 ? table_bytes : 1.0);
+  constexpr double kAtOne = 0.0068, kInL2 = 0.25;
+  if (r >= 2.0) return kInL2;
+  if (r >= 1.0) return exp(log(kAtOne) + (log(kInL2) - log(kAtOne)) * (r - 1.0));
+  return kAtOne * pow(r, 0.55);
 }
 
 SegMap whole(u64 n) {
