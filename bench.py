@@ -871,10 +871,10 @@ def run_b200(args):
                                 f"radix join |R|=2^{args.log_r} PK x |S|=2^{args.log_s} FK in total, split over {G} GPUs "
                                 f"(BASELINE configs[4] is 2^30 x 2^33)"),
                    "algo": args.algo, "radix_bits": int(last.radix_bits), "passes": int(last.passes),
-                   "tuples_per_step": tuples, "l2": "inputs (9 GiB/GPU) larger than L2, no flush needed",
+                   "tuples_per_step": tuples, "l2": f"inputs ({8 * (rk.n + rk.m) / 2**30:.0f} GiB/GPU) larger than L2, no flush needed",
                    "exchange": "none" if G == 1 else (f"pipelined over the copy engines: local scatter by (owner GPU, low {rk.b1} bits) into "
                                                       f"fixed-capacity regions, one device-to-device copy per (peer, stage) over NVLink "
-                                                      f"(CUDA IPC) under pass 2 + join of the previous stage; S in {rk.chunks} chunks"
+                                                      f"(CUDA IPC) under pass 2 + join of the previous stage, ring order kept in lock step by tokens; S in {rk.chunks} chunks"
                                                       if args.exchange == "xchg" else
                                                       "fused with radix pass 1, histogram-free: TMA stores into fixed-capacity regions of the owners' pass-1 buffers over NVLink (CUDA IPC)"
                                                       if args.exchange == "regions" else

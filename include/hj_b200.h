@@ -245,13 +245,18 @@ int hj_join_regions(hj_handle *h, const uint64_t *R1, uint64_t n, const uint64_t
 /* ---- pipelined exchange over the copy engines (multi-GPU, round 2) ---------------------------
  * The SMs never touch NVLink: every rank scatters a STAGE of its slices (stage 0 = R, stages 1..s_chunks =
  * equal chunks of S by position; a join is additive over disjoint parts of S) LOCALLY by (owner GPU, low
- * pass-1 key bits) into per-destination blocks of fixed-capacity regions; one stream per peer ships block
+ * pass-1 key bits) into per-destination blocks of fixed-capacity regions; one copy stream per rank ships block
  * `dest` to rank dest's receive WINDOW with a plain device-to-device copy (copy engines over NVLink through
- * the CUDA-IPC mapping), followed by the block's fill levels and a flag word carrying the step's epoch.  The
- * compute stream scatters stage t+1, then waits on the device (bounded: 10 s) for stage t's flags, runs radix
- * pass 2 on what arrived (parallel_radix_join.c:402-440 with one parent per (source, low bits) region) and
- * joins it -- the copies of stage t+1 run under pass 2 + join of stage t, and nothing but the final counter
- * read-back synchronises with the host.
+ * the CUDA-IPC mapping), followed by the block's fill levels and a flag word carrying the step's epoch -- stage
+ * after stage, the peers of a stage in ring order (rank+1 first), and with more than two ranks the ring is kept
+ * in lock step: before shipping round k+1 a rank's copy stream waits (cuStreamWaitValue64 on a word of its own
+ * window) for its successor's "round k done" token, so no GPU ever receives from two senders at once.  Blocks
+ * start on 2 MiB boundaries and every allocation is a whole number of 2 MiB pages (the copy engines write into a
+ * small-page allocation at 530 instead of 760 GB/s).  The compute stream scatters all stages, then stage by stage
+ * waits on the device (bounded: 10 s) for the stage's flags, runs radix pass 2 on what arrived
+ * (parallel_radix_join.c:402-440 with one parent per (source, low bits) region) and joins the chunks in groups
+ * (one group at 2 ranks, two at 4, one per chunk from 8 on) -- the copies of the later stages run under pass 2 +
+ * join of the earlier ones, and nothing but the final counter read-back synchronises with the host.
  *   hj_xchg_create   plans the stages, allocates the send blocks and this rank's window (one allocation:
  *                    export it with hj_ipc_export); the handle must be HJ_ALGO_RADIX with an explicit
  *                    2-pass plan (num_partitions, passes = 2, pass1_bits) identical on all ranks,
