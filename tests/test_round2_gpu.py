@@ -352,3 +352,41 @@ def test_wide_tuples_refuse_what_is_not_built(hj):
     with pytest.raises(hj.HJError) as e:
         hj.HashJoin("adaptive", tuple_bytes=16)
     assert e.value.code == hj.HJ_EINVAL
+
+
+# ---- the reference's own inputs at sizes beyond the small parity cases ("what's weak") ----
+def test_mc_pk_fk_at_2_22_by_2_25(hj):
+    """create_relation_pk / create_relation_fk (mc/src/generator.c:241-282,409-445; seeds of mc/src/main.c) at
+    2^22 x 2^25: every S tuple finds its one R tuple.  Expected pair sum computed with numpy (R indexed by key):
+    the C oracle needs 15 s at this size and is pinned against the same definition on the small cases."""
+    n, m = 1 << 22, 1 << 25
+    R, S = hj.mc_relation_pk(n), hj.mc_relation_fk(m, n)
+    key = np.uint64(0xFFFFFFFF)
+    by_key = np.zeros(n + 1, dtype=np.uint64)
+    by_key[(R & key).astype(np.int64)] = R                       # PK: keys 1..n, each once
+    assert (by_key[1:] != 0).all()
+    with np.errstate(over="ignore"):
+        want = (m, int((by_key[(S & key).astype(np.int64)] + S).sum(dtype=np.uint64)))
+    for algo in ("radix", "adaptive", "atomic"):
+        with hj.HashJoin(algo, key_mask=0xFFFFFFFF) as h:
+            res = h.join(R, S)
+            assert (res.matches, res.checksum) == want, algo
+            assert res.zero_keys == 0
+
+
+@pytest.mark.parametrize("log_w", [8, 12, 16, 20, 22])
+def test_local_shuffle_windows_at_2_22(hj, log_w):
+    """DataGen local_shuffle with --shuffleRange 2^8 .. 2^22 (experiments/motivation.sh:21-24) at |R| = |S| = 2^22,
+    S = sorted 1..n (main.cpp:93): unique keys, so matches = n and the checksum has the closed form n(n+1); every
+    algorithm, and the adaptive switch whichever way it goes."""
+    n = 1 << 22
+    R = hj.generate_data("local_shuffle", n, n, 1 << log_w)
+    S = hj.generate_data("sorted", n)
+    for algo in ("atomic", "nocc", "radix", "adaptive"):
+        with hj.HashJoin(algo) as h:
+            res = h.join(R, S)
+            assert (res.matches, res.checksum) == (n, n * (n + 1)), (algo, log_w)
+            if algo in ("atomic", "nocc"):
+                sums = h.checksums(R)
+                assert sums.input_sum == n * (n + 1) // 2
+                assert (sums.table_sum + sums.overflow_sum) % (1 << 64) == sums.input_sum
